@@ -1,0 +1,231 @@
+/*
+ * hetb200.h — C ABI of libhetb200.so: B200-native (sm_100a) kernels for the
+ * relational-GNN hot path of K-Wu/HET (Hector).
+ *
+ * This is the drop-in boundary. Every entry point takes plain device pointers
+ * and sizes (no torch types), runs on the CUDA stream passed as `stream`
+ * (a cudaStream_t cast to void*), enqueues work and returns without
+ * synchronising. Return value: 0 on success, a negative HETB_E* code on bad
+ * arguments, a positive cudaError_t if a launch failed.
+ *
+ * The torch shim (het_b200/csrc/torch_bindings.cpp) registers the SAME op
+ * names the reference registers under `torch.ops.torch_hrt.*` and forwards
+ * to these functions. Each declaration cites the reference interface it
+ * replaces (paths relative to the reference repo root).
+ *
+ * Conventions (same as the reference):
+ *   - all index arrays are int64, contiguous, device resident;
+ *   - all float arrays are fp32, contiguous, device resident;
+ *   - "row" = source node, "col" = destination node in the original
+ *     orientation; in-CSR rows are destinations, out-CSR rows are sources;
+ *   - `eids[p]` maps position p of a format to the row of a per-edge tensor;
+ *   - H = heads, F = features per head, D = H*F.
+ */
+#ifndef HETB200_H_
+#define HETB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HETB_OK 0
+#define HETB_EINVAL (-1)      /* null pointer / negative size */
+#define HETB_EUNSUPPORTED (-2) /* shape or kind outside what is implemented */
+#define HETB_ENOMEM (-3)      /* scratch allocation failed */
+
+/* ABI version and a printable build string (replaces
+ * hrt/buildutils/genutils/gen_headers.py:17-40 `build_debug_info`). */
+int hetb_abi_version(void);
+const char *hetb_build_info(void);
+/* Number of kernel launches issued by this library since process start
+ * (bench.py reports it as `gpu_launches`). */
+int64_t hetb_launch_count(void);
+
+/* ------------------------------------------------------------------------
+ * Relation-typed linear layer (segment MM, gather-MM-scatter)
+ * ---------------------------------------------------------------------- */
+
+/* Y[c_idx?[i], h, :] (=|+=) A[a_idx?[i], (a_heads==1 ? 0 : h), :] · W[s, h, :, :]
+ * for every segment s and every row i in [seg_ptrs[s], seg_ptrs[s+1]).
+ *   A  : [*, a_heads, K]      W : [S, H, K, N]      Y : [*, c_heads, N]
+ *   a_idx / c_idx may be NULL (identity).  c_heads is H, or 1 with
+ *   accumulate!=0, in which case the H per-head results are summed.
+ *   accumulate!=0 adds into Y with atomics (rows may repeat in c_idx).
+ * Replaces: rgnn_relational_matmul (OpExport/RGNNOps.inc.h:238-295 →
+ * RGNN/my_shmem_sgemm_func.cu.h:504-531), its ACGatherScatterListIdentical
+ * twin (:629-664), rgnn_relational_matmul_no_scatter_gather_list
+ * (RGNNOps.inc.h:21-88 → my_shmem_sgemm_func.cu.h:538-564) and the delta-
+ * input halves of their backward ops (RGNNOps.inc.h:946-1010, 664-753 →
+ * my_shmem_sgemm_func.cu.h:566-595, 711-745), which are the same contraction
+ * with the pre-transposed weight and the index roles swapped. */
+int hetb_segment_mm(const float *A, const int64_t *a_idx, int a_heads,
+                    const float *W, float *Y, const int64_t *c_idx,
+                    int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
+                    int64_t num_rows, int H, int K, int N, int accumulate,
+                    void *stream);
+
+/* dW[s, h, :, :] += Σ_{i in segment s} A[a_idx?[i], (a_heads==1?0:h), :]^T
+ *                                     · G[g_idx?[i], (g_heads==1?0:h), :]
+ *   A : [*, a_heads, K]   G : [*, g_heads, N]   dW : [S, H, K, N] (caller
+ *   zero-fills, as the reference's Python does: backend/rgnn_layers_and_funcs.py:52-55).
+ * Replaces the delta-weight halves of the backward ops
+ * (RGNNOps.inc.h:756-944 → my_shmem_sgemm_func.cu.h:597-628, 747-776). */
+int hetb_segment_mm_grad_w(const float *A, const int64_t *a_idx, int a_heads,
+                           const float *G, const int64_t *g_idx, int g_heads,
+                           float *dW, const int64_t *seg_ptrs,
+                           int64_t num_segs, int64_t num_rows, int H, int K,
+                           int N, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Edge-wise inner product (HGT attention score)
+ * ---------------------------------------------------------------------- */
+
+/* out[eids[i], h] = Σ_f left[eids[i], h, f] · right[row_idx[i], h, f]
+ * Replaces rgnn_inner_product_right_node_separatecoo, kind 0
+ * (RGNNOps.inc.h:609-658 → RGNN/InnerProductEdgeParallel.cu.h:13-113). */
+int hetb_inner_product_fwd(const int64_t *eids, const int64_t *row_idx,
+                           int64_t num_edges, const float *left,
+                           const float *right, float *out, int H, int F,
+                           void *stream);
+
+/* grad_left[eids[i],h,:]  = g[eids[i],h] · right[row_idx[i],h,:]
+ * grad_right[row_idx[i],h,:] += g[eids[i],h] · left[eids[i],h,:]   (summed —
+ * the reference stores instead of accumulating, InnerProductEdgeParallel.cu.h:180-183,
+ * a known bug we do not reproduce).  grad_right must arrive zero-filled.
+ * Replaces backward_inner_product_right_node_separatecoo
+ * (RGNNOps.inc.h:1131-1181 → InnerProductEdgeParallel.cu.h:119-202). */
+int hetb_inner_product_bwd(const int64_t *eids, const int64_t *row_idx,
+                           int64_t num_edges, const float *left,
+                           const float *right, const float *grad_out,
+                           float *grad_left, float *grad_right, int H, int F,
+                           void *stream);
+
+/* ------------------------------------------------------------------------
+ * RGAT edge attention pipeline (logits → edge softmax → aggregation)
+ * ---------------------------------------------------------------------- */
+
+/* Over in-CSR rows d (destinations), positions p in [row_ptr[d], row_ptr[d+1]):
+ *   e = eids[p];  x = el[e,h] + er[e,h];
+ *   exp_out[e,h] = exp(x > 0 ? x : slope*x);   sum[d,h] = Σ_p exp_out[e,h];
+ *   ret[d,h,:] = Σ_p exp_out[e,h] / sum[d,h] · feat[e,h,:]
+ * sum/exp_out/ret may arrive uninitialised (backend/rgat_layers_and_funcs.py:656-664);
+ * every element is written. Rows without in-edges get sum = 0, ret = 0.
+ * Replaces relational_fused_gat_csr with CompactAsOfNodeFlag=false
+ * (OpExport/RGATOps.inc.h:251-277 → GAT/FusedGAT.cu.h:33-222). */
+int hetb_rgat_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
+                      int64_t num_rows, int64_t num_edges, const float *feat,
+                      const float *el, const float *er, float *sum,
+                      float *exp_out, float *ret, int H, int F, float slope,
+                      void *stream);
+
+/* Edge-parallel twin over a COO (dst = col_idx[i], e = eids[i]); same outputs.
+ * Replaces relational_fused_gat_separate_coo, kind 0
+ * (RGATOps.inc.h:170-245 → RGAT/RGATKernelsSeparateCOO.cu.h:17-215). */
+int hetb_rgat_fwd_coo(const int64_t *col_idx, const int64_t *eids,
+                      int64_t num_nodes, int64_t num_edges, const float *feat,
+                      const float *el, const float *er, float *sum,
+                      float *exp_out, float *ret, int H, int F, float slope,
+                      void *stream);
+
+/* For every edge position p (dst d = dst_idx[p], e = eids[p]):
+ *   a = exp_in[e,h] / sum[d,h];
+ *   grad_feat[e,h,:] = a · gout[d,h,:]
+ *   t = Σ_f gout[d,h,f]·(feat[e,h,f] − ret[d,h,f]) · a · (el+er > 0 ? 1 : slope)
+ *   grad_el[e,h] = grad_er[e,h] = t
+ * (closed form: GAT/FusedGATBackward.cu.h:245-266). Serves both
+ * backward_relational_fused_gat_csr (RGATOps.inc.h:430-461 →
+ * FusedGATBackward.cu.h:31-148; dst_idx = out-CSR col_indices) and
+ * backward_relational_fused_gat_separate_coo (RGATOps.inc.h:465-551;
+ * dst_idx = COO col_indices). Each edge id is written exactly once, so the
+ * reference's atomics are not needed. */
+int hetb_rgat_bwd(const int64_t *dst_idx, const int64_t *eids,
+                  int64_t num_edges, const float *feat, const float *el,
+                  const float *er, const float *sum, const float *exp_in,
+                  const float *ret, const float *gout, float *grad_feat,
+                  float *grad_el, float *grad_er, int H, int F, float slope,
+                  void *stream);
+
+/* ------------------------------------------------------------------------
+ * HGT edge attention pipeline
+ * ---------------------------------------------------------------------- */
+
+/* Over in-CSR rows d: e = eids[p], r = rel[p];
+ *   t[e,h] = expf(attn[e,h] · mu[r,h]);  sum[d,h] = Σ_p t;  norm[e,h] = t/sum[d,h]
+ * t_out or norm_out may be NULL. sum is fully written (0 for empty rows).
+ * Replaces hgt_full_graph_edge_softmax_ops_csr
+ * (OpExport/HGTOps.inc.h:190-203 → HGT/HGTForwardKernels.cu.h:425-587). */
+int hetb_hgt_edge_softmax_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
+                                  const int64_t *rel, int64_t num_rows,
+                                  int64_t num_edges, const float *attn,
+                                  const float *mu, float *sum, float *t_out,
+                                  float *norm_out, int H, void *stream);
+
+/* ret[d,h,:] = Σ_p w[e,h] · msg[e,h,:], with w = score[e,h] / sum[d,h] when
+ * divide_by_sum != 0 (what the reference kernel does,
+ * HGTForwardKernels.cu.h:304-309, switch 1) and w = score[e,h] otherwise.
+ * Replaces hgt_full_graph_message_mean_aggregation_csr
+ * (HGTOps.inc.h:180-188 → HGTForwardKernels.cu.h:244-369). */
+int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
+                               int64_t num_rows, int64_t num_edges,
+                               const float *msg, const float *score,
+                               const float *sum, float *ret, int H, int F,
+                               int divide_by_sum, void *stream);
+
+/* grad_msg[e,h,:] = norm[e,h] · gout[dst_idx[p],h,:]
+ * Replaces backward_hgt_full_graph_message_mean_aggregation_csr
+ * (HGTOps.inc.h:477-487 → HGT/HGTBackwardKernels.cu.h:343-440). */
+int hetb_hgt_aggregate_bwd(const int64_t *dst_idx, const int64_t *eids,
+                           int64_t num_edges, const float *norm,
+                           const float *gout, float *grad_msg, int H, int F,
+                           void *stream);
+
+/* s = Σ_f gout[d,h,f]·(msg[e,h,f] − out[d,h,f]) · norm[e,h]
+ * grad_attn[e,h] = s · mu[r,h];   grad_mu[r,h] += s · attn[e,h]
+ * with r = rel[p] (the reference reads relation 0 for every edge in the
+ * non-compact path, HGTBackwardKernels.cu.h:533,617-618 "FIXME"; we use the
+ * edge's relation). grad_mu must arrive zero-filled.
+ * Replaces backward_hgt_full_graph_edge_softmax_ops_csr
+ * (HGTOps.inc.h:553-566 → HGTBackwardKernels.cu.h:499-627). */
+int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
+                              const int64_t *rel, int64_t num_edges,
+                              int64_t num_rels, const float *msg,
+                              const float *attn, const float *norm,
+                              const float *out, const float *gout,
+                              const float *mu, float *grad_attn,
+                              float *grad_mu, int H, int F, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Relation sort / CSR construction (bit-exact integer work, on the GPU)
+ * ---------------------------------------------------------------------- */
+
+/* Bytes of device scratch the converters below need for `num_edges` edges and
+ * keys below `max_key`. The caller allocates it (so the library never calls
+ * cudaMalloc on the hot path). */
+int64_t hetb_sort_scratch_bytes(int64_t num_edges, int64_t max_key);
+
+/* Stable sort of edge tuples by `key` (0 <= key < num_keys): writes
+ * ptrs[num_keys+1] (exclusive scan of key counts) and, for each payload
+ * array in[j] (j < num_payload <= 4), out[j] = in[j] permuted into key order.
+ * Order inside one key = original order. This one primitive builds:
+ *   COO -> CSR          (key = src, payloads dst/rel/eid;
+ *                        python/utils_lite/sparse_matrix_converters.py:7-39, stable)
+ *   CSR transpose       (key = col, payloads expanded-row/rel/eid;
+ *                        DataConverters.inc.h:283-344 → MyHyb/MyHyb.h:31-75)
+ *   relation sort       (key = rel after an eid sort; MyHyb.h:1099-1150 +
+ *                        python/utils/coo_sorters.py:156-170)              */
+int hetb_stable_sort_by_key(const int64_t *key, int64_t num_edges,
+                            int64_t num_keys, int num_payload,
+                            const int64_t *const *in, int64_t *const *out,
+                            int64_t *ptrs, void *scratch,
+                            int64_t scratch_bytes, void *stream);
+
+/* row_idx[p] = r for p in [row_ptr[r], row_ptr[r+1]) — CSR → COO row expansion. */
+int hetb_expand_row_ptr(const int64_t *row_ptr, int64_t num_rows,
+                        int64_t num_edges, int64_t *row_idx, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HETB200_H_ */
