@@ -1,0 +1,654 @@
+// torch_hrt operator surface: registers the SAME op names and argument orders
+// that the reference registers from hrt/include/DGLHackKernel/OpExport/*.inc.h
+// (TORCH_LIBRARY_FRAGMENT(torch_hrt, ...)), and forwards every call to the
+// C ABI of libhetb200.so (include/hetb200.h). No math lives here: this file
+// only validates tensors, unpacks pointers/sizes and picks the current stream.
+//
+// There is deliberately no CPU implementation: every compute op requires CUDA
+// tensors and fails loudly otherwise.
+#include <ATen/ATen.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <torch/library.h>
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "hetb200.h"
+
+namespace {
+
+using at::Tensor;
+using TensorDict = c10::Dict<std::string, at::Tensor>;
+
+void *stream_of(const Tensor &t) {
+  return (void *)c10::cuda::getCurrentCUDAStream(t.device().index()).stream();
+}
+
+void check_rc(int rc, const char *op) {
+  if (rc == 0) return;
+  const char *why = rc == HETB_EINVAL          ? "invalid argument"
+                    : rc == HETB_EUNSUPPORTED ? "shape/kind not supported by hetb200"
+                    : rc == HETB_ENOMEM       ? "out of scratch memory"
+                                              : "CUDA launch error";
+  TORCH_CHECK(false, "torch_hrt::", op, ": ", why, " (code ", rc, ")");
+}
+
+const float *f32(const Tensor &t, const char *op, const char *name) {
+  TORCH_CHECK(t.is_cuda(), "torch_hrt::", op, ": `", name,
+              "` must be a CUDA tensor (hetb200 has no CPU path)");
+  TORCH_CHECK(t.scalar_type() == at::kFloat, "torch_hrt::", op, ": `", name,
+              "` must be float32");
+  TORCH_CHECK(t.is_contiguous(), "torch_hrt::", op, ": `", name,
+              "` must be contiguous");
+  return t.data_ptr<float>();
+}
+float *f32w(Tensor &t, const char *op, const char *name) {
+  return const_cast<float *>(f32(t, op, name));
+}
+const int64_t *i64(const Tensor &t, const char *op, const char *name) {
+  TORCH_CHECK(t.is_cuda(), "torch_hrt::", op, ": `", name,
+              "` must be a CUDA tensor (hetb200 has no CPU path)");
+  TORCH_CHECK(t.scalar_type() == at::kLong, "torch_hrt::", op, ": `", name,
+              "` must be int64");
+  TORCH_CHECK(t.is_contiguous(), "torch_hrt::", op, ": `", name,
+              "` must be contiguous");
+  return t.data_ptr<int64_t>();
+}
+// product of all dims after the first (the reference's SeastarComputeXLength)
+int64_t xlen(const Tensor &t) {
+  int64_t r = 1;
+  for (int64_t d = 1; d < t.dim(); ++d) r *= t.size(d);
+  return r;
+}
+void not_implemented(const char *op) {
+  TORCH_CHECK(false, "torch_hrt::", op,
+              " is registered for interface compatibility but is outside the "
+              "hot path implemented by hetb200");
+}
+
+// ---------------------------------------------------------------- misc ---
+void build_debug_info() { std::printf("%s\n", hetb_build_info()); }
+int64_t hetb200_launch_count() { return hetb_launch_count(); }
+
+// ------------------------------------------------------------ RGNN ops ---
+// OpExport/RGNNOps.inc.h:238-295
+void rgnn_relational_matmul(TensorDict args, int64_t kind, Tensor &weights,
+                            Tensor &node_feat, Tensor &ret,
+                            bool input_num_head_one) {
+  const char *op = "rgnn_relational_matmul";
+  TORCH_CHECK(weights.dim() == 4, op, ": weights must be [R,H,in,out/H]");
+  const int H = (int)weights.size(1), K = (int)weights.size(2),
+            N = (int)weights.size(3);
+  const int a_heads = input_num_head_one ? 1 : H;
+  c10::cuda::CUDAGuard guard(ret.device());
+  if (kind == 0) {
+    Tensor rel_ptrs = args.at("separate_coo_rel_ptrs");
+    Tensor gather = args.at("separate_coo_node_indices");
+    Tensor eids = args.at("separate_coo_eids");
+    check_rc(hetb_segment_mm(f32(node_feat, op, "node_feat"),
+                             i64(gather, op, "separate_coo_node_indices"),
+                             a_heads, f32(weights, op, "weights"),
+                             f32w(ret, op, "ret"),
+                             i64(eids, op, "separate_coo_eids"), H,
+                             i64(rel_ptrs, op, "separate_coo_rel_ptrs"),
+                             rel_ptrs.numel() - 1, eids.numel(), H, K, N, 0,
+                             stream_of(ret)),
+             op);
+  } else if (kind == 1) {  // CompactAsOfNodeKind::Enabled: rows are (rel, unique node)
+    Tensor rel_ptrs = args.at("unique_srcs_and_dests_rel_ptrs");
+    Tensor nodes = args.at("unique_srcs_and_dests_node_indices");
+    check_rc(hetb_segment_mm(f32(node_feat, op, "node_feat"),
+                             i64(nodes, op, "unique_srcs_and_dests_node_indices"),
+                             a_heads, f32(weights, op, "weights"),
+                             f32w(ret, op, "ret"), nullptr, H,
+                             i64(rel_ptrs, op, "unique_srcs_and_dests_rel_ptrs"),
+                             rel_ptrs.numel() - 1, nodes.numel(), H, K, N, 0,
+                             stream_of(ret)),
+             op);
+  } else {
+    check_rc(HETB_EUNSUPPORTED, op);
+  }
+}
+
+// OpExport/RGNNOps.inc.h:946-1010. weights_transposed is [R,H,out/H,in].
+void backward_rgnn_relational_matmul(TensorDict args, int64_t kind,
+                                     Tensor &weights_transposed,
+                                     Tensor &node_feat, Tensor &gradout,
+                                     Tensor &grad_node_feat,
+                                     Tensor &grad_weights,
+                                     bool input_num_head_one) {
+  const char *op = "backward_rgnn_relational_matmul";
+  TORCH_CHECK(weights_transposed.dim() == 4, op, ": weights must be 4-D");
+  const int H = (int)weights_transposed.size(1),
+            N = (int)weights_transposed.size(2),
+            K = (int)weights_transposed.size(3);
+  const int a_heads = input_num_head_one ? 1 : H;
+  c10::cuda::CUDAGuard guard(gradout.device());
+  void *st = stream_of(gradout);
+  const int64_t *rel_ptrs, *gather, *scatter;
+  int64_t R, M;
+  bool identical = false;
+  if (kind == 0) {
+    Tensor t_rel = args.at("separate_coo_rel_ptrs");
+    Tensor t_gather = args.at("separate_coo_node_indices");
+    Tensor t_eids = args.at("separate_coo_eids");
+    rel_ptrs = i64(t_rel, op, "separate_coo_rel_ptrs");
+    gather = i64(t_gather, op, "separate_coo_node_indices");
+    scatter = i64(t_eids, op, "separate_coo_eids");
+    R = t_rel.numel() - 1;
+    M = t_eids.numel();
+    // same pointer-equality dispatch as the reference (RGNNOps.inc.h:253):
+    // the gather list is the edge-id permutation, so no output row repeats.
+    identical = (gather == scatter);
+  } else if (kind == 1) {
+    Tensor t_rel = args.at("unique_srcs_and_dests_rel_ptrs");
+    Tensor t_nodes = args.at("unique_srcs_and_dests_node_indices");
+    rel_ptrs = i64(t_rel, op, "unique_srcs_and_dests_rel_ptrs");
+    gather = i64(t_nodes, op, "unique_srcs_and_dests_node_indices");
+    scatter = nullptr;
+    R = t_rel.numel() - 1;
+    M = t_nodes.numel();
+  } else {
+    check_rc(HETB_EUNSUPPORTED, op);
+    return;
+  }
+  const int accumulate = (identical && a_heads == H) ? 0 : 1;
+  // dX[gather[i]] += dY[scatter[i]] · W^T[r]
+  check_rc(hetb_segment_mm(f32(gradout, op, "gradout"), scatter, H,
+                           f32(weights_transposed, op, "weights_transposed"),
+                           f32w(grad_node_feat, op, "grad_node_feat"), gather,
+                           a_heads, rel_ptrs, R, M, H, N, K, accumulate, st),
+           op);
+  // dW[r] += X[gather[i]]^T · dY[scatter[i]]
+  check_rc(hetb_segment_mm_grad_w(f32(node_feat, op, "node_feat"), gather,
+                                  a_heads, f32(gradout, op, "gradout"), scatter,
+                                  H, f32w(grad_weights, op, "grad_weights"),
+                                  rel_ptrs, R, M, H, K, N, st),
+           op);
+}
+
+// OpExport/RGNNOps.inc.h:83-88
+void rgnn_relational_matmul_no_scatter_gather_list(Tensor &ntype_offset_ptrs,
+                                                   Tensor &weights,
+                                                   Tensor &inputs,
+                                                   Tensor &ret) {
+  const char *op = "rgnn_relational_matmul_no_scatter_gather_list";
+  TORCH_CHECK(weights.dim() == 4, op, ": weights must be [T,H,in,out]");
+  const int H = (int)weights.size(1), K = (int)weights.size(2),
+            N = (int)weights.size(3);
+  const int64_t M = inputs.size(0);
+  const int a_heads = (xlen(inputs) == (int64_t)H * K) ? H : 1;
+  TORCH_CHECK(xlen(inputs) == (int64_t)a_heads * K, op, ": inputs row length ",
+              xlen(inputs), " does not match weights");
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_segment_mm(f32(inputs, op, "inputs"), nullptr, a_heads,
+                           f32(weights, op, "weights"), f32w(ret, op, "ret"),
+                           nullptr, H, i64(ntype_offset_ptrs, op, "ntype_offset_ptrs"),
+                           ntype_offset_ptrs.numel() - 1, M, H, K, N, 0,
+                           stream_of(ret)),
+           op);
+}
+
+// OpExport/RGNNOps.inc.h:744-753
+void backward_rgnn_relational_matmul_no_scatter_gather_list(
+    Tensor &ntype_offset_ptrs, Tensor &weights_transposed,
+    Tensor &node_feat_input, Tensor &grad_node_feat_output,
+    Tensor &grad_node_feat_input, Tensor &grad_weights) {
+  const char *op = "backward_rgnn_relational_matmul_no_scatter_gather_list";
+  TORCH_CHECK(weights_transposed.dim() == 4, op, ": weights must be 4-D");
+  const int H = (int)weights_transposed.size(1),
+            N = (int)weights_transposed.size(2),
+            K = (int)weights_transposed.size(3);
+  const int64_t M = node_feat_input.size(0);
+  const int a_heads = (xlen(node_feat_input) == (int64_t)H * K) ? H : 1;
+  c10::cuda::CUDAGuard guard(grad_node_feat_output.device());
+  void *st = stream_of(grad_node_feat_output);
+  const int64_t *ptrs = i64(ntype_offset_ptrs, op, "ntype_offset_ptrs");
+  const int64_t T = ntype_offset_ptrs.numel() - 1;
+  const int accumulate = (a_heads == 1 && H > 1) ? 1 : 0;
+  check_rc(hetb_segment_mm(f32(grad_node_feat_output, op, "grad_node_feat_output"),
+                           nullptr, H,
+                           f32(weights_transposed, op, "weights_transposed"),
+                           f32w(grad_node_feat_input, op, "grad_node_feat_input"),
+                           nullptr, a_heads, ptrs, T, M, H, N, K, accumulate, st),
+           op);
+  check_rc(hetb_segment_mm_grad_w(
+               f32(node_feat_input, op, "node_feat_input"), nullptr, a_heads,
+               f32(grad_node_feat_output, op, "grad_node_feat_output"), nullptr,
+               H, f32w(grad_weights, op, "grad_weights"), ptrs, T, M, H, K, N, st),
+           op);
+}
+
+// OpExport/RGNNOps.inc.h:609-658
+void rgnn_inner_product_right_node_separatecoo(
+    TensorDict args, int64_t kind, Tensor &rel_ptrs, Tensor &eids,
+    Tensor &row_indices, Tensor &col_indices, Tensor &left_side_data,
+    Tensor &right_node_vectors, Tensor &edge_inner_product) {
+  const char *op = "rgnn_inner_product_right_node_separatecoo";
+  (void)args; (void)rel_ptrs; (void)col_indices;
+  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  TORCH_CHECK(right_node_vectors.dim() == 3, op,
+              ": right_node_vectors must be [N,H,F]");
+  const int H = (int)right_node_vectors.size(1), F = (int)right_node_vectors.size(2);
+  c10::cuda::CUDAGuard guard(edge_inner_product.device());
+  check_rc(hetb_inner_product_fwd(
+               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"),
+               eids.numel(), f32(left_side_data, op, "left_side_data"),
+               f32(right_node_vectors, op, "right_node_vectors"),
+               f32w(edge_inner_product, op, "edge_inner_product"), H, F,
+               stream_of(edge_inner_product)),
+           op);
+}
+
+// OpExport/RGNNOps.inc.h:1131-1181
+void backward_inner_product_right_node_separatecoo(
+    TensorDict args, int64_t kind, Tensor &rel_ptrs, Tensor &eids,
+    Tensor &row_indices, Tensor &col_indices, Tensor &left_side_data,
+    Tensor &right_node_vectors, Tensor &grad_inner_product,
+    Tensor &grad_left_side_data, Tensor &grad_right_node_vectors) {
+  const char *op = "backward_inner_product_right_node_separatecoo";
+  (void)args; (void)rel_ptrs; (void)col_indices;
+  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  const int H = (int)right_node_vectors.size(1), F = (int)right_node_vectors.size(2);
+  c10::cuda::CUDAGuard guard(grad_inner_product.device());
+  check_rc(hetb_inner_product_bwd(
+               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"),
+               eids.numel(), f32(left_side_data, op, "left_side_data"),
+               f32(right_node_vectors, op, "right_node_vectors"),
+               f32(grad_inner_product, op, "grad_inner_product"),
+               f32w(grad_left_side_data, op, "grad_left_side_data"),
+               f32w(grad_right_node_vectors, op, "grad_right_node_vectors"), H,
+               F, stream_of(grad_inner_product)),
+           op);
+}
+
+// ------------------------------------------------------------ RGAT ops ---
+// OpExport/RGATOps.inc.h:251-277
+void relational_fused_gat_csr(Tensor &incsr_row_ptr, Tensor &incsr_col_indices,
+                              Tensor &incsr_eids, Tensor &incsr_reltypes,
+                              Tensor &unique_rel_ptrs,
+                              Tensor &unique_node_indices, Tensor &feat_src,
+                              Tensor &el, Tensor &er, Tensor &sum, Tensor &exp,
+                              Tensor &ret, double slope,
+                              bool compact_as_of_node) {
+  const char *op = "relational_fused_gat_csr";
+  (void)incsr_col_indices; (void)incsr_reltypes; (void)unique_rel_ptrs;
+  (void)unique_node_indices;
+  if (compact_as_of_node) check_rc(HETB_EUNSUPPORTED, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_rgat_fwd_csr(i64(incsr_row_ptr, op, "incsr_row_ptr"),
+                             i64(incsr_eids, op, "incsr_eids"),
+                             incsr_row_ptr.numel() - 1, incsr_eids.numel(),
+                             f32(feat_src, op, "feat_src"), f32(el, op, "el"),
+                             f32(er, op, "er"), f32w(sum, op, "sum"),
+                             f32w(exp, op, "exp"), f32w(ret, op, "ret"), H, F,
+                             (float)slope, stream_of(ret)),
+           op);
+}
+
+// OpExport/RGATOps.inc.h:430-461
+void backward_relational_fused_gat_csr(
+    Tensor &outcsr_row_ptr, Tensor &outcsr_col_indices, Tensor &outcsr_eids,
+    Tensor &outcsr_reltypes, Tensor &unique_rel_ptrs,
+    Tensor &unique_node_indices, Tensor &feat_src, Tensor &el, Tensor &er,
+    Tensor &sum, Tensor &exp, Tensor &ret, Tensor &gradout,
+    Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope,
+    bool compact_as_of_node) {
+  const char *op = "backward_relational_fused_gat_csr";
+  (void)outcsr_row_ptr; (void)outcsr_reltypes; (void)unique_rel_ptrs;
+  (void)unique_node_indices;
+  if (compact_as_of_node) check_rc(HETB_EUNSUPPORTED, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_rgat_bwd(i64(outcsr_col_indices, op, "outcsr_col_indices"),
+                         i64(outcsr_eids, op, "outcsr_eids"),
+                         outcsr_eids.numel(), f32(feat_src, op, "feat_src"),
+                         f32(el, op, "el"), f32(er, op, "er"),
+                         f32(sum, op, "sum"), f32(exp, op, "exp"),
+                         f32(ret, op, "ret"), f32(gradout, op, "gradout"),
+                         f32w(grad_feat_src, op, "grad_feat_src"),
+                         f32w(grad_el, op, "grad_el"),
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope,
+                         stream_of(gradout)),
+           op);
+}
+
+// OpExport/RGATOps.inc.h:170-245
+void relational_fused_gat_separate_coo(Tensor &eids, Tensor &rel_ptrs,
+                                       Tensor &row_indices, Tensor &col_indices,
+                                       int64_t kind, TensorDict args,
+                                       Tensor &feat_src, Tensor &el, Tensor &er,
+                                       Tensor &sum, Tensor &exp, Tensor &ret,
+                                       double slope) {
+  const char *op = "relational_fused_gat_separate_coo";
+  (void)rel_ptrs; (void)row_indices; (void)args;
+  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_rgat_fwd_coo(i64(col_indices, op, "col_indices"),
+                             i64(eids, op, "eids"), ret.size(0), eids.numel(),
+                             f32(feat_src, op, "feat_src"), f32(el, op, "el"),
+                             f32(er, op, "er"), f32w(sum, op, "sum"),
+                             f32w(exp, op, "exp"), f32w(ret, op, "ret"), H, F,
+                             (float)slope, stream_of(ret)),
+           op);
+}
+
+// OpExport/RGATOps.inc.h:465-551
+void backward_relational_fused_gat_separate_coo(
+    Tensor &eids, Tensor &rel_ptrs, Tensor &row_indices, Tensor &col_indices,
+    int64_t kind, TensorDict args, Tensor &feat_src, Tensor &el, Tensor &er,
+    Tensor &sum, Tensor &exp, Tensor &ret, Tensor &gradout,
+    Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope) {
+  const char *op = "backward_relational_fused_gat_separate_coo";
+  (void)rel_ptrs; (void)row_indices; (void)args;
+  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_rgat_bwd(i64(col_indices, op, "col_indices"),
+                         i64(eids, op, "eids"), eids.numel(),
+                         f32(feat_src, op, "feat_src"), f32(el, op, "el"),
+                         f32(er, op, "er"), f32(sum, op, "sum"),
+                         f32(exp, op, "exp"), f32(ret, op, "ret"),
+                         f32(gradout, op, "gradout"),
+                         f32w(grad_feat_src, op, "grad_feat_src"),
+                         f32w(grad_el, op, "grad_el"),
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope,
+                         stream_of(gradout)),
+           op);
+}
+
+// ------------------------------------------------------------- HGT ops ---
+// OpExport/HGTOps.inc.h:190-203
+void hgt_full_graph_edge_softmax_ops_csr(
+    Tensor &row_ptr, Tensor &col_indices, Tensor &eids, Tensor &reltypes,
+    Tensor &unnormalized_attn_score, Tensor &mu,
+    Tensor &edgesoftmax_sum_per_node,
+    Tensor &mu_softmax_applied_unnormalized_attn_score,
+    Tensor &normalized_attn_score) {
+  const char *op = "hgt_full_graph_edge_softmax_ops_csr";
+  (void)col_indices;
+  const int H = (int)xlen(unnormalized_attn_score);
+  c10::cuda::CUDAGuard guard(normalized_attn_score.device());
+  check_rc(hetb_hgt_edge_softmax_fwd_csr(
+               i64(row_ptr, op, "row_ptr"), i64(eids, op, "eids"),
+               i64(reltypes, op, "reltypes"), row_ptr.numel() - 1, eids.numel(),
+               f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
+               f32(mu, op, "mu"),
+               f32w(edgesoftmax_sum_per_node, op, "edgesoftmax_sum_per_node"),
+               f32w(mu_softmax_applied_unnormalized_attn_score, op,
+                    "mu_softmax_applied_unnormalized_attn_score"),
+               f32w(normalized_attn_score, op, "normalized_attn_score"), H,
+               stream_of(normalized_attn_score)),
+           op);
+}
+
+// OpExport/HGTOps.inc.h:180-188 (reltypes before eids, as in the reference).
+// Like the reference kernel (HGTForwardKernels.cu.h:304-309) this divides
+// edge_attn_score by edgesoftmax_sum_per_node: pass the UN-normalised
+// exp(mu*score) tensor to get a softmax-weighted sum.
+void hgt_full_graph_message_mean_aggregation_csr(
+    Tensor &incsr_row_ptrs, Tensor &incsr_col_indices, Tensor &incsr_reltypes,
+    Tensor &incsr_eids, Tensor &edge_messages, Tensor &edge_attn_score,
+    Tensor &edgesoftmax_sum_per_node, Tensor &mu, Tensor &ret) {
+  const char *op = "hgt_full_graph_message_mean_aggregation_csr";
+  (void)incsr_col_indices; (void)incsr_reltypes; (void)mu;
+  const int H = (int)xlen(edge_attn_score);
+  const int F = (int)(xlen(edge_messages) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_hgt_aggregate_fwd_csr(
+               i64(incsr_row_ptrs, op, "incsr_row_ptrs"),
+               i64(incsr_eids, op, "incsr_eids"), incsr_row_ptrs.numel() - 1,
+               incsr_eids.numel(), f32(edge_messages, op, "edge_messages"),
+               f32(edge_attn_score, op, "edge_attn_score"),
+               f32(edgesoftmax_sum_per_node, op, "edgesoftmax_sum_per_node"),
+               f32w(ret, op, "ret"), H, F, 1, stream_of(ret)),
+           op);
+}
+
+// OpExport/HGTOps.inc.h:477-487
+void backward_hgt_full_graph_message_mean_aggregation_csr(
+    Tensor &outcsr_row_ptrs, Tensor &outcsr_col_indices,
+    Tensor &outcsr_reltypes, Tensor &outcsr_eids,
+    Tensor &edgesoftmax_sum_per_node, Tensor &normalized_attn_score,
+    Tensor &gradout, Tensor &grad_message) {
+  const char *op = "backward_hgt_full_graph_message_mean_aggregation_csr";
+  (void)outcsr_row_ptrs; (void)outcsr_reltypes; (void)edgesoftmax_sum_per_node;
+  const int H = (int)xlen(normalized_attn_score);
+  const int F = (int)(xlen(grad_message) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_aggregate_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"),
+               i64(outcsr_eids, op, "outcsr_eids"), outcsr_eids.numel(),
+               f32(normalized_attn_score, op, "normalized_attn_score"),
+               f32(gradout, op, "gradout"), f32w(grad_message, op, "grad_message"),
+               H, F, stream_of(gradout)),
+           op);
+}
+
+// OpExport/HGTOps.inc.h:553-566
+void backward_hgt_full_graph_edge_softmax_ops_csr(
+    Tensor &outcsr_row_ptr, Tensor &outcsr_col_indices, Tensor &outcsr_eids,
+    Tensor &outcsr_reltypes, Tensor &message, Tensor &unnormalized_attn_score,
+    Tensor &normalized_attn_score, Tensor &out, Tensor &gradout, Tensor &mu,
+    Tensor &grad_attn_score, Tensor &grad_mu) {
+  const char *op = "backward_hgt_full_graph_edge_softmax_ops_csr";
+  (void)outcsr_row_ptr;
+  const int H = (int)xlen(unnormalized_attn_score);
+  const int F = (int)(xlen(message) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_edge_softmax_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"),
+               i64(outcsr_eids, op, "outcsr_eids"),
+               i64(outcsr_reltypes, op, "outcsr_reltypes"), outcsr_eids.numel(),
+               mu.size(0), f32(message, op, "message"),
+               f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
+               f32(normalized_attn_score, op, "normalized_attn_score"),
+               f32(out, op, "out"), f32(gradout, op, "gradout"),
+               f32(mu, op, "mu"), f32w(grad_attn_score, op, "grad_attn_score"),
+               f32w(grad_mu, op, "grad_mu"), H, F, stream_of(gradout)),
+           op);
+}
+
+// ---------------------------------------------------------- converters ---
+// The reference requires CPU tensors (DataConverters.inc.h asserts
+// device().is_cpu()); here CPU inputs are staged to the current CUDA device,
+// converted there, and returned on the input's device.
+struct Staged {
+  std::vector<Tensor> dev;
+  at::Device home;
+};
+Staged stage(std::initializer_list<Tensor> ts, const char *op) {
+  Staged s{{}, ts.begin()->device()};
+  for (const Tensor &t : ts) {
+    TORCH_CHECK(t.scalar_type() == at::kLong, "torch_hrt::", op,
+                ": index tensors must be int64");
+    TORCH_CHECK(t.device() == s.home, "torch_hrt::", op,
+                ": all index tensors must be on one device");
+    s.dev.push_back(t.is_cuda() ? t.contiguous() : t.contiguous().cuda());
+  }
+  return s;
+}
+std::vector<Tensor> unstage(const Staged &s, std::vector<Tensor> out) {
+  if (!s.home.is_cuda())
+    for (auto &t : out) t = t.to(s.home);
+  return out;
+}
+
+// out[j] = in[j] permuted by a stable sort on key; returns ptrs as out.back()
+std::vector<Tensor> sort_by_key(const Tensor &key, int64_t num_keys,
+                                const std::vector<Tensor> &payload,
+                                const char *op) {
+  const int64_t E = key.numel();
+  c10::cuda::CUDAGuard guard(key.device());
+  auto opts = key.options();
+  std::vector<Tensor> out;
+  const int64_t *in_ptrs[4] = {nullptr, nullptr, nullptr, nullptr};
+  int64_t *out_ptrs[4] = {nullptr, nullptr, nullptr, nullptr};
+  TORCH_CHECK(payload.size() <= 4, op, ": too many payload arrays");
+  for (size_t j = 0; j < payload.size(); ++j) {
+    out.push_back(at::empty({E}, opts));
+    in_ptrs[j] = payload[j].data_ptr<int64_t>();
+    out_ptrs[j] = out.back().data_ptr<int64_t>();
+  }
+  Tensor ptrs = at::empty({num_keys + 1}, opts);
+  const int64_t bytes = hetb_sort_scratch_bytes(E, num_keys);
+  Tensor scratch = at::empty({bytes}, opts.dtype(at::kByte));
+  check_rc(hetb_stable_sort_by_key(key.data_ptr<int64_t>(), E, num_keys,
+                                   (int)payload.size(), in_ptrs, out_ptrs,
+                                   ptrs.data_ptr<int64_t>(), scratch.data_ptr(),
+                                   bytes, stream_of(key)),
+           op);
+  out.push_back(ptrs);
+  return out;
+}
+
+Tensor expand_rows(const Tensor &row_ptrs, int64_t E, const char *op) {
+  c10::cuda::CUDAGuard guard(row_ptrs.device());
+  Tensor rows = at::empty({E}, row_ptrs.options());
+  check_rc(hetb_expand_row_ptr(row_ptrs.data_ptr<int64_t>(),
+                               row_ptrs.numel() - 1, E,
+                               rows.data_ptr<int64_t>(), stream_of(row_ptrs)),
+           op);
+  return rows;
+}
+
+// DataConverters.inc.h:283-344 → MyHyb.h:31-75 (stable by original position)
+std::vector<Tensor> transpose_csr(Tensor &csr_row_ptrs, Tensor &csr_col_indices,
+                                  Tensor &csr_reltypes, Tensor &csr_eids) {
+  const char *op = "transpose_csr";
+  Staged s = stage({csr_row_ptrs, csr_col_indices, csr_reltypes, csr_eids}, op);
+  const int64_t E = s.dev[1].numel();
+  const int64_t num_rows = s.dev[0].numel() - 1;
+  Tensor rows = expand_rows(s.dev[0], E, op);
+  auto r = sort_by_key(s.dev[1], num_rows, {rows, s.dev[2], s.dev[3]}, op);
+  return unstage(s, {r[3], r[0], r[1], r[2]});
+}
+
+// DataConverters.inc.h:10-77 → MyHyb.h:1047-1097: order (rel, row, original).
+std::vector<Tensor> convert_integrated_coo_to_separate_coo(
+    Tensor &row_indices, Tensor &col_indices, Tensor &reltypes, Tensor &eids,
+    int64_t num_rows, int64_t num_rels) {
+  const char *op = "convert_integrated_coo_to_separate_coo";
+  Staged s = stage({row_indices, col_indices, reltypes, eids}, op);
+  auto a = sort_by_key(s.dev[0], num_rows,
+                       {s.dev[0], s.dev[1], s.dev[2], s.dev[3]}, op);
+  auto b = sort_by_key(a[2], num_rels, {a[0], a[1], a[3]}, op);
+  return unstage(s, {b[3], b[0], b[1], b[2]});
+}
+
+// DataConverters.inc.h:216-281 → MyHyb.h:1099-1150
+std::vector<Tensor> convert_integrated_csr_to_separate_coo(
+    Tensor &row_ptrs, Tensor &col_indices, Tensor &reltypes, Tensor &eids) {
+  const char *op = "convert_integrated_csr_to_separate_coo";
+  Staged s = stage({row_ptrs, col_indices, reltypes, eids}, op);
+  const int64_t E = s.dev[1].numel();
+  // num_rels = max(rel)+1, as the reference infers it (MyHyb.h:347)
+  const int64_t num_rels = E ? s.dev[2].max().item<int64_t>() + 1 : 0;
+  Tensor rows = expand_rows(s.dev[0], E, op);
+  auto b = sort_by_key(s.dev[2], num_rels, {rows, s.dev[1], s.dev[3]}, op);
+  return unstage(s, {b[3], b[0], b[1], b[2]});
+}
+
+std::vector<Tensor> separate_csr_from_coo(const Staged &s, const Tensor &rows,
+                                          const Tensor &cols, const Tensor &rels,
+                                          const Tensor &eids, int64_t num_rows,
+                                          int64_t num_rels, const char *op) {
+  Tensor key = rels * num_rows + rows;
+  auto b = sort_by_key(key, num_rows * num_rels, {cols, eids}, op);
+  Tensor row_ptrs = b[2];
+  Tensor rel_ptrs =
+      row_ptrs.index({at::indexing::Slice(0, at::indexing::None, num_rows)})
+          .contiguous();
+  return unstage(s, {rel_ptrs, row_ptrs, b[0], b[1]});
+}
+
+// DataConverters.inc.h:79-146 → MyHyb.h:996-1045
+std::vector<Tensor> convert_integrated_coo_to_separate_csr(
+    Tensor &row_indices, Tensor &col_indices, Tensor &reltypes, Tensor &eids,
+    int64_t num_rows, int64_t num_rels) {
+  const char *op = "convert_integrated_coo_to_separate_csr";
+  Staged s = stage({row_indices, col_indices, reltypes, eids}, op);
+  return separate_csr_from_coo(s, s.dev[0], s.dev[1], s.dev[2], s.dev[3],
+                               num_rows, num_rels, op);
+}
+
+// DataConverters.inc.h:148-214
+std::vector<Tensor> convert_integrated_csr_to_separate_csr(
+    Tensor &row_ptrs, Tensor &col_indices, Tensor &reltypes, Tensor &eids) {
+  const char *op = "convert_integrated_csr_to_separate_csr";
+  Staged s = stage({row_ptrs, col_indices, reltypes, eids}, op);
+  const int64_t E = s.dev[1].numel();
+  const int64_t num_rows = s.dev[0].numel() - 1;
+  const int64_t num_rels = E ? s.dev[2].max().item<int64_t>() + 1 : 0;
+  Tensor rows = expand_rows(s.dev[0], E, op);
+  return separate_csr_from_coo(s, rows, s.dev[1], s.dev[2], s.dev[3], num_rows,
+                               num_rels, op);
+}
+
+}  // namespace
+
+TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
+  m.def("build_debug_info", build_debug_info);
+  m.def("hetb200_launch_count", hetb200_launch_count);
+  // RGNN (OpExport/RGNNOps.inc.h:1189-1206)
+  m.def("rgnn_relational_matmul", rgnn_relational_matmul);
+  m.def("backward_rgnn_relational_matmul", backward_rgnn_relational_matmul);
+  m.def("rgnn_relational_matmul_no_scatter_gather_list",
+        rgnn_relational_matmul_no_scatter_gather_list);
+  m.def("backward_rgnn_relational_matmul_no_scatter_gather_list",
+        backward_rgnn_relational_matmul_no_scatter_gather_list);
+  m.def("rgnn_inner_product_right_node_separatecoo",
+        rgnn_inner_product_right_node_separatecoo);
+  m.def("backward_inner_product_right_node_separatecoo",
+        backward_inner_product_right_node_separatecoo);
+  // RGAT (OpExport/RGATOps.inc.h:560-571). The reference's Python calls the
+  // CSR ops without the trailing bool (backend/rgat_layers_and_funcs.py:49-63),
+  // so it is given a default here.
+  m.def(
+      "relational_fused_gat_csr(Tensor(a!) incsr_row_ptr, Tensor(b!) "
+      "incsr_col_indices, Tensor(c!) incsr_eids, Tensor(d!) incsr_reltypes, "
+      "Tensor(e!) unique_srcs_and_dests_rel_ptrs, Tensor(f!) "
+      "unique_srcs_and_dests_node_indices, Tensor(g!) feat_src, Tensor(h!) el, "
+      "Tensor(i!) er, Tensor(j!) sum, Tensor(k!) exp, Tensor(l!) ret, float "
+      "slope, bool CompactAsOfNodeFlag=False) -> ()",
+      relational_fused_gat_csr);
+  m.def(
+      "backward_relational_fused_gat_csr(Tensor(a!) outcsr_row_ptr, Tensor(b!) "
+      "outcsr_col_indices, Tensor(c!) outcsr_eids, Tensor(d!) outcsr_reltypes, "
+      "Tensor(e!) unique_srcs_and_dests_rel_ptrs, Tensor(f!) "
+      "unique_srcs_and_dests_node_indices, Tensor(g!) feat_src, Tensor(h!) el, "
+      "Tensor(i!) er, Tensor(j!) sum, Tensor(k!) exp, Tensor(l!) ret, "
+      "Tensor(m!) gradout, Tensor(n!) grad_feat_src, Tensor(o!) grad_el, "
+      "Tensor(p!) grad_er, float slope, bool CompactAsOfNodeFlag=False) -> ()",
+      backward_relational_fused_gat_csr);
+  m.def("relational_fused_gat_separate_coo", relational_fused_gat_separate_coo);
+  m.def("backward_relational_fused_gat_separate_coo",
+        backward_relational_fused_gat_separate_coo);
+  // HGT (OpExport/HGTOps.inc.h:656-674)
+  m.def("hgt_full_graph_edge_softmax_ops_csr",
+        hgt_full_graph_edge_softmax_ops_csr);
+  m.def("hgt_full_graph_message_mean_aggregation_csr",
+        hgt_full_graph_message_mean_aggregation_csr);
+  m.def("backward_hgt_full_graph_message_mean_aggregation_csr",
+        backward_hgt_full_graph_message_mean_aggregation_csr);
+  m.def("backward_hgt_full_graph_edge_softmax_ops_csr",
+        backward_hgt_full_graph_edge_softmax_ops_csr);
+  // Data converters (OpExport/DataConverters.inc.h:346-357)
+  m.def("transpose_csr", transpose_csr);
+  m.def("convert_integrated_csr_to_separate_csr",
+        convert_integrated_csr_to_separate_csr);
+  m.def("convert_integrated_csr_to_separate_coo",
+        convert_integrated_csr_to_separate_coo);
+  m.def("convert_integrated_coo_to_separate_csr",
+        convert_integrated_coo_to_separate_csr);
+  m.def("convert_integrated_coo_to_separate_coo",
+        convert_integrated_coo_to_separate_coo);
+}
