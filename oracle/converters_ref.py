@@ -1,0 +1,81 @@
+"""CPU oracle for relation sort / CSR construction — TEST INFRASTRUCTURE ONLY.
+
+numpy restatement (int64, bit-exact) of the reference's converters. Every
+ordering is defined with *stable* sorts so the result is unique:
+
+* ``coo2csr``            python/utils_lite/sparse_matrix_converters.py:7-39
+                         (the reference's argsort is unstable, so its in-row
+                         order is unspecified; we define it as stable)
+* ``transpose_csr``      MyHyb/MyHyb.h:31-75 (new row = old col; inside a row:
+                         ascending old row, then original position)
+* ``to_separate_coo``    MyHyb/MyHyb.h:1047-1150 (order rel, row, original)
+* ``sort_by_etype_eids`` python/utils/coo_sorters.py:156-170 (per relation by eid)
+* ``to_separate_csr``    MyHyb/MyHyb.h:996-1045
+* ``canonicalize_eids``  python/utils/mydgl_graph.py:736-824
+
+Pinned against the reference's own C++ (MyHyb.h compiled into oracle/_ref by
+oracle/build_ref.py) in tests/test_oracle_converters.py, and against the one
+property the reference's test asserts (transpose twice preserves row_ptrs,
+python/test/test_kernel_correctness.py:44).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+I64 = np.int64
+
+
+def _ptrs(keys: np.ndarray, n: int) -> np.ndarray:
+    p = np.zeros(n + 1, dtype=I64)
+    np.cumsum(np.bincount(keys, minlength=n), out=p[1:])
+    return p
+
+
+def expand_rows(row_ptrs: np.ndarray) -> np.ndarray:
+    return np.repeat(np.arange(row_ptrs.size - 1, dtype=I64), np.diff(row_ptrs))
+
+
+def coo2csr(src, dst, rel, eid, num_rows):
+    o = np.argsort(src, kind="stable")
+    return _ptrs(src, num_rows), dst[o].astype(I64), rel[o].astype(I64), eid[o].astype(I64)
+
+
+def transpose_csr(row_ptrs, col, rel, eid):
+    n = row_ptrs.size - 1
+    rows = expand_rows(row_ptrs)
+    o = np.argsort(col, kind="stable")
+    return _ptrs(col, n), rows[o], rel[o].astype(I64), eid[o].astype(I64)
+
+
+def to_separate_coo(row, col, rel, eid, num_rows, num_rels):
+    """order (rel, row, original position) -> rel_ptrs, row, col, eid"""
+    o = np.argsort(rel * I64(num_rows) + row, kind="stable")
+    return _ptrs(rel, num_rels), row[o].astype(I64), col[o].astype(I64), eid[o].astype(I64)
+
+
+def csr_to_separate_coo(row_ptrs, col, rel, eid):
+    num_rels = int(rel.max()) + 1 if rel.size else 0
+    return to_separate_coo(expand_rows(row_ptrs), col, rel, eid, row_ptrs.size - 1, num_rels)
+
+
+def to_separate_csr(row, col, rel, eid, num_rows, num_rels):
+    key = rel * I64(num_rows) + row
+    o = np.argsort(key, kind="stable")
+    row_ptrs = _ptrs(key, num_rows * num_rels)
+    return row_ptrs[::num_rows].copy(), row_ptrs, col[o].astype(I64), eid[o].astype(I64)
+
+
+def sort_by_etype_eids(rel_ptrs, row, col, eid):
+    row, col, eid = row.copy(), col.copy(), eid.copy()
+    for r in range(rel_ptrs.size - 1):
+        a, b = int(rel_ptrs[r]), int(rel_ptrs[r + 1])
+        o = np.argsort(eid[a:b], kind="stable")
+        row[a:b], col[a:b], eid[a:b] = row[a:b][o], col[a:b][o], eid[a:b][o]
+    return row, col, eid
+
+
+def canonicalize_eids(separate_coo_eids, *other_eid_arrays):
+    """remap so the separate-COO eids become 0..E-1 in order."""
+    remap = np.empty(separate_coo_eids.size, dtype=I64)
+    remap[separate_coo_eids] = np.arange(separate_coo_eids.size, dtype=I64)
+    return (np.arange(separate_coo_eids.size, dtype=I64),) + tuple(remap[a] for a in other_eid_arrays)
