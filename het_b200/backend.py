@@ -1,0 +1,250 @@
+"""autograd wrappers around ``torch.ops.torch_hrt`` with the reference's names.
+
+Host-side mirror of hrt/python/backend/{rgnn,rgat,hgt}_layers_and_funcs.py: each
+function allocates the outputs/intermediates the op contract expects, calls one
+or two ``K.<op>`` in forward and the matching ``K.backward_<op>`` in backward.
+Same function names, argument meaning and op call order as the reference, so the
+models in ``het_b200.models`` read like the reference's.
+"""
+from __future__ import annotations
+
+import torch as th
+
+from .kernels import K
+
+
+# ----- rgnn_layers_and_funcs.py:8-73 -------------------------------------
+class RgnnRelationalMatmul(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, relptrs, node_indices, eids, weights, inputs, ret, input_num_head_one_flag):
+        ctx.save_for_backward(relptrs, node_indices, eids, weights, inputs)
+        ctx.input_num_head_one_flag = input_num_head_one_flag
+        ctx.mark_dirty(ret)
+        K.rgnn_relational_matmul(
+            {"separate_coo_rel_ptrs": relptrs, "separate_coo_node_indices": node_indices,
+             "separate_coo_eids": eids},
+            0, weights, inputs, ret, input_num_head_one_flag)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        relptrs, node_indices, eids, weights, inputs = ctx.saved_tensors
+        grad_weight = th.zeros_like(weights, memory_format=th.contiguous_format)
+        grad_input = th.zeros_like(inputs, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"separate_coo_rel_ptrs": relptrs, "separate_coo_node_indices": node_indices,
+             "separate_coo_eids": eids},
+            0, th.transpose(weights, 2, 3).contiguous(), inputs, gradout.contiguous(),
+            grad_input, grad_weight, ctx.input_num_head_one_flag)
+        return None, None, None, grad_weight, grad_input, None, None
+
+
+# ----- rgnn_layers_and_funcs.py:76-120 -----------------------------------
+class RgnnRelationalMatmulNoScatterGatherList(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, ntype_offset_ptrs, weights, inputs, ret):
+        ctx.mark_dirty(ret)
+        K.rgnn_relational_matmul_no_scatter_gather_list(ntype_offset_ptrs, weights, inputs, ret)
+        ctx.save_for_backward(ntype_offset_ptrs, weights, inputs)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        ntype_offset_ptrs, weights, inputs = ctx.saved_tensors
+        grad_weight = th.zeros_like(weights, memory_format=th.contiguous_format)
+        grad_input = th.zeros_like(inputs, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(
+            ntype_offset_ptrs, th.transpose(weights, 2, 3).contiguous(), inputs,
+            gradout.contiguous(), grad_input, grad_weight)
+        return None, grad_weight, grad_input, None
+
+
+# ----- rgnn_layers_and_funcs.py:350-416 ----------------------------------
+class RgnnInnerProductEdgeAndNode(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, rel_ptrs, eids, row_indices, col_indices, left_edge_data, right_node_vectors, ret):
+        ctx.save_for_backward(rel_ptrs, eids, row_indices, col_indices, left_edge_data, right_node_vectors)
+        ctx.mark_dirty(ret)
+        K.rgnn_inner_product_right_node_separatecoo(
+            dict(), 0, rel_ptrs, eids, row_indices, col_indices, left_edge_data,
+            right_node_vectors, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        rel_ptrs, eids, row_indices, col_indices, left, right = ctx.saved_tensors
+        grad_left = th.zeros_like(left, memory_format=th.contiguous_format)
+        grad_right = th.zeros_like(right, memory_format=th.contiguous_format)
+        K.backward_inner_product_right_node_separatecoo(
+            dict(), 0, rel_ptrs, eids, row_indices, col_indices, left, right,
+            gradout.contiguous(), grad_left, grad_right)
+        return None, None, None, None, grad_left, grad_right, None
+
+
+def rgnn_relational_matmul(arg_tensor_dict, weights, inputs, input_num_head_one_flag, compact_as_of_node_kind):
+    """rgnn_layers_and_funcs.py:420-470 (kind 0; compact kinds are a later row)."""
+    if compact_as_of_node_kind != 0:
+        raise NotImplementedError("CompactAsOfNodeKind != Disabled")
+    ret = th.empty(
+        (arg_tensor_dict["separate_coo_node_indices"].numel(), weights.size(1), weights.size(3)),
+        dtype=weights.dtype, device=weights.device)
+    return RgnnRelationalMatmul.apply(
+        arg_tensor_dict["separate_coo_rel_ptrs"], arg_tensor_dict["separate_coo_node_indices"],
+        arg_tensor_dict["separate_coo_eids"], weights.contiguous(), inputs.contiguous(), ret,
+        input_num_head_one_flag)
+
+
+def rgnn_relational_matmul_no_scatter_gather_list(ntype_offset_ptrs, weights, inputs):
+    """rgnn_layers_and_funcs.py:473-492"""
+    ret = th.empty((inputs.size(0), weights.size(1) * weights.size(3)), dtype=weights.dtype,
+                   device=weights.device)
+    return RgnnRelationalMatmulNoScatterGatherList.apply(
+        ntype_offset_ptrs, weights.contiguous(), inputs.contiguous(), ret)
+
+
+def rgnn_inner_product_right_node(graph, left_side_data, right_node_vectors, compact_as_of_node_kind,
+                                  left_mapper_suffix=None):
+    """rgnn_layers_and_funcs.py:498-530 (kind 0)."""
+    if compact_as_of_node_kind != 0:
+        raise NotImplementedError("CompactAsOfNodeKind != Disabled")
+    coo = graph.get_separate_coo_original()
+    ret = th.empty([coo["eids"].numel(), right_node_vectors.size(1)], dtype=right_node_vectors.dtype,
+                   device=right_node_vectors.device)
+    return RgnnInnerProductEdgeAndNode.apply(
+        coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"],
+        left_side_data.contiguous(), right_node_vectors.contiguous(), ret)
+
+
+# ----- rgat_layers_and_funcs.py:8-117, 651-684 ---------------------------
+class RelationalFusedGatCSR(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, incsr_row_ptr, incsr_col_indices, incsr_eids, incsr_reltypes,
+                outcsr_row_ptr, outcsr_col_indices, outcsr_eids, outcsr_reltypes,
+                unique_rel_ptr, unique_node_indices, feat_src, el, er, s, exp, ret, slope):
+        ctx.mark_dirty(ret)
+        K.relational_fused_gat_csr(
+            incsr_row_ptr, incsr_col_indices, incsr_eids, incsr_reltypes, unique_rel_ptr,
+            unique_node_indices, feat_src, el, er, s, exp, ret, slope)
+        ctx.save_for_backward(outcsr_row_ptr, outcsr_col_indices, outcsr_eids, outcsr_reltypes,
+                              unique_rel_ptr, unique_node_indices, feat_src, el, er, s, exp, ret)
+        ctx.slope = slope
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        (outcsr_row_ptr, outcsr_col_indices, outcsr_eids, outcsr_reltypes, unique_rel_ptr,
+         unique_node_indices, feat_src, el, er, s, exp, ret) = ctx.saved_tensors
+        grad_el = th.empty_like(el, memory_format=th.contiguous_format)
+        grad_er = th.empty_like(er, memory_format=th.contiguous_format)
+        grad_feat_src = th.empty_like(feat_src, memory_format=th.contiguous_format)
+        K.backward_relational_fused_gat_csr(
+            outcsr_row_ptr, outcsr_col_indices, outcsr_eids, outcsr_reltypes, unique_rel_ptr,
+            unique_node_indices, feat_src, el, er, s, exp, ret, gradout.contiguous(),
+            grad_feat_src, grad_el, grad_er, ctx.slope)
+        return (None,) * 10 + (grad_feat_src, grad_el, grad_er, None, None, None, None)
+
+
+def relational_fused_gat_csr(graph, feat_src, el, er, slope):
+    incsr, outcsr = graph.get_in_csr(), graph.get_out_csr()
+    uniq = graph.get_separate_unique_node_indices()
+    exp = el.new_empty([graph.get_num_edges()] + list(el.size()[1:]))
+    s = el.new_empty([graph.get_num_nodes(), el.size(1)])
+    ret = el.new_empty([graph.get_num_nodes()] + list(feat_src.size()[1:]))
+    return RelationalFusedGatCSR.apply(
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"],
+        outcsr["row_ptrs"], outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"],
+        uniq["rel_ptrs"], uniq["node_indices"], feat_src.contiguous(), el.contiguous(),
+        er.contiguous(), s, exp, ret, slope)
+
+
+# ----- rgat_layers_and_funcs.py:233-322, 725-750 -------------------------
+class RelationalFusedGatSeparateCOO(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, eids, rel_ptrs, row_indices, col_indices, feat_src, el, er, s, exp, ret, slope):
+        ctx.mark_dirty(ret)
+        K.relational_fused_gat_separate_coo(
+            eids, rel_ptrs, row_indices, col_indices, 0, dict(), feat_src, el, er, s, exp, ret, slope)
+        ctx.save_for_backward(eids, rel_ptrs, row_indices, col_indices, feat_src, el, er, s, exp, ret)
+        ctx.slope = slope
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        eids, rel_ptrs, row_indices, col_indices, feat_src, el, er, s, exp, ret = ctx.saved_tensors
+        grad_el = th.empty_like(el, memory_format=th.contiguous_format)
+        grad_er = th.empty_like(er, memory_format=th.contiguous_format)
+        grad_feat_src = th.empty_like(feat_src, memory_format=th.contiguous_format)
+        K.backward_relational_fused_gat_separate_coo(
+            eids, rel_ptrs, row_indices, col_indices, 0, dict(), feat_src, el, er, s, exp, ret,
+            gradout.contiguous(), grad_feat_src, grad_el, grad_er, ctx.slope)
+        return None, None, None, None, grad_feat_src, grad_el, grad_er, None, None, None, None
+
+
+def relational_fused_gat_separate_coo(g, feat, el, er, negative_slope):
+    coo = g.get_separate_coo_original()
+    exp = el.new_empty([g.get_num_edges()] + list(el.size()[1:]))
+    s = el.new_empty([g.get_num_nodes(), el.size(1)])
+    ret = el.new_empty([g.get_num_nodes()] + list(feat.size()[1:]))
+    return RelationalFusedGatSeparateCOO.apply(
+        coo["eids"], coo["rel_ptrs"], coo["row_indices"], coo["col_indices"], feat.contiguous(),
+        el.contiguous(), er.contiguous(), s, exp, ret, negative_slope)
+
+
+# ----- hgt_layers_and_funcs.py:296-415 -----------------------------------
+class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSR(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes,
+                outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes,
+                unnormalized_attn_score, mu, edgesoftmax_sum_per_node,
+                mu_softmax_applied_unnormalized_attn_score, normalized_attn_score,
+                message_per_edge, new_h):
+        ctx.mark_dirty(new_h)
+        K.hgt_full_graph_edge_softmax_ops_csr(
+            incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, unnormalized_attn_score,
+            mu, edgesoftmax_sum_per_node, mu_softmax_applied_unnormalized_attn_score,
+            normalized_attn_score)
+        # The aggregation op divides its score argument by the per-node sum
+        # (as the reference kernel does), so it is given exp(mu*score), not the
+        # already-normalised score the reference's Python passes
+        # (hgt_layers_and_funcs.py:332-342, which double-normalises).
+        K.hgt_full_graph_message_mean_aggregation_csr(
+            incsr_row_ptrs, incsr_col_indices, incsr_reltypes, incsr_eids, message_per_edge,
+            mu_softmax_applied_unnormalized_attn_score, edgesoftmax_sum_per_node, mu, new_h)
+        ctx.save_for_backward(outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes,
+                              unnormalized_attn_score, mu, edgesoftmax_sum_per_node,
+                              normalized_attn_score, message_per_edge, new_h)
+        return new_h
+
+    @staticmethod
+    def backward(ctx, gradout):
+        (outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, unnormalized_attn_score,
+         mu, edgesoftmax_sum_per_node, normalized_attn_score, message_per_edge,
+         new_h) = ctx.saved_tensors
+        gradout = gradout.contiguous()
+        grad_message = th.empty_like(message_per_edge, memory_format=th.contiguous_format)
+        K.backward_hgt_full_graph_message_mean_aggregation_csr(
+            outcsr_row_ptrs, outcsr_col_indices, outcsr_reltypes, outcsr_eids,
+            edgesoftmax_sum_per_node, normalized_attn_score, gradout, grad_message)
+        grad_attn_score = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+        grad_mu = th.zeros_like(mu, memory_format=th.contiguous_format)
+        K.backward_hgt_full_graph_edge_softmax_ops_csr(
+            outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, message_per_edge,
+            unnormalized_attn_score, normalized_attn_score, new_h, gradout, mu, grad_attn_score,
+            grad_mu)
+        return (None,) * 8 + (grad_attn_score, grad_mu, None, None, None, grad_message, None)
+
+
+def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(graph, message_per_edge,
+                                                                 unnormalized_attn_score, mu):
+    """hgt_layers_and_funcs.py:520-560"""
+    incsr, outcsr = graph.get_in_csr(), graph.get_out_csr()
+    n, h = graph.get_num_nodes(), mu.size(1)
+    new_h = message_per_edge.new_empty(n, h, message_per_edge.size(2))
+    ssum = message_per_edge.new_empty(n, h)
+    t = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    norm = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    return HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSR.apply(
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"],
+        outcsr["row_ptrs"], outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"],
+        unnormalized_attn_score.contiguous(), mu.contiguous(), ssum, t, norm,
+        message_per_edge.contiguous(), new_h)

@@ -593,11 +593,31 @@ std::vector<Tensor> convert_integrated_csr_to_separate_csr(
                                num_rels, op);
 }
 
+// hetb200 extension (not in the reference): stable sort of up to four int64
+// payload arrays by an int64 key in [0, num_keys); returns the permuted
+// payloads followed by the segment offsets ptrs[num_keys+1]. COO->CSR is
+// sort_by_key(src, N, [dst, rel, eid]); relation sort is sort_by_key(rel, R, ...).
+std::vector<Tensor> hetb200_stable_sort_by_key(Tensor key, int64_t num_keys,
+                                               std::vector<Tensor> payload) {
+  const char *op = "hetb200_stable_sort_by_key";
+  std::vector<Tensor> all = {key};
+  for (auto &t : payload) all.push_back(t);
+  Staged s{{}, key.device()};
+  for (const Tensor &t : all) {
+    TORCH_CHECK(t.scalar_type() == at::kLong, op, ": tensors must be int64");
+    TORCH_CHECK(t.numel() == key.numel(), op, ": payload length mismatch");
+    s.dev.push_back(t.is_cuda() ? t.contiguous() : t.contiguous().cuda());
+  }
+  std::vector<Tensor> pl(s.dev.begin() + 1, s.dev.end());
+  return unstage(s, sort_by_key(s.dev[0], num_keys, pl, op));
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("build_debug_info", build_debug_info);
   m.def("hetb200_launch_count", hetb200_launch_count);
+  m.def("hetb200_stable_sort_by_key", hetb200_stable_sort_by_key);
   // RGNN (OpExport/RGNNOps.inc.h:1189-1206)
   m.def("rgnn_relational_matmul", rgnn_relational_matmul);
   m.def("backward_rgnn_relational_matmul", backward_rgnn_relational_matmul);

@@ -1,0 +1,91 @@
+"""Device-resident heterograph container with the reference's accessor names.
+
+Host-side mirror of ``MyDGLGraph`` (hrt/python/utils/mydgl_graph.py:293-420): the
+models and backend functions ask it for dicts of int64 index tensors
+(``get_separate_coo_original``, ``get_in_csr``, ``get_out_csr``,
+``get_original_node_type_offsets`` ...). Unlike the reference, every format is
+built ON THE GPU by the hand-written stable radix sort behind
+``K.hetb200_stable_sort_by_key`` (csrc/convert.cu) instead of CPU
+vector-of-vector bucketing (MyHyb/MyHyb.h:1099-1150) and Python dict remaps
+(mydgl_graph.py:765-824).
+
+Orderings (all bit-exact against oracle/converters_ref.py):
+  separate COO : edges sorted by (relation, referential eid)        [a16]
+  out-CSR      : stable by source;  in-CSR : stable by destination  [a17]
+  eids         : canonicalised so separate-COO eids are 0..E-1      [a18]
+"""
+from __future__ import annotations
+
+import torch
+
+from .graphs import HeteroCOO
+from .kernels import K
+
+
+class HetGraph:
+    def __init__(self, coo: HeteroCOO, device="cuda"):
+        dev = torch.device(device)
+        self.name = coo.name
+        self.num_nodes = coo.num_nodes
+        self.num_rels = coo.num_rels
+        self.num_edges = coo.num_edges
+        src = torch.from_numpy(coo.src).to(dev)
+        dst = torch.from_numpy(coo.dst).to(dev)
+        rel = torch.from_numpy(coo.etype).to(dev)
+        eid = torch.arange(self.num_edges, dtype=torch.int64, device=dev)
+        self.node_type_offsets = torch.from_numpy(coo.node_type_offsets).to(dev)
+        self.rel_src_type = torch.from_numpy(coo.rel_src_type).to(dev)
+        self.rel_dst_type = torch.from_numpy(coo.rel_dst_type).to(dev)
+
+        # relation sort: input is in eid order, so a stable sort by relation
+        # yields (relation, eid) order — the net effect of ToSeparateCOO +
+        # sort_coo_by_etype_eids (python/utils/coo_sorters.py:156-170).
+        row, col, old_eid, rel_ptrs = K.hetb200_stable_sort_by_key(rel, self.num_rels, [src, dst, eid])
+        # canonicalize_eids("separate_coo"): separate-COO position becomes the edge id
+        remap = torch.empty_like(old_eid)
+        remap[old_eid] = eid
+        self.separate_coo = {
+            "rel_ptrs": rel_ptrs, "row_indices": row, "col_indices": col, "eids": eid,
+        }
+        new_eid = remap  # edge id of original edge i
+        o_col, o_rel, o_eid, o_ptr = K.hetb200_stable_sort_by_key(src, self.num_nodes, [dst, rel, new_eid])
+        self.out_csr = {"row_ptrs": o_ptr, "col_indices": o_col, "rel_types": o_rel, "eids": o_eid}
+        i_col, i_rel, i_eid, i_ptr = K.hetb200_stable_sort_by_key(dst, self.num_nodes, [src, rel, new_eid])
+        self.in_csr = {"row_ptrs": i_ptr, "col_indices": i_col, "rel_types": i_rel, "eids": i_eid}
+        self._empty = torch.empty(0, dtype=torch.int64, device=dev)
+
+    # ---- accessor names of the reference's MyDGLGraph -------------------
+    def get_separate_coo_original(self):
+        return self.separate_coo
+
+    def get_in_csr(self):
+        return self.in_csr
+
+    def get_out_csr(self):
+        return self.out_csr
+
+    def get_original_node_type_offsets(self):
+        return self.node_type_offsets
+
+    def get_separate_unique_node_indices(self):
+        # compact-as-of-node lists (kinds 1-4) are a later §8(f) row; the
+        # non-compact ops ignore these tensors.
+        return {"rel_ptrs": self._empty, "node_indices": self._empty}
+
+    def get_num_nodes(self):
+        return self.num_nodes
+
+    def get_num_edges(self):
+        return self.num_edges
+
+    def get_num_rels(self):
+        return self.num_rels
+
+    def get_num_ntypes(self):
+        return int(self.node_type_offsets.numel() - 1)
+
+    def index_bytes(self) -> int:
+        tot = 0
+        for d in (self.separate_coo, self.in_csr, self.out_csr):
+            tot += sum(t.numel() * 8 for t in d.values())
+        return tot

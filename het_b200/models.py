@@ -1,0 +1,164 @@
+"""RGAT / HGT layers with the reference's op sequence (default, non-compact flags).
+
+Host-side mirror of hrt/python/RGAT/models.py:16-385 (``HET_RGATLayer``) and
+hrt/python/HGT/models.py:15-286 (``HET_HGTLayerHetero``): same parameters, same
+shapes, same ``B.*`` call order, so the parity tests can
+compare layer outputs and every parameter gradient with the oracle's restatement.
+"""
+from __future__ import annotations
+
+import math
+
+import torch as th
+import torch.nn as nn
+
+from . import backend as B
+
+
+class HET_RelGraphEmbed(nn.Module):
+    """Learnable [N, D] node features (hrt/python/RGNNUtils/RGNNUtils.py:78-121)."""
+
+    def __init__(self, num_nodes, embed_size):
+        super().__init__()
+        self.embeds = nn.Parameter(th.empty(num_nodes, embed_size))
+        nn.init.uniform_(self.embeds, -1.0, 1.0)
+
+    def forward(self, _=None):
+        return self.embeds
+
+
+class HET_RGATLayer(nn.Module):
+    def __init__(self, in_feat, out_feat, num_rels, num_heads, *, bias=True, activation=None,
+                 self_loop=False, gat_edge_parallel_flag=False, dropout=0.0, leaky_relu_slope=0.2):
+        super().__init__()
+        assert out_feat % num_heads == 0, "out_feat must be a multiple of num_heads"
+        self.in_feat, self.out_feat = in_feat, out_feat
+        self.num_rels, self.num_heads = num_rels, num_heads
+        self.bias, self.activation, self.self_loop = bias, activation, self_loop
+        self.gat_edge_parallel_flag = gat_edge_parallel_flag
+        self.leaky_relu_slope = leaky_relu_slope
+        self.conv_weights = nn.Parameter(th.empty(num_rels, num_heads, in_feat, out_feat // num_heads))
+        self.attn_l = nn.Parameter(th.empty(num_rels, num_heads, out_feat // num_heads))
+        self.attn_r = nn.Parameter(th.empty(num_rels, num_heads, out_feat // num_heads))
+        if bias:
+            self.h_bias = nn.Parameter(th.empty(out_feat))
+        if self_loop:
+            self.loop_weight = nn.Parameter(th.empty(in_feat, out_feat))
+        self.dropout = nn.Dropout(dropout)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        gain = nn.init.calculate_gain("relu")
+        if self.bias:
+            nn.init.zeros_(self.h_bias)
+        if self.self_loop:
+            nn.init.xavier_uniform_(self.loop_weight, gain=gain)
+        nn.init.xavier_uniform_(self.conv_weights, gain=gain)
+        nn.init.xavier_uniform_(self.attn_l, gain=gain)
+        nn.init.xavier_uniform_(self.attn_r, gain=gain)
+
+    def forward(self, g, inputs):
+        coo = g.get_separate_coo_original()
+
+        def mm(gather, w, x, head_one):
+            return B.rgnn_relational_matmul(
+                {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": gather,
+                 "separate_coo_eids": coo["eids"]}, w, x, head_one, 0)
+
+        feat_src_per_edge = mm(coo["row_indices"], self.conv_weights, inputs, True)
+        el = mm(coo["eids"], self.attn_l.unsqueeze(-1), feat_src_per_edge, False)
+        feat_dst_per_edge = mm(coo["col_indices"], self.conv_weights, inputs, True)
+        er = mm(coo["eids"], self.attn_r.unsqueeze(-1), feat_dst_per_edge, False)
+        if self.gat_edge_parallel_flag:
+            h = B.relational_fused_gat_separate_coo(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
+        else:
+            h = B.relational_fused_gat_csr(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
+        h = h.view(-1, self.out_feat)
+        if self.self_loop:
+            h = h + th.matmul(inputs, self.loop_weight)
+        if self.bias:
+            h = h + self.h_bias
+        if self.activation:
+            h = self.activation(h)
+        return self.dropout(h)
+
+
+class HET_RGATModel(nn.Module):
+    """Stack of RGAT layers (hrt/python/RGAT/models.py:388-512)."""
+
+    def __init__(self, num_rels, in_dim, h_dim, out_dim, num_heads=1, num_layers=1, **kw):
+        super().__init__()
+        dims = [in_dim] + [h_dim] * (num_layers - 1) + [out_dim]
+        self.layers = nn.ModuleList(
+            HET_RGATLayer(dims[i], dims[i + 1], num_rels, num_heads,
+                          activation=th.relu if i + 1 < num_layers else None, **kw)
+            for i in range(num_layers))
+
+    def forward(self, g, h):
+        for layer in self.layers:
+            h = layer(g, h)
+        return h
+
+
+class HET_HGTLayerHetero(nn.Module):
+    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0):
+        super().__init__()
+        self.in_dim, self.out_dim = in_dim, out_dim
+        self.num_ntypes, self.num_relations = num_ntypes, num_rels
+        self.num_heads = num_heads
+        self.d_k = out_dim // num_heads
+        self.sqrt_dk = math.sqrt(self.d_k)
+        self.k_linears = nn.Parameter(th.empty(num_ntypes, 1, in_dim, out_dim))
+        self.q_linears = nn.Parameter(th.empty(num_ntypes, 1, in_dim, out_dim))
+        self.v_linears = nn.Parameter(th.empty(num_ntypes, 1, in_dim, out_dim))
+        self.a_linears = nn.Parameter(th.empty(num_ntypes, 1, out_dim, out_dim))
+        self.relation_pri = nn.Parameter(th.ones(num_rels, num_heads))
+        self.relation_att = nn.Parameter(th.empty(num_rels, num_heads, self.d_k, self.d_k))
+        self.relation_msg = nn.Parameter(th.empty(num_rels, num_heads, self.d_k, self.d_k))
+        self.skip = nn.Parameter(th.ones(num_ntypes, 1, 1, 1))
+        self.drop = nn.Dropout(dropout)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for p in (self.relation_att, self.relation_msg, self.k_linears, self.q_linears,
+                  self.v_linears, self.a_linears):
+            nn.init.xavier_uniform_(p)
+
+    def forward(self, G, h):
+        offs = G.get_original_node_type_offsets()
+        k = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
+        q = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.q_linears, h).view(-1, self.num_heads, self.d_k)
+        v = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.v_linears, h).view(-1, self.num_heads, self.d_k)
+        coo = G.get_separate_coo_original()
+
+        def mm(gather, w, x):
+            return B.rgnn_relational_matmul(
+                {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": gather,
+                 "separate_coo_eids": coo["eids"]}, w, x, False, 0)
+
+        attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
+        attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")
+        message_per_edge = mm(coo["row_indices"], self.relation_msg, v)
+        new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(
+            G, message_per_edge, attn_score, self.relation_pri / self.sqrt_dk)
+        new_h = B.rgnn_relational_matmul_no_scatter_gather_list(
+            offs, th.sigmoid(self.skip) * self.a_linears, new_h.view(-1, self.out_dim))
+        return new_h
+
+
+class HET_HGT_DGLHetero(nn.Module):
+    """Stack of HGT layers. The reference model wires a single layer
+    (hrt/python/HGT/models.py:312-330, second layer commented out); the
+    BASELINE "HGT 2-layer" config stacks it with ``num_layers=2``."""
+
+    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, num_layers=1, dropout=0.0):
+        super().__init__()
+        dims = [in_dim] + [out_dim] * num_layers
+        self.layers = nn.ModuleList(
+            HET_HGTLayerHetero(num_ntypes, num_rels, dims[i], dims[i + 1], num_heads, dropout)
+            for i in range(num_layers))
+
+    def forward(self, G, h):
+        for layer in self.layers:
+            h = layer(G, h)
+        return h
