@@ -1,0 +1,80 @@
+"""Parity of the relation-typed linear layer (segment MM, gather-MM-scatter) and
+its backward, through the torch_hrt ops, against the fp64 CPU oracle."""
+import pytest
+import torch
+
+from oracle import het_ops_ref as R
+from tests.test_gpu_ops import build, close
+
+pytestmark = pytest.mark.gpu
+
+# (nodes, edges, relations, heads, K, N, input_num_head_one)
+SHAPES = [
+    (60, 500, 3, 1, 64, 64, True),     # RGAT conv_weights, 1 head
+    (60, 500, 3, 4, 64, 16, True),     # RGAT conv_weights, 4 heads share the input row
+    (80, 900, 8, 4, 16, 16, False),    # HGT relation_att / relation_msg
+    (50, 400, 37, 1, 32, 128, True),   # many tiny segments, wider output
+    (50, 700, 4, 2, 32, 1, False),     # attention logits el/er (N == 1 row-dot path)
+    (50, 300, 5, 1, 64, 1, False),
+    (30, 200, 3, 1, 5, 3, True),       # odd sizes -> generic fallback
+    (40, 1, 2, 1, 64, 64, True),       # single edge
+]
+
+
+@pytest.mark.parametrize("n,e,r,H,Kd,Nd,head_one", SHAPES)
+def test_relational_matmul_fwd_bwd(cuda, n, e, r, H, Kd, Nd, head_one):
+    from het_b200.kernels import K
+    g = build(cuda, n, e, r, seed=e + Kd)
+    sc = g.get_separate_coo_original()
+    torch.manual_seed(Kd * Nd + e)
+    a_heads = 1 if head_one else H
+    W = torch.randn(r, H, Kd, Nd, device=cuda) / Kd ** 0.5
+    for gather_name in ("row_indices", "eids"):
+        gather = sc[gather_name]
+        rows_in = n if gather_name == "row_indices" else e
+        X = torch.randn(rows_in, a_heads, Kd, device=cuda)
+        args = {"separate_coo_rel_ptrs": sc["rel_ptrs"], "separate_coo_node_indices": gather,
+                "separate_coo_eids": sc["eids"]}
+        ret = torch.full((e, H, Nd), float("nan"), device=cuda)
+        K.rgnn_relational_matmul(args, 0, W, X, ret, head_one)
+        want = R.segment_mm(X.cpu(), gather.cpu(), W.cpu(), sc["eids"].cpu(), sc["rel_ptrs"].cpu(), e, a_heads)
+        close(ret, want, f"fwd/{gather_name}")
+        gout = torch.randn(e, H, Nd, device=cuda)
+        gX, gW = torch.zeros_like(X), torch.zeros_like(W)
+        K.backward_rgnn_relational_matmul(args, 0, W.transpose(2, 3).contiguous(), X, gout, gX, gW, head_one)
+        gX_ref, gW_ref = R.segment_mm_bwd(X.cpu(), gather.cpu(), W.cpu(), sc["eids"].cpu(), sc["rel_ptrs"].cpu(),
+                                          gout.cpu(), a_heads)
+        close(gX, gX_ref, f"grad_input/{gather_name}")
+        close(gW, gW_ref, f"grad_weight/{gather_name}", rtol=2e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("sizes,Kd,Nd", [([40, 0, 300, 7], 64, 64), ([129], 64, 64), ([5, 5, 5], 32, 16),
+                                          ([1000, 3], 128, 128), ([17, 60], 12, 20)])
+def test_no_scatter_gather_list_fwd_bwd(cuda, sizes, Kd, Nd):
+    """rows sorted by node type; weights [T,1,K,N] (HGT k/q/v/a linears)."""
+    from het_b200.kernels import K
+    T, M = len(sizes), sum(sizes)
+    offs = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int64)
+    torch.manual_seed(M + Kd)
+    W = torch.randn(T, 1, Kd, Nd, device=cuda) / Kd ** 0.5
+    X = torch.randn(M, Kd, device=cuda)
+    ret = torch.full((M, Nd), float("nan"), device=cuda)
+    offs_d = offs.to(cuda)
+    K.rgnn_relational_matmul_no_scatter_gather_list(offs_d, W, X, ret)
+    want = R.segment_mm(X.cpu(), None, W.cpu(), None, offs, M, 1)
+    close(ret, want, "fwd")
+    gout = torch.randn(M, Nd, device=cuda)
+    gX, gW = torch.zeros_like(X), torch.zeros_like(W)
+    K.backward_rgnn_relational_matmul_no_scatter_gather_list(offs_d, W.transpose(2, 3).contiguous(), X, gout, gX, gW)
+    gX_ref, gW_ref = R.segment_mm_bwd(X.cpu(), None, W.cpu(), None, offs, gout.cpu(), 1)
+    close(gX, gX_ref, "grad_input")
+    close(gW, gW_ref, "grad_weight", rtol=2e-4, atol=2e-5)
+
+
+def test_ops_reject_cpu_tensors():
+    """No CPU fallback: compute ops fail loudly on CPU tensors."""
+    from het_b200.kernels import K
+    offs = torch.tensor([0, 4])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        K.rgnn_relational_matmul_no_scatter_gather_list(offs, torch.zeros(1, 1, 4, 4), torch.zeros(4, 4),
+                                                        torch.zeros(4, 4))
