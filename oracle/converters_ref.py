@@ -65,6 +65,19 @@ def to_separate_csr(row, col, rel, eid, num_rows, num_rels):
     return row_ptrs[::num_rows].copy(), row_ptrs, col[o].astype(I64), eid[o].astype(I64)
 
 
+def separate_csr_rel_ptrs_ref_quirk(row_ptrs, num_rows, num_rels):
+    """What the reference actually returns as rel_ptrs from
+    ConvertIntegratedCOOToSeparateCSR (MyHyb.h:1039-1041): it adds the GLOBAL running
+    row_ptrs value at the end of each relation instead of that relation's edge count, so
+    rel_ptrs[r+1] = sum_{q<=r} (edges in relations 0..q). A reference bug (documented,
+    not copied: ``to_separate_csr`` returns the true offsets); kept so the golden
+    vectors pin the rest of the function bit-exactly."""
+    ends = row_ptrs[num_rows::num_rows][:num_rels]
+    out = np.zeros(num_rels + 1, dtype=I64)
+    np.cumsum(ends, out=out[1:])
+    return out
+
+
 def sort_by_etype_eids(rel_ptrs, row, col, eid):
     row, col, eid = row.copy(), col.copy(), eid.copy()
     for r in range(rel_ptrs.size - 1):
