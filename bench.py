@@ -1,0 +1,445 @@
+#!/usr/bin/env python
+"""Benchmark of the HET/Hector hot path on B200 — one JSON line on stdout (rank 0).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl hetb200|reference]
+                    [--workload rgat_bgs|hgt_mag|rgat_wikikg2|rgat_aifb] [--no-graph]
+
+A "step" is one full-graph training epoch (forward, loss, backward, Adam) exactly as the
+reference times it (hrt/python/RGNNUtils/RGNNUtils.py:291-345). Default workload at N=1 is
+BASELINE.json configs[1]: RGAT 1 layer, hidden 64, 1 head, on the synthetic BGS-shaped
+heterograph. For N>1 the graph grows with N (N x BGS-shaped, "scaling": "weak") and is
+sharded by destination range with an NCCL all-gather of node features per layer.
+
+`value`  : edges/s with everything resident in HBM (CUDA events, max over ranks).
+`e2e`    : the same metric through het_b200.train.FullGraphTrainer.step_from_host — node
+           features and labels copied from pinned host memory every step, loss read back.
+`roofline`: the kernel with the largest share of the step, timed alone inside this run.
+`cpu_baseline`: the repo's DGL baseline model restated in plain torch (oracle/models_ref.py),
+           timed on this box's host cores on a bounded sample.
+`--impl reference`: that CPU baseline as its own arm (the reference's CUDA build and DGL are
+           not installable here — DESIGN.md).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (model, graph shape, heads, layers, BASELINE.json config it corresponds to)
+    "rgat_aifb": ("rgat", "aifb", 1, 1, "configs[0] graph, RGAT"),
+    "rgat_bgs": ("rgat", "bgs", 1, 1, "configs[1]"),
+    "hgt_mag": ("hgt", "mag", 4, 2, "configs[2]"),
+    "rgat_wikikg2": ("rgat", "wikikg2", 1, 1, "configs[3]"),
+}
+METRIC = "rgnn_fullgraph_fwd_bwd_edges_per_s"
+UNIT = "edges/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="hetb200", choices=["hetb200", "reference"])
+    ap.add_argument("--workload", default="rgat_bgs", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=None, help="graph scale (default 1.0 x gpus)")
+    ap.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the repo's DGL baseline models, restated (oracle/models_ref.py)
+# ---------------------------------------------------------------------------
+def cpu_dgl_baseline(wl, coo, steps, warmup, budget_s):
+    """Times fwd + loss + bwd + Adam of the DGL-baseline restatement in fp32 on all host
+    cores. Returns (edges_per_s, ms_per_step, cores, sample description, steps done)."""
+    import torch
+    import torch.nn.functional as Fn
+    from oracle import models_ref as M
+
+    kind, _, heads, layers, _ = WORKLOADS[wl]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n, R, D = coo.num_nodes, coo.num_rels, 64
+    src, dst, et = (torch.from_numpy(a) for a in (coo.src, coo.dst, coo.etype))
+    offs = coo.node_type_offsets
+    ranges = [(int(offs[s]), int(offs[s + 1]), int(offs[d]), int(offs[d + 1]))
+              for s, d in zip(coo.rel_src_type, coo.rel_dst_type)]
+    g = torch.Generator().manual_seed(0)
+    x = torch.nn.Parameter(torch.rand(n, D, generator=g) * 2 - 1)
+    labels = torch.randint(0, D, (n,), generator=g)
+    F = D // heads
+
+    def P(*shape):
+        return torch.nn.Parameter(torch.randn(*shape, generator=g) * 0.1)
+
+    if kind == "rgat":
+        ps = [dict(fc=P(R, D, D), al=P(R, heads, F), ar=P(R, heads, F)) for _ in range(layers)]
+
+        def fwd():
+            h = x
+            for p in ps:
+                h = M.dgl_rgat_layer(src, dst, et, h, p["fc"], p["al"], p["ar"], 0.2, R, ranges)
+            return h
+    else:
+        T = coo.num_ntypes
+        ps = [dict(k=P(T, 1, D, D), q=P(T, 1, D, D), v=P(T, 1, D, D), a=P(T, 1, D, D), pri=P(R, heads),
+                   att=P(R, heads, F, F), msg=P(R, heads, F, F), skip=P(T, 1, 1, 1)) for _ in range(layers)]
+        offs_t = torch.from_numpy(offs)
+
+        def fwd():
+            h = x
+            for p in ps:
+                h = M.dgl_hgt_layer(src, dst, et, offs_t, coo.rel_dst_type, h, p["k"], p["q"], p["v"], p["a"],
+                                    p["pri"], p["att"], p["msg"], p["skip"], R, ranges)
+            return h
+    params = [x] + [t for p in ps for t in p.values()]
+    opt = torch.optim.Adam(params, lr=1e-2)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        loss = Fn.nll_loss(Fn.log_softmax(fwd(), dim=-1), labels)
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+
+    t_begin = time.perf_counter()
+    for _ in range(warmup):
+        step()
+        if time.perf_counter() - t_begin > budget_s / 2:
+            break
+    done, t0 = 0, time.perf_counter()
+    while done < steps:
+        step()
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = (time.perf_counter() - t0) / done
+    sample = (f"{done} full-graph step(s) of the DGL-baseline {kind.upper()} restatement (fp32, {layers} layer(s), "
+              f"{heads} head(s)) on {coo.name}: N={n} R={R} E={coo.num_edges}")
+    return coo.num_edges * layers / dt, dt * 1e3, cores, sample, done
+
+
+# ---------------------------------------------------------------------------
+# Per-kernel roofline legs (timed alone, L2 flushed between launches)
+# ---------------------------------------------------------------------------
+def _time_kernel(torch, fn, flush, reps=10):
+    """Average device time (ms) of fn() over `reps` launches, each preceded by an L2 flush
+    (a 256 MB write, larger than the 126 MB L2). CUDA events on torch's current stream,
+    which is the stream the torch_hrt ops launch on."""
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(reps):
+        flush.add_(1.0)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / reps
+
+
+def kernel_rooflines(trainer, peak_gbs, peak_src):
+    """Times the hot kernels of one RGAT / HGT layer in isolation on the trainer's graph and
+    returns roofline dicts. `achieved` = algorithmic (compulsory) bytes / time, with the
+    byte formulas of SURVEY.md §8(d) / DESIGN.md §4 (s = 4 B fp32, i = 8 B int64 indices)."""
+    import torch
+    from het_b200.kernels import K
+    g, dev = trainer.g, trainer.device
+    E, N, Ns, R = g.num_edges, g.num_nodes, g.num_src_nodes, g.num_rels
+    coo, ic, oc = g.get_separate_coo_original(), g.get_in_csr(), g.get_out_csr()
+    layer = trainer.model.layers[0]
+    H = layer.num_heads
+    D = 64
+    F = D // H
+    flush = torch.zeros(64 * 1024 * 1024, device=dev)
+    uniq_src = int(torch.unique(coo["row_indices"]).numel())
+    out = []
+
+    def leg(name, fn, nbytes, note):
+        ms = _time_kernel(torch, fn, flush)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"kernel": name, "bound": "hbm", "achieved": round(gbs, 1), "peak": peak_gbs, "unit": "GB/s",
+                    "frac": round(gbs / peak_gbs, 4), "peak_source": peak_src, "ms": round(ms, 4),
+                    "algorithmic_bytes": int(nbytes), "traffic": None, "note": note})
+
+    x = torch.rand(Ns, D, device=dev) * 2 - 1
+    eidx = torch.empty(0, dtype=torch.int64, device=dev)
+    if trainer.kind == "rgat":
+        W = layer.conv_weights.detach().contiguous()
+        WT = W.transpose(2, 3).contiguous()
+        feat = torch.empty(E, H, F, device=dev)
+        d_row = {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": coo["row_indices"],
+                 "separate_coo_eids": coo["eids"]}
+        leg("segment_mm_fwd(gather src, X.W_r)", lambda: K.rgnn_relational_matmul(d_row, 0, W, x, feat, True),
+            uniq_src * D * 4 + E * D * 4 + R * D * D * 4 + E * 8,
+            "M_unique_in*Din*s + M*Dout*s + G*Din*Dout*s + M*i")
+        el, er = torch.randn(E, H, 1, device=dev), torch.randn(E, H, 1, device=dev)
+        ssum, ex, ret = torch.empty(N, H, device=dev), torch.empty(E, H, 1, device=dev), torch.empty(N, H, F, device=dev)
+        leg("rgat_edge_softmax_aggregate_fwd(in-CSR)",
+            lambda: K.relational_fused_gat_csr(ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], eidx,
+                                               eidx, feat, el, er, ssum, ex, ret, 0.2),
+            E * D * 4 + 2 * E * H * 4 + E * 8 + (N + 1) * 8 + E * H * 4 + N * H * 4 + N * D * 4,
+            "feat + el,er + eids + row_ptr ; exp + sum + ret")
+        gout = torch.randn(N, H, F, device=dev)
+        gf, gel, ger = torch.empty_like(feat), torch.empty_like(el), torch.empty_like(er)
+        leg("rgat_edge_bwd(out-CSR)",
+            lambda: K.backward_relational_fused_gat_csr(oc["row_ptrs"], oc["col_indices"], oc["eids"], oc["rel_types"],
+                                                        eidx, eidx, feat, el, er, ssum, ex, ret, gout, gf, gel, ger, 0.2),
+            E * D * 4 + 3 * E * H * 4 + N * H * 4 + 2 * N * D * 4 + 2 * E * 8 + E * D * 4 + 2 * E * H * 4,
+            "feat,el,er,exp,sum,ret,gout,idx ; grad_feat,grad_el,grad_er")
+        gx, gw = torch.zeros_like(x), torch.zeros_like(W)
+        leg("segment_mm_bwd(dX scatter + dW)",
+            lambda: K.backward_rgnn_relational_matmul(d_row, 0, WT, x, gf, gx, gw, True),
+            E * D * 4 + 2 * uniq_src * D * 4 + 2 * R * D * D * 4 + E * 8,
+            "dY + X_unique + W ; dX_unique + dW ; gather list")
+    else:
+        Watt = layer.relation_att.detach().contiguous()
+        q = torch.randn(N, H, F, device=dev)
+        k = torch.randn(Ns, H, F, device=dev)
+        wq = torch.empty(E, H, F, device=dev)
+        d_col = {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": coo["col_indices"],
+                 "separate_coo_eids": coo["eids"]}
+        uniq_dst = int(torch.unique(coo["col_indices"]).numel())
+        leg("segment_mm_fwd(gather dst, q.W_att)", lambda: K.rgnn_relational_matmul(d_col, 0, Watt, q, wq, False),
+            uniq_dst * D * 4 + E * D * 4 + R * H * F * F * 4 + E * 8, "M_unique_in*D*s + M*D*s + W + M*i")
+        score = torch.empty(E, H, device=dev)
+        leg("inner_product_fwd", lambda: K.rgnn_inner_product_right_node_separatecoo(
+            {}, 0, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, score),
+            E * D * 4 + uniq_src * D * 4 + 2 * E * 8 + E * H * 4, "left + right_unique + idx ; score")
+        mu = torch.ones(R, H, device=dev) / 4
+        ssum, t, norm = torch.empty(N, H, device=dev), torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
+        leg("hgt_edge_softmax_fwd(in-CSR)", lambda: K.hgt_full_graph_edge_softmax_ops_csr(
+            ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], score, mu, ssum, t, norm),
+            E * H * 4 + 2 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4, "a + eid,rel + row_ptr ; t + norm + sum")
+        new_h = torch.empty(N, H, F, device=dev)
+        leg("hgt_aggregate_fwd(in-CSR)", lambda: K.hgt_full_graph_message_mean_aggregation_csr(
+            ic["row_ptrs"], ic["col_indices"], ic["rel_types"], ic["eids"], wq, t, ssum, mu, new_h),
+            E * D * 4 + E * H * 4 + E * 8 + (N + 1) * 8 + N * H * 4 + N * D * 4, "msg + t + eid + row_ptr + sum ; out")
+    del flush
+    return out
+
+
+# ---------------------------------------------------------------------------
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def _make_graph(args):
+    from het_b200 import graphs
+    kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
+    scale = args.scale if args.scale is not None else float(max(1, args.gpus))
+    return graphs.SHAPES[shape](scale=scale), scale
+
+
+def run_reference(args, rank):
+    """The reference arm: the repo's DGL baseline (restated, oracle/models_ref.py) on the host
+    cores. Rank 0 only; other ranks exit without work."""
+    if rank != 0:
+        return
+    coo, scale = _make_graph(args)
+    kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
+    val, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, args.steps, args.warmup, budget_s=150.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s), hidden 64, {heads} head(s), "
+                               f"{coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
+                   "timing": "time.perf_counter around fwd+loss+bwd+Adam, all host cores"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback for the product path)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == max(1, args.gpus), f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    from het_b200.kernels import launch_count
+    from het_b200.train import FullGraphTrainer
+
+    kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
+    coo, scale = _make_graph(args)
+    use_graph = not args.no_graph
+    trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
+                               cuda_graph=use_graph)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident arm -----------------------------------------------------
+    l0 = launch_count()
+    trainer._zero("embed")
+    eager_loss = None
+    if use_graph:  # count this library's launches per step once, eagerly (graph replays bypass the host counter)
+        trainer.cuda_graph = False
+        eager_loss = float(trainer.step())
+        trainer.cuda_graph = True
+    launches_per_step = launch_count() - l0
+    for _ in range(max(3, args.warmup)):
+        trainer.step()
+    if not use_graph:
+        l1 = launch_count(); trainer.step(); launches_per_step = launch_count() - l1
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        loss = trainer.step()
+    ev1.record()
+    barrier()
+    ms_total = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = float(ms_total.item()) / args.steps
+    clocks = sampler.stop() if sampler else None
+    final_loss = float(loss.item())
+    value = coo.num_edges * layers / (ms_step * 1e-3)
+
+    # ---- end-to-end arm (host buffers, H2D + D2H inside the timed region) --
+    gen = torch.Generator().manual_seed(7)
+    x_host = (torch.rand(trainer.n_local, 64, generator=gen) * 2 - 1).pin_memory()
+    y_host = torch.randint(0, 64, (trainer.n_local,), generator=gen).pin_memory()
+    for _ in range(max(3, args.warmup)):
+        trainer.step_from_host(x_host, y_host)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        e2e_loss = trainer.step_from_host(x_host, y_host)
+    e1.record()
+    barrier()
+    e_ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+    e2e_ms_step = float(e_ms.item()) / args.steps
+    e2e_value = coo.num_edges * layers / (e2e_ms_step * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = _peaks()
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {
+            "workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s) fwd+loss+bwd+Adam, hidden 64, "
+                        f"{heads} head(s), {coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
+            "parallelism": "single GPU" if world == 1 else f"destination-range shards x{world}, NCCL all-gather of "
+                           "source rows per layer, reduce-scatter in backward, all-reduce of weight grads",
+            "cuda_graph": use_graph,
+            "l2": "inputs larger than L2: per-edge tensors of one step total "
+                  f"{coo.num_edges // world * 64 * 4 * 6 / 1e6:.0f} MB per GPU vs 126 MB L2 (no flush between steps)",
+            "edges_per_step": coo.num_edges * layers,
+        },
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_step,
+                "h2d_bytes_per_step": trainer.h2d_bytes_per_step() * world,
+                "d2h_bytes_per_step": trainer.d2h_bytes_per_step() * world, "loss": e2e_loss},
+        "gpu_launches": int(launches_per_step * args.steps),
+        "gpu_launches_per_step": int(launches_per_step),
+        "clocks": clocks, "loss": final_loss, "eager_first_loss": eager_loss,
+    }
+    if not args.no_roofline:
+        legs = kernel_rooflines(trainer, peak, peak_src)
+        top = max(legs, key=lambda d: d["ms"])
+        line["roofline"] = {k: top[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "kernel",
+                                                 "ms", "algorithmic_bytes", "peak_source")}
+        line["kernels"] = legs
+    if world == 1 and not args.no_cpu_baseline:
+        del trainer
+        torch.cuda.empty_cache()
+        v, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, 3, 1, budget_s=25.0)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                                "ms_per_step": ms}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

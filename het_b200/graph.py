@@ -23,19 +23,36 @@ from .kernels import K
 
 
 class HetGraph:
+    """``num_nodes`` rows index destinations (in-CSR rows, op outputs); sources index
+    ``num_src_nodes`` rows (out-CSR rows, gathered inputs). On one GPU both are N. A
+    destination-range shard (het_b200/parallel.py) has local destination ids and sources
+    that index the all-gathered feature matrix."""
+
     def __init__(self, coo: HeteroCOO, device="cuda"):
+        self._build(coo.name, torch.from_numpy(coo.src), torch.from_numpy(coo.dst),
+                    torch.from_numpy(coo.etype), coo.num_nodes, coo.num_nodes, coo.num_rels,
+                    torch.from_numpy(coo.node_type_offsets), device)
         dev = torch.device(device)
-        self.name = coo.name
-        self.num_nodes = coo.num_nodes
-        self.num_rels = coo.num_rels
-        self.num_edges = coo.num_edges
-        src = torch.from_numpy(coo.src).to(dev)
-        dst = torch.from_numpy(coo.dst).to(dev)
-        rel = torch.from_numpy(coo.etype).to(dev)
-        eid = torch.arange(self.num_edges, dtype=torch.int64, device=dev)
-        self.node_type_offsets = torch.from_numpy(coo.node_type_offsets).to(dev)
         self.rel_src_type = torch.from_numpy(coo.rel_src_type).to(dev)
         self.rel_dst_type = torch.from_numpy(coo.rel_dst_type).to(dev)
+
+    @classmethod
+    def from_arrays(cls, name, src, dst, rel, num_src_nodes, num_dst_nodes, num_rels,
+                    node_type_offsets, device="cuda"):
+        g = cls.__new__(cls)
+        g._build(name, src, dst, rel, num_src_nodes, num_dst_nodes, num_rels, node_type_offsets, device)
+        return g
+
+    def _build(self, name, src, dst, rel, num_src_nodes, num_dst_nodes, num_rels, node_type_offsets, device):
+        dev = torch.device(device)
+        self.name = name
+        self.num_nodes = int(num_dst_nodes)
+        self.num_src_nodes = int(num_src_nodes)
+        self.num_rels = int(num_rels)
+        self.num_edges = int(src.numel())
+        src, dst, rel = src.to(dev), dst.to(dev), rel.to(dev)
+        eid = torch.arange(self.num_edges, dtype=torch.int64, device=dev)
+        self.node_type_offsets = node_type_offsets.to(dev)
 
         # relation sort: input is in eid order, so a stable sort by relation
         # yields (relation, eid) order — the net effect of ToSeparateCOO +
@@ -48,7 +65,7 @@ class HetGraph:
             "rel_ptrs": rel_ptrs, "row_indices": row, "col_indices": col, "eids": eid,
         }
         new_eid = remap  # edge id of original edge i
-        o_col, o_rel, o_eid, o_ptr = K.hetb200_stable_sort_by_key(src, self.num_nodes, [dst, rel, new_eid])
+        o_col, o_rel, o_eid, o_ptr = K.hetb200_stable_sort_by_key(src, self.num_src_nodes, [dst, rel, new_eid])
         self.out_csr = {"row_ptrs": o_ptr, "col_indices": o_col, "rel_types": o_rel, "eids": o_eid}
         i_col, i_rel, i_eid, i_ptr = K.hetb200_stable_sort_by_key(dst, self.num_nodes, [src, rel, new_eid])
         self.in_csr = {"row_ptrs": i_ptr, "col_indices": i_col, "rel_types": i_rel, "eids": i_eid}

@@ -57,7 +57,11 @@ class HET_RGATLayer(nn.Module):
         nn.init.xavier_uniform_(self.attn_l, gain=gain)
         nn.init.xavier_uniform_(self.attn_r, gain=gain)
 
-    def forward(self, g, inputs):
+    def forward(self, g, inputs, inputs_dst=None):
+        """``inputs`` rows are indexed by source ids; ``inputs_dst`` (default: the same
+        tensor) by destination ids — they differ only on a destination-range shard."""
+        if inputs_dst is None:
+            inputs_dst = inputs
         coo = g.get_separate_coo_original()
 
         def mm(gather, w, x, head_one):
@@ -67,7 +71,7 @@ class HET_RGATLayer(nn.Module):
 
         feat_src_per_edge = mm(coo["row_indices"], self.conv_weights, inputs, True)
         el = mm(coo["eids"], self.attn_l.unsqueeze(-1), feat_src_per_edge, False)
-        feat_dst_per_edge = mm(coo["col_indices"], self.conv_weights, inputs, True)
+        feat_dst_per_edge = mm(coo["col_indices"], self.conv_weights, inputs_dst, True)
         er = mm(coo["eids"], self.attn_r.unsqueeze(-1), feat_dst_per_edge, False)
         if self.gat_edge_parallel_flag:
             h = B.relational_fused_gat_separate_coo(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
@@ -75,7 +79,7 @@ class HET_RGATLayer(nn.Module):
             h = B.relational_fused_gat_csr(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
         h = h.view(-1, self.out_feat)
         if self.self_loop:
-            h = h + th.matmul(inputs, self.loop_weight)
+            h = h + th.matmul(inputs_dst, self.loop_weight)
         if self.bias:
             h = h + self.h_bias
         if self.activation:
@@ -94,9 +98,10 @@ class HET_RGATModel(nn.Module):
                           activation=th.relu if i + 1 < num_layers else None, **kw)
             for i in range(num_layers))
 
-    def forward(self, g, h):
+    def forward(self, g, h, gather=None):
+        """``gather`` (multi-GPU): maps owned rows to the all-gathered source matrix."""
         for layer in self.layers:
-            h = layer(g, h)
+            h = layer(g, h) if gather is None else layer(g, gather(h), h)
         return h
 
 
@@ -124,16 +129,20 @@ class HET_HGTLayerHetero(nn.Module):
                   self.v_linears, self.a_linears):
             nn.init.xavier_uniform_(p)
 
-    def forward(self, G, h):
+    def forward(self, G, h, gather=None):
+        """``gather`` (multi-GPU): all-gathers K and V rows of the owned destinations into
+        the source-indexed matrices; Q stays local (it is gathered by destination)."""
         offs = G.get_original_node_type_offsets()
         k = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
         q = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.q_linears, h).view(-1, self.num_heads, self.d_k)
         v = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.v_linears, h).view(-1, self.num_heads, self.d_k)
+        if gather is not None:
+            k, v = gather(k), gather(v)
         coo = G.get_separate_coo_original()
 
-        def mm(gather, w, x):
+        def mm(idx, w, x):
             return B.rgnn_relational_matmul(
-                {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": gather,
+                {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": idx,
                  "separate_coo_eids": coo["eids"]}, w, x, False, 0)
 
         attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
@@ -158,7 +167,7 @@ class HET_HGT_DGLHetero(nn.Module):
             HET_HGTLayerHetero(num_ntypes, num_rels, dims[i], dims[i + 1], num_heads, dropout)
             for i in range(num_layers))
 
-    def forward(self, G, h):
+    def forward(self, G, h, gather=None):
         for layer in self.layers:
-            h = layer(G, h)
+            h = layer(G, h, gather)
         return h

@@ -1,0 +1,142 @@
+"""Full-graph training step — the call a user makes.
+
+Host-side mirror of ``HET_RGNN_train`` (hrt/python/RGNNUtils/RGNNUtils.py:199-345):
+one "epoch" is one full-graph step = ``model(g, node_embed)`` → ``nll_loss(log_softmax)``
+→ ``loss.backward()`` → ``optimizer.step()`` (Adam over the model and the learnable node
+embedding, RGNNUtils.py:78-121). Two differences, both B200-first:
+
+* the whole step (forward, loss, backward, Adam) is captured once in a CUDA graph and
+  replayed, because at BGS size every kernel is a few microseconds and the step is
+  otherwise launch-bound;
+* with ``world > 1`` the graph is sharded by destination range (het_b200/parallel.py).
+
+``step()`` keeps everything resident in HBM (the reference's embedding path).
+``step_from_host(x, labels)`` is the end-to-end path for graphs that come with node
+features: it copies this step's features and labels from pinned host memory, runs the same
+forward/backward/Adam (the feature gradient is still produced, as the embedding path's
+is) and returns the loss as a Python float (a device→host read).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as Fn
+
+from . import parallel
+from .graph import HetGraph
+from .graphs import HeteroCOO
+from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel
+
+
+class FullGraphTrainer:
+    def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
+                 layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0):
+        assert kind in ("rgat", "hgt")
+        self.kind, self.device, self.rank, self.world, self.group = kind, torch.device(device), rank, world, group
+        self.num_nodes_total = coo.num_nodes
+        self.num_edges_total = coo.num_edges
+        if world > 1:
+            self.plan = parallel.make_shard(coo, rank, world)
+            self.g = parallel.shard_graph(self.plan, coo, self.device)
+            self.n_local = self.plan.num_local_nodes
+            self.lo = self.plan.lo
+        else:
+            self.plan = None
+            self.g = HetGraph(coo, self.device)
+            self.n_local, self.lo = coo.num_nodes, 0
+        self.num_edges_local = self.g.num_edges
+
+        torch.manual_seed(seed)  # identical replicated weights on every rank
+        if kind == "rgat":
+            self.model = HET_RGATModel(coo.num_rels, hidden, hidden, out_dim, heads, layers).to(self.device)
+        else:
+            self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers).to(self.device)
+        gen = torch.Generator().manual_seed(seed + 1)
+        embed_full = torch.rand(coo.num_nodes, hidden, generator=gen) * 2 - 1
+        labels_full = torch.randint(0, out_dim, (coo.num_nodes,), generator=gen)
+        self.embed = HET_RelGraphEmbed(self.n_local, hidden).to(self.device)
+        with torch.no_grad():
+            self.embed.embeds.copy_(embed_full[self.lo:self.lo + self.n_local])
+        self.labels = labels_full[self.lo:self.lo + self.n_local].to(self.device)
+        self.x_in = torch.zeros(self.n_local, hidden, device=self.device, requires_grad=True)
+        self.labels_in = torch.zeros(self.n_local, dtype=torch.int64, device=self.device)
+
+        cap = bool(cuda_graph)
+        self.opt_embed = torch.optim.Adam(list(self.model.parameters()) + list(self.embed.parameters()),
+                                          lr=lr, capturable=cap)
+        self.opt_feat = torch.optim.Adam(list(self.model.parameters()), lr=lr, capturable=cap)
+        self.cuda_graph = cap
+        self._graphs = {}
+        self._loss = {}
+
+    # ------------------------------------------------------------------
+    def _gather(self, x):
+        return parallel.all_gather_rows(x, self.plan.max_rows, self.group)
+
+    def forward(self, h0):
+        if self.world == 1:
+            return self.model(self.g, h0)
+        return self.model(self.g, h0, self._gather)
+
+    def _step_body(self, mode):
+        if mode == "embed":
+            h0, labels, opt = self.embed(), self.labels, self.opt_embed
+        else:
+            h0, labels, opt = self.x_in, self.labels_in, self.opt_feat
+        logits = self.forward(h0)
+        loss = Fn.nll_loss(Fn.log_softmax(logits, dim=-1), labels, reduction="sum") / self.num_nodes_total
+        loss.backward()
+        if self.world > 1:
+            parallel.all_reduce_grads(list(self.model.parameters()), self.group)
+        opt.step()
+        return loss.detach()
+
+    def _zero(self, mode):
+        opt = self.opt_embed if mode == "embed" else self.opt_feat
+        opt.zero_grad(set_to_none=True)
+        self.x_in.grad = None
+
+    def _run(self, mode):
+        if not self.cuda_graph:
+            self._zero(mode)
+            self._loss[mode] = self._step_body(mode)
+            return self._loss[mode]
+        if mode not in self._graphs:
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(side):
+                for _ in range(3):  # warm-up outside capture (lazy inits, Adam state)
+                    self._zero(mode)
+                    self._step_body(mode)
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            self._zero(mode)
+            with torch.cuda.graph(graph):
+                self._loss[mode] = self._step_body(mode)
+            self._graphs[mode] = graph
+        self._graphs[mode].replay()
+        return self._loss[mode]
+
+    # ------------------------------------------------------------------
+    def step(self) -> torch.Tensor:
+        """One epoch with the learnable node embedding (everything resident)."""
+        return self._run("embed")
+
+    def step_from_host(self, x_host: torch.Tensor, labels_host: torch.Tensor) -> float:
+        """One epoch with this step's node features / labels coming from pinned host memory."""
+        with torch.no_grad():
+            self.x_in.copy_(x_host, non_blocking=True)
+            self.labels_in.copy_(labels_host, non_blocking=True)
+        loss = self._run("feat")
+        if self.world > 1:
+            loss = loss.clone()
+            dist.all_reduce(loss, group=self.group)
+        return float(loss.item())
+
+    def h2d_bytes_per_step(self) -> int:
+        return self.n_local * self.x_in.shape[1] * 4 + self.n_local * 8
+
+    @staticmethod
+    def d2h_bytes_per_step() -> int:
+        return 4

@@ -76,27 +76,34 @@ def hgt_layer(src, dst, etype, offs, h, k_w, q_w, v_w, a_w, rel_pri, rel_att, re
 
 
 # ------------------------- DGL baselines, restated ------------------------
-def dgl_rgat_layer(src, dst, etype, x, fc_w, attn_l, attn_r, slope, num_rels):
+def dgl_rgat_layer(src, dst, etype, x, fc_w, attn_l, attn_r, slope, num_rels, ranges=None):
     """HeteroGraphConv({rel: GATConv}, aggregate='sum'): softmax per (dst, relation).
-    fc_w [R,Din,H*F]; attn_* [R,H,F]."""
+    fc_w [R,Din,H*F]; attn_* [R,H,F]. ``ranges[r] = (s_lo, s_hi, d_lo, d_hi)``: node-id
+    ranges of relation r's source / destination node types — GATConv's fc runs on the nodes
+    of those types only (DGL passes per-type feature dicts); None = all nodes."""
     n, H, Fh = x.shape[0], attn_l.shape[1], attn_l.shape[2]
     out = torch.zeros(n, H, Fh, dtype=x.dtype)
     for r in range(num_rels):
-        m = etype == r
-        if not bool(m.any()):
+        idx = torch.nonzero(etype == r).squeeze(1)
+        if idx.numel() == 0:
             continue
-        s, d = src[m], dst[m]
-        f = (x @ fc_w[r]).view(n, H, Fh)
-        e = torch.nn.functional.leaky_relu((f * attn_l[r]).sum(-1)[s] + (f * attn_r[r]).sum(-1)[d], slope)
+        s, d = src[idx], dst[idx]
+        s_lo, s_hi, d_lo, d_hi = ranges[r] if ranges is not None else (0, n, 0, n)
+        fs = (x[s_lo:s_hi] @ fc_w[r]).view(-1, H, Fh)
+        fd = fs if (s_lo, s_hi) == (d_lo, d_hi) else (x[d_lo:d_hi] @ fc_w[r]).view(-1, H, Fh)
+        e = torch.nn.functional.leaky_relu(
+            (fs * attn_l[r]).sum(-1)[s - s_lo] + (fd * attn_r[r]).sum(-1)[d - d_lo], slope)
         e = torch.exp(e - e.max())
         a = _segment_softmax_sum(e, d, n)
-        out.index_add_(0, d, a.unsqueeze(-1) * f[s])
+        out = out.index_add(0, d, a.unsqueeze(-1) * fs[s - s_lo])
     return out.reshape(n, -1)
 
 
 def dgl_hgt_layer(src, dst, etype, offs, ntype_of_rel_dst, h, k_w, q_w, v_w, a_w, rel_pri,
-                  rel_att, rel_msg, skip, num_rels):
-    """HGT/models_dgl.py: per-relation edge_softmax, cross_reducer='mean'."""
+                  rel_att, rel_msg, skip, num_rels, ranges=None):
+    """HGT/models_dgl.py: per-relation edge_softmax, cross_reducer='mean'.
+    ``ranges[r] = (s_lo, s_hi, d_lo, d_hi)`` as in dgl_rgat_layer (the relation's K/V
+    projections run on its source node type only)."""
     n, H, dk = h.shape[0], rel_att.shape[1], rel_att.shape[2]
     k = _typed_linear(h, k_w, offs).view(n, H, dk)
     q = _typed_linear(h, q_w, offs).view(n, H, dk)
@@ -108,12 +115,13 @@ def dgl_hgt_layer(src, dst, etype, offs, ntype_of_rel_dst, h, k_w, q_w, v_w, a_w
         if not bool(m.any()):
             continue
         s, d = src[m], dst[m]
-        kk = torch.einsum("nhk,hkf->nhf", k, rel_att[r])
-        vv = torch.einsum("nhk,hkf->nhf", v, rel_msg[r])
-        t = (q[d] * kk[s]).sum(-1) * rel_pri[r] / (dk ** 0.5)
+        s_lo, s_hi = (ranges[r][0], ranges[r][1]) if ranges is not None else (0, n)
+        kk = torch.einsum("nhk,hkf->nhf", k[s_lo:s_hi], rel_att[r])
+        vv = torch.einsum("nhk,hkf->nhf", v[s_lo:s_hi], rel_msg[r])
+        t = (q[d] * kk[s - s_lo]).sum(-1) * rel_pri[r] / (dk ** 0.5)
         t = torch.exp(t - t.max())
         a = _segment_softmax_sum(t, d, n)
-        acc.index_add_(0, d, a.unsqueeze(-1) * vv[s])
+        acc = acc.index_add(0, d, a.unsqueeze(-1) * vv[s - s_lo])
         t_d = int(ntype_of_rel_dst[r])
         cnt[int(offs[t_d]):int(offs[t_d + 1])] += 1
     acc = acc / cnt.clamp(min=1)
