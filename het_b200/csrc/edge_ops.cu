@@ -23,49 +23,133 @@ __device__ __forceinline__ float leaky_exp(float x, float slope) {
 }
 
 // ---------------------------------------------------------------------------
-// Destination-parallel weighted aggregation over an in-CSR.
+// Edge-balanced weighted aggregation over an in-CSR.
+//
+// Work is split by CSR *position*, not by destination row: lane group g owns the
+// kChunk consecutive positions [g*kChunk, (g+1)*kChunk) and walks them in order,
+// carrying the running row. A row that lies inside one chunk is reduced in
+// registers and stored once; a row that crosses a chunk boundary (a power-law hub
+// spans thousands of chunks) is accumulated with 128-bit vector reductions into
+// its output row, which a pre-pass has zeroed, and (RGAT) normalised by a
+// post-pass once its sum is complete. Every SM gets the same number of edges
+// whatever the degree distribution.
 //   MODE 0 (RGAT): w = exp(lrelu(el[e,h]+er[e,h])); writes exp_out, sum;
 //                  ret = (Σ w·feat) / Σ w
-//   MODE 1 (HGT):  w = score[e,h]; ret = (Σ w·feat) · (divide ? 1/sum[d,h] : 1)
+//   MODE 1 (HGT):  w = score[e,h] · (divide ? 1/sum[d,h] : 1); ret = Σ w·feat
 // ---------------------------------------------------------------------------
-template <int LPR, int MODE>
+constexpr int kChunk = 32;
+
+__device__ __forceinline__ bool row_is_split(int64_t start, int64_t end) {
+  return end > start && (start / kChunk) != ((end - 1) / kChunk);
+}
+
+// Pre-pass: rows without in-edges get ret = 0 (and sum = 0); rows that cross a
+// chunk boundary are zeroed so the walkers can accumulate into them.
+template <int LPR>
 __global__ void __launch_bounds__(kThreads)
-    dst_aggregate_kernel(const int64_t *__restrict__ row_ptr,
-                         const int64_t *__restrict__ eids, int64_t num_rows,
-                         const float *__restrict__ feat,
-                         const float *__restrict__ wa,  // el | score
-                         const float *__restrict__ wb,  // er | unused
-                         float *__restrict__ sum, float *__restrict__ exp_out,
-                         float *__restrict__ ret, int H, int hw, float slope,
-                         int divide) {
+    agg_prepare_kernel(const int64_t *__restrict__ row_ptr, int64_t num_rows,
+                       float *__restrict__ sum, float *__restrict__ ret, int H,
+                       int hw, int write_sum) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
-  __shared__ int64_t heavy_row[GROUPS];
-  __shared__ int heavy_n;
-  __shared__ float4 red_acc[GROUPS][LPR];
-  __shared__ float red_sum[GROUPS][LPR];
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int64_t d = (int64_t)blockIdx.x * GROUPS + g;
+  if (d >= num_rows) return;
+  const int64_t start = __ldg(row_ptr + d), end = __ldg(row_ptr + d + 1);
+  if (end == start || row_is_split(start, end)) {
+    st4(ret + d * D + 4 * l, make_float4(0.f, 0.f, 0.f, 0.f));
+    if (write_sum && (l % hw) == 0) sum[d * H + l / hw] = 0.f;
+  }
+}
 
-  const int g = threadIdx.x / LPR;
-  const int l = threadIdx.x % LPR;
+// Post-pass (RGAT): split rows hold Σ w·feat; divide by the completed Σ w.
+template <int LPR>
+__global__ void __launch_bounds__(kThreads)
+    agg_normalize_kernel(const int64_t *__restrict__ row_ptr, int64_t num_rows,
+                         const float *__restrict__ sum, float *__restrict__ ret,
+                         int H, int hw) {
+  constexpr int GROUPS = kThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int64_t d = (int64_t)blockIdx.x * GROUPS + g;
+  if (d >= num_rows) return;
+  const int64_t start = __ldg(row_ptr + d), end = __ldg(row_ptr + d + 1);
+  if (!row_is_split(start, end)) return;
+  const float s = sum[d * H + l / hw];
+  const float inv = s > 0.f ? 1.f / s : 0.f;
+  float4 v = *reinterpret_cast<const float4 *>(ret + d * D + 4 * l);
+  st4(ret + d * D + 4 * l, make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv));
+}
+
+template <int LPR, int MODE>
+__global__ void __launch_bounds__(kThreads)
+    chunk_aggregate_kernel(const int64_t *__restrict__ row_ptr,
+                           const int64_t *__restrict__ eids, int64_t num_rows,
+                           int64_t E, const float *__restrict__ feat,
+                           const float *__restrict__ wa,  // el | score
+                           const float *__restrict__ wb,  // er | unused
+                           float *__restrict__ sum, float *__restrict__ exp_out,
+                           float *__restrict__ ret, int H, int hw, float slope,
+                           int divide) {
+  constexpr int GROUPS = kThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
-  if (threadIdx.x == 0) heavy_n = 0;
-  __syncthreads();
+  const int64_t p0 = ((int64_t)blockIdx.x * GROUPS + g) * kChunk;
+  if (p0 >= E) return;
+  const int64_t p1 = (p0 + kChunk < E) ? p0 + kChunk : E;
 
-  const int64_t d = (int64_t)blockIdx.x * GROUPS + g;
-  int64_t start = 0, end = 0;
-  if (d < num_rows) {
-    start = __ldg(row_ptr + d);
-    end = __ldg(row_ptr + d + 1);
+  // row containing p0: largest d with row_ptr[d] <= p0 (skips empty rows)
+  int64_t lo = 0, hi = num_rows;
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (__ldg(row_ptr + mid) <= p0) lo = mid; else hi = mid;
   }
-  const bool heavy = (end - start) > kHeavyDegree;
-  if (heavy) {
-    if (l == 0) heavy_row[atomicAdd(&heavy_n, 1)] = d;
-  } else if (d < num_rows) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    float s = 0.f;
-    int64_t p = start;
-    for (; p + 4 <= end; p += 4) {
+  int64_t d = lo;
+  int64_t row_start = __ldg(row_ptr + d), row_end = __ldg(row_ptr + d + 1);
+  float inv_d = 1.f;
+  if (MODE == 1 && divide) {
+    const float sd = __ldg(sum + d * H + h);
+    inv_d = sd != 0.f ? 1.f / sd : 0.f;
+  }
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float s = 0.f;
+
+  auto flush = [&]() {
+    const bool complete = row_start >= p0 && row_end <= p1;
+    if (MODE == 0) {
+      if (complete) {
+        const float inv = s > 0.f ? 1.f / s : 0.f;
+        if (leader) sum[d * H + h] = s;
+        st4(ret + d * D + 4 * l, make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv));
+      } else {
+        if (leader) atomicAdd(sum + d * H + h, s);
+        red_add4(ret + d * D + 4 * l, acc);
+      }
+    } else {
+      if (complete) st4(ret + d * D + 4 * l, acc);
+      else red_add4(ret + d * D + 4 * l, acc);
+    }
+  };
+
+  int64_t p = p0;
+  while (p < p1) {
+    if (p == row_end) {
+      flush();
+      ++d;
+      while (__ldg(row_ptr + d + 1) == p) ++d;  // empty rows
+      row_start = p;
+      row_end = __ldg(row_ptr + d + 1);
+      acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      s = 0.f;
+      if (MODE == 1 && divide) {
+        const float sd = __ldg(sum + d * H + h);
+        inv_d = sd != 0.f ? 1.f / sd : 0.f;
+      }
+    }
+    const int64_t stop = row_end < p1 ? row_end : p1;
+    for (; p + 4 <= stop; p += 4) {
       int64_t e[4];
       float w[4];
       float4 v[4];
@@ -76,7 +160,7 @@ __global__ void __launch_bounds__(kThreads)
         if (MODE == 0)
           w[j] = __ldg(wa + e[j] * H + h) + __ldg(wb + e[j] * H + h);
         else
-          w[j] = __ldg(wa + e[j] * H + h);
+          w[j] = __ldg(wa + e[j] * H + h) * inv_d;
         v[j] = ldcs4(feat + e[j] * D + 4 * l);
       }
 #pragma unroll
@@ -89,153 +173,147 @@ __global__ void __launch_bounds__(kThreads)
         s += w[j];
       }
     }
-    for (; p < end; ++p) {
+    for (; p < stop; ++p) {
       const int64_t e = __ldg(eids + p);
       float w;
       if (MODE == 0) {
         w = leaky_exp(__ldg(wa + e * H + h) + __ldg(wb + e * H + h), slope);
         if (leader) exp_out[e * H + h] = w;
       } else {
-        w = __ldg(wa + e * H + h);
+        w = __ldg(wa + e * H + h) * inv_d;
       }
       fma4(acc, w, ldcs4(feat + e * D + 4 * l));
       s += w;
     }
-    float inv;
-    if (MODE == 0) {
-      inv = s > 0.f ? 1.f / s : 0.f;
-      if (leader) sum[d * H + h] = s;
-    } else {
-      float sd = divide ? __ldg(sum + d * H + h) : 1.f;
-      inv = divide ? (sd != 0.f ? 1.f / sd : 0.f) : 1.f;
-    }
-    st4(ret + d * D + 4 * l,
-        make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv));
   }
-  __syncthreads();
-
-  // Heavy rows: the CTA's GROUPS lane groups stride over the row's edges.
-  const int nh = heavy_n;
-  for (int q = 0; q < nh; ++q) {
-    const int64_t hd = heavy_row[q];
-    const int64_t hs = __ldg(row_ptr + hd), he = __ldg(row_ptr + hd + 1);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    float s = 0.f;
-    for (int64_t p = hs + g; p < he; p += GROUPS) {
-      const int64_t e = __ldg(eids + p);
-      float w;
-      if (MODE == 0) {
-        w = leaky_exp(__ldg(wa + e * H + h) + __ldg(wb + e * H + h), slope);
-        if (leader) exp_out[e * H + h] = w;
-      } else {
-        w = __ldg(wa + e * H + h);
-      }
-      fma4(acc, w, ldcs4(feat + e * D + 4 * l));
-      s += w;
-    }
-    red_acc[g][l] = acc;
-    red_sum[g][l] = s;
-    __syncthreads();
-    for (int stride = GROUPS / 2; stride > 0; stride >>= 1) {
-      if (g < stride) {
-        float4 a = red_acc[g][l], b = red_acc[g + stride][l];
-        red_acc[g][l] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-        red_sum[g][l] += red_sum[g + stride][l];
-      }
-      __syncthreads();
-    }
-    if (g == 0) {
-      float4 a = red_acc[0][l];
-      float st = red_sum[0][l];
-      float inv;
-      if (MODE == 0) {
-        inv = st > 0.f ? 1.f / st : 0.f;
-        if (leader) sum[hd * H + h] = st;
-      } else {
-        float sd = divide ? __ldg(sum + hd * H + h) : 1.f;
-        inv = divide ? (sd != 0.f ? 1.f / sd : 0.f) : 1.f;
-      }
-      st4(ret + hd * D + 4 * l,
-          make_float4(a.x * inv, a.y * inv, a.z * inv, a.w * inv));
-    }
-    __syncthreads();
-  }
+  flush();
 }
 
 // ---------------------------------------------------------------------------
-// HGT edge softmax over an in-CSR: one thread per (destination, head).
+// HGT edge softmax over an in-CSR, edge-balanced: one lane per CSR position
+// (coalesced eids / rel loads), all H heads in that lane. The destination of a
+// position is found by binary search over row_ptr (the upper levels stay in
+// L1); sums of positions that share a destination are combined with a
+// segmented warp scan, so a row inside one warp's 32 positions is stored once
+// and a row spanning warps is accumulated atomically into its pre-zeroed sum.
+//   pass 1: t = exp(attn·mu[rel]);  sum[d] = Σ t        pass 2: norm = t / sum[d]
 // ---------------------------------------------------------------------------
+constexpr int kMaxHeads = 8;
+
+template <int HH>
+__device__ __forceinline__ void load_heads(const float *__restrict__ p, float *out) {
+  if constexpr (HH % 4 == 0) {
+#pragma unroll
+    for (int q = 0; q < HH / 4; ++q) {
+      const float4 v = __ldg(reinterpret_cast<const float4 *>(p) + q);
+      out[4 * q] = v.x; out[4 * q + 1] = v.y; out[4 * q + 2] = v.z; out[4 * q + 3] = v.w;
+    }
+  } else {
+#pragma unroll
+    for (int h = 0; h < HH; ++h) out[h] = __ldg(p + h);
+  }
+}
+template <int HH>
+__device__ __forceinline__ void store_heads(float *__restrict__ p, const float *v) {
+  if constexpr (HH % 4 == 0) {
+#pragma unroll
+    for (int q = 0; q < HH / 4; ++q)
+      reinterpret_cast<float4 *>(p)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int h = 0; h < HH; ++h) p[h] = v[h];
+  }
+}
+
+__device__ __forceinline__ int64_t row_of_position(const int64_t *__restrict__ row_ptr,
+                                                   int64_t num_rows, int64_t p) {
+  int64_t lo = 0, hi = num_rows;
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (__ldg(row_ptr + mid) <= p) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
 __global__ void __launch_bounds__(kThreads)
-    hgt_softmax_fwd_kernel(const int64_t *__restrict__ row_ptr,
+    zero_f32_kernel(float *__restrict__ p, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) p[i] = 0.f;
+}
+
+template <int HH>
+__global__ void __launch_bounds__(kThreads)
+    hgt_softmax_sum_kernel(const int64_t *__restrict__ row_ptr,
                            const int64_t *__restrict__ eids,
                            const int64_t *__restrict__ rel, int64_t num_rows,
-                           const float *__restrict__ attn,
-                           const float *__restrict__ mu,
-                           float *__restrict__ sum, float *__restrict__ t_out,
-                           float *__restrict__ norm_out, int H) {
-  // rows_per_cta = kThreads / H (H is a power of two <= 32, checked on host)
-  __shared__ int64_t heavy_row[kThreads];
-  __shared__ int heavy_n;
-  __shared__ float red[kThreads];
-  const int rows_per_cta = kThreads / H;
-  const int g = threadIdx.x / H;
-  const int h = threadIdx.x % H;
-  if (threadIdx.x == 0) heavy_n = 0;
-  __syncthreads();
-  const int64_t d = (int64_t)blockIdx.x * rows_per_cta + g;
-  int64_t start = 0, end = 0;
-  if (d < num_rows) {
-    start = __ldg(row_ptr + d);
-    end = __ldg(row_ptr + d + 1);
+                           int64_t E, const float *__restrict__ attn,
+                           const float *__restrict__ mu, float *__restrict__ sum,
+                           float *__restrict__ t_out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  const int64_t warp_p0 = p - lane;
+  if (warp_p0 >= E) return;  // whole warp out of range
+  const bool ok = p < E;
+  int64_t d = -1 - (int64_t)lane;  // unique sentinel per idle lane
+  float t[HH];
+#pragma unroll
+  for (int h = 0; h < HH; ++h) t[h] = 0.f;
+  if (ok) {
+    d = row_of_position(row_ptr, num_rows, p);
+    const int64_t e = __ldg(eids + p);
+    const int64_t r = __ldg(rel + p);
+    float a[HH], m[HH];
+    load_heads<HH>(attn + e * HH, a);
+    load_heads<HH>(mu + r * HH, m);
+#pragma unroll
+    for (int h = 0; h < HH; ++h) t[h] = __expf(a[h] * m[h]);
+    if (t_out) store_heads<HH>(t_out + e * HH, t);
   }
-  if (end - start > kHeavyDegree) {
-    if (h == 0) heavy_row[atomicAdd(&heavy_n, 1)] = d;
-  } else if (d < num_rows) {
-    float s = 0.f;
-    for (int64_t p = start; p < end; ++p) {
-      const int64_t e = __ldg(eids + p);
-      const int64_t r = __ldg(rel + p);
-      s += __expf(__ldg(attn + e * H + h) * __ldg(mu + r * H + h));
-    }
-    sum[d * H + h] = s;
-    const float inv = s > 0.f ? 1.f / s : 0.f;
-    for (int64_t p = start; p < end; ++p) {
-      const int64_t e = __ldg(eids + p);
-      const int64_t r = __ldg(rel + p);
-      const float t = __expf(__ldg(attn + e * H + h) * __ldg(mu + r * H + h));
-      if (t_out) t_out[e * H + h] = t;
-      if (norm_out) norm_out[e * H + h] = t * inv;
+  // segmented inclusive scan keyed on d (positions ascend, so equal d are adjacent)
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int64_t dn = __shfl_up_sync(0xffffffffu, d, off);
+#pragma unroll
+    for (int h = 0; h < HH; ++h) {
+      const float vn = __shfl_up_sync(0xffffffffu, t[h], off);
+      if (lane >= off && dn == d) t[h] += vn;
     }
   }
-  __syncthreads();
-  const int nh = heavy_n;
-  for (int q = 0; q < nh; ++q) {
-    const int64_t hd = heavy_row[q];
-    const int64_t hs = __ldg(row_ptr + hd), he = __ldg(row_ptr + hd + 1);
-    float s = 0.f;
-    for (int64_t p = hs + g; p < he; p += rows_per_cta) {
-      const int64_t e = __ldg(eids + p);
-      const int64_t r = __ldg(rel + p);
-      s += __expf(__ldg(attn + e * H + h) * __ldg(mu + r * H + h));
+  const int64_t d_next = __shfl_down_sync(0xffffffffu, d, 1);
+  if (ok && (lane == 31 || d_next != d)) {  // tail of a run holds its total
+    const int64_t start = __ldg(row_ptr + d), end = __ldg(row_ptr + d + 1);
+    const int64_t warp_p1 = warp_p0 + 32;
+    if (start >= warp_p0 && end <= warp_p1) {
+#pragma unroll
+      for (int h = 0; h < HH; ++h) sum[d * HH + h] = t[h];
+    } else {
+#pragma unroll
+      for (int h = 0; h < HH; ++h) atomicAdd(sum + d * HH + h, t[h]);
     }
-    red[threadIdx.x] = s;
-    __syncthreads();
-    for (int stride = rows_per_cta / 2; stride > 0; stride >>= 1) {
-      if (g < stride) red[threadIdx.x] += red[threadIdx.x + stride * H];
-      __syncthreads();
-    }
-    const float st = red[h];
-    if (g == 0) sum[hd * H + h] = st;
-    const float inv = st > 0.f ? 1.f / st : 0.f;
-    for (int64_t p = hs + g; p < he; p += rows_per_cta) {
-      const int64_t e = __ldg(eids + p);
-      const int64_t r = __ldg(rel + p);
-      const float t = __expf(__ldg(attn + e * H + h) * __ldg(mu + r * H + h));
-      if (t_out) t_out[e * H + h] = t;
-      if (norm_out) norm_out[e * H + h] = t * inv;
-    }
-    __syncthreads();
   }
+}
+
+template <int HH>
+__global__ void __launch_bounds__(kThreads)
+    hgt_softmax_norm_kernel(const int64_t *__restrict__ row_ptr,
+                            const int64_t *__restrict__ eids,
+                            const int64_t *__restrict__ rel, int64_t num_rows,
+                            int64_t E, const float *__restrict__ attn,
+                            const float *__restrict__ mu,
+                            const float *__restrict__ sum,
+                            float *__restrict__ norm_out) {
+  const int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  if (p >= E) return;
+  const int64_t d = row_of_position(row_ptr, num_rows, p);
+  const int64_t e = __ldg(eids + p);
+  const int64_t r = __ldg(rel + p);
+  float a[HH], m[HH], sd[HH], o[HH];
+  load_heads<HH>(attn + e * HH, a);
+  load_heads<HH>(mu + r * HH, m);
+  load_heads<HH>(sum + d * HH, sd);
+#pragma unroll
+  for (int h = 0; h < HH; ++h) o[h] = sd[h] > 0.f ? __expf(a[h] * m[h]) / sd[h] : 0.f;
+  store_heads<HH>(norm_out + e * HH, o);
 }
 
 // ---------------------------------------------------------------------------
@@ -529,10 +607,18 @@ extern "C" int hetb_rgat_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
   if (!lpr) return HETB_EUNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   const int groups = kThreads / lpr;
-  const int64_t grid = ceil_div64(num_rows, groups);
-  DISPATCH_LPR(lpr, (dst_aggregate_kernel<L, 0><<<(unsigned)grid, kThreads, 0, st>>>(
-                        row_ptr, eids, num_rows, feat, el, er, sum, exp_out,
-                        ret, H, F / 4, slope, 0)));
+  const int64_t row_grid = ceil_div64(num_rows, groups);
+  DISPATCH_LPR(lpr, (agg_prepare_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
+                        row_ptr, num_rows, sum, ret, H, F / 4, 1)));
+  HETB_LAUNCH_OK();
+  if (num_edges == 0) return HETB_OK;
+  const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
+  DISPATCH_LPR(lpr, (chunk_aggregate_kernel<L, 0><<<(unsigned)grid, kThreads, 0, st>>>(
+                        row_ptr, eids, num_rows, num_edges, feat, el, er, sum,
+                        exp_out, ret, H, F / 4, slope, 0)));
+  HETB_LAUNCH_OK();
+  DISPATCH_LPR(lpr, (agg_normalize_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
+                        row_ptr, num_rows, sum, ret, H, F / 4)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -551,9 +637,14 @@ extern "C" int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr,
   if (!lpr) return HETB_EUNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   const int groups = kThreads / lpr;
-  const int64_t grid = ceil_div64(num_rows, groups);
-  DISPATCH_LPR(lpr, (dst_aggregate_kernel<L, 1><<<(unsigned)grid, kThreads, 0, st>>>(
-                        row_ptr, eids, num_rows, msg, score, nullptr,
+  const int64_t row_grid = ceil_div64(num_rows, groups);
+  DISPATCH_LPR(lpr, (agg_prepare_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
+                        row_ptr, num_rows, nullptr, ret, H, F / 4, 0)));
+  HETB_LAUNCH_OK();
+  if (num_edges == 0) return HETB_OK;
+  const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
+  DISPATCH_LPR(lpr, (chunk_aggregate_kernel<L, 1><<<(unsigned)grid, kThreads, 0, st>>>(
+                        row_ptr, eids, num_rows, num_edges, msg, score, nullptr,
                         const_cast<float *>(sum), nullptr, ret, H, F / 4, 0.f,
                         divide_by_sum)));
   HETB_LAUNCH_OK();
@@ -568,12 +659,33 @@ extern "C" int hetb_hgt_edge_softmax_fwd_csr(
   if (num_rows == 0) return HETB_OK;
   HETB_CHECK_ARG(row_ptr && sum);
   HETB_CHECK_ARG(num_edges == 0 || (eids && rel && attn && mu));
-  if (!is_pow2(H) || H > 32) return HETB_EUNSUPPORTED;
+  if (!is_pow2(H) || H > kMaxHeads) return HETB_EUNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
-  const int64_t grid = ceil_div64(num_rows, kThreads / H);
-  hgt_softmax_fwd_kernel<<<(unsigned)grid, kThreads, 0, st>>>(
-      row_ptr, eids, rel, num_rows, attn, mu, sum, t_out, norm_out, H);
-  HETB_LAUNCH_OK();
+  {
+    const int64_t n = num_rows * H;
+    const int64_t need = ceil_div64(n, kThreads);
+    const int zg = (int)(need < kNumSMs * 16 ? need : kNumSMs * 16);
+    zero_f32_kernel<<<zg, kThreads, 0, st>>>(sum, n);
+    HETB_LAUNCH_OK();
+  }
+  if (num_edges == 0) return HETB_OK;
+  const int64_t grid = ceil_div64(num_edges, kThreads);
+#define HGT_SM(HV)                                                             \
+  case HV:                                                                     \
+    hgt_softmax_sum_kernel<HV><<<(unsigned)grid, kThreads, 0, st>>>(           \
+        row_ptr, eids, rel, num_rows, num_edges, attn, mu, sum, t_out);        \
+    HETB_LAUNCH_OK();                                                          \
+    if (norm_out) {                                                            \
+      hgt_softmax_norm_kernel<HV><<<(unsigned)grid, kThreads, 0, st>>>(        \
+          row_ptr, eids, rel, num_rows, num_edges, attn, mu, sum, norm_out);   \
+      HETB_LAUNCH_OK();                                                        \
+    }                                                                          \
+    break;
+  switch (H) {
+    HGT_SM(1) HGT_SM(2) HGT_SM(4) HGT_SM(8)
+    default: return HETB_EUNSUPPORTED;
+  }
+#undef HGT_SM
   return HETB_OK;
 }
 
