@@ -389,6 +389,19 @@ static int pick_lpr(int d) {
 
 using namespace hetb;
 
+// defined in segment_mm_tc.cu (tcgen05 path)
+int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
+                       const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
+                       int64_t num_rows, int H, int K, int N, int accumulate, void *stream);
+
+static int g_segmm_impl = 0;  // 0 auto, 1 SIMT only, 2 tensor core only
+
+extern "C" int hetb_set_segment_mm_impl(int impl) {
+  if (impl < 0 || impl > 2) return HETB_EINVAL;
+  g_segmm_impl = impl;
+  return HETB_OK;
+}
+
 extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
                                int a_heads, const float *W, float *Y,
                                const int64_t *c_idx, int c_heads,
@@ -404,6 +417,17 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
   cudaStream_t st = (cudaStream_t)stream;
   const int S = (int)num_segs;
   const int C = H * N;
+
+  // Tensor-core path (tcgen05/TMEM, 3xTF32): 64-wide contraction and output, segments of
+  // useful size (a tile pays one pass per segment piece it straddles).
+  if (g_segmm_impl != 1) {
+    const bool worth = num_rows >= 4096 && num_rows / num_segs >= 16;
+    if (g_segmm_impl == 2 || worth) {
+      const int rc = hetb_segment_mm_tc(A, a_idx, a_heads, W, Y, c_idx, c_heads, seg_ptrs, num_segs,
+                                        num_rows, H, K, N, accumulate, stream);
+      if (rc != HETB_EUNSUPPORTED || g_segmm_impl == 2) return rc;
+    }
+  }
 
   // N == 1 with per-head input: row-dot fast path.
   if (N == 1 && a_heads == H && c_heads == H && is_pow2(H) && is_pow2(K) &&

@@ -1,0 +1,421 @@
+// Grouped segment MM on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
+//
+//   Y[c_idx?[i], :] (=|+=) A[a_idx?[i], :] · B_s        for rows i of segment s
+//
+// with a 64-wide contraction and a 64-wide output (hidden 64, every BASELINE.json
+// config), fp32 in / fp32 out. B_s is the [64 x 64] matrix the (heads, K, N) weight
+// W[s] denotes: dense when the input has one head, block-diagonal per head when input
+// and output are both per-head (HGT's 4 x (16 x 16)), or the stacked [H*K, N] matrix
+// when the heads are summed into one output row (delta-input of RGAT).
+//
+// Precision: the tensor core has no fp32 MMA. Each operand is split in registers
+// into a tf32 "hi" part (low 13 mantissa bits cleared) and the exact remainder
+// "lo", and D = A_lo·B_hi + A_hi·B_lo + A_hi·B_hi is accumulated in fp32 in TMEM
+// (3xTF32): relative error ~2^-21, inside the 1e-4 parity bar. The kernel is HBM
+// bound (16 FLOP/B), so the 3x MMA count costs nothing.
+//
+// Structure (persistent, one CTA per SM, warp specialised, 416 threads):
+//   warps 0-3   epilogue : tcgen05.ld the 128x64 accumulator, stage through
+//                          swizzled shared memory, 128-bit coalesced row stores
+//                          (scatter through c_idx, or vector reductions)
+//   warp  4     MMA      : one elected lane issues 24 tcgen05.mma.kind::tf32
+//                          (M128 N64 K8) per work item, commits to mbarriers
+//   warps 5-12  producers: gather A rows with 128-bit loads (16 lanes per 256 B
+//                          row), split hi/lo, store into the 128B-swizzled K-major
+//                          layout the UMMA descriptors expect; stage B_s transposed
+// Two shared-memory stages (A_hi, A_lo, B_hi, B_lo = 96 KB each) and two TMEM
+// accumulator stages (64 columns each) let the gather of item i+1, the MMAs of item
+// i and the stores of item i-1 overlap. Gathered rows cannot be fetched as TMA
+// tiles (every row has its own address), hence the register path for A; the B
+// operand is 16 KB and is re-staged only when the segment changes.
+//
+// Work items: the row space is cut into 128-row tiles on a GLOBAL grid; a tile
+// that straddles segment boundaries yields one item per segment piece (the full
+// tile is multiplied, only that piece's rows are stored). No host schedule, no
+// device->host copy of the segment offsets, no allocation (the reference needs all
+// three per call: OpExport/RGNNOps.inc.h:150-169).
+#include "common.cuh"
+
+namespace hetb {
+namespace tc {
+
+constexpr int TM = 128;  // rows per tile (UMMA M)
+constexpr int KK = 64;   // contraction width
+constexpr int NN = 64;   // output width (UMMA N)
+constexpr int kEpiWarps = 4;
+constexpr int kProdWarps = 8;
+constexpr int kProdThreads = kProdWarps * 32;
+constexpr int kThreads = (kEpiWarps + 1 + kProdWarps) * 32;  // 416
+constexpr int kStages = 2;
+
+constexpr uint32_t kPanelA = TM * 128;            // one 32-float K panel of A: 16 KB
+constexpr uint32_t kPanelB = NN * 128;            // 8 KB
+constexpr uint32_t kBytesA = 2 * kPanelA;         // 32 KB (hi or lo)
+constexpr uint32_t kBytesB = 2 * kPanelB;         // 16 KB
+constexpr uint32_t kStageBytes = 2 * kBytesA + 2 * kBytesB;  // 96 KB
+constexpr uint32_t kOffAlo = kBytesA, kOffBhi = 2 * kBytesA, kOffBlo = 2 * kBytesA + kBytesB;
+constexpr uint32_t kEpiBytes = TM * NN * 4;       // 32 KB
+constexpr uint32_t kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+// B_s index maps (see header)
+enum BMode : int { kDense = 0, kBlockDiag = 1, kStacked = 2 };
+
+// ------------------------------------------------------------------ PTX ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded spin: a protocol bug traps (a launch error the caller sees) instead of
+// hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > (1u << 26)) __trap();
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// tcgen05.commit: the mbarrier gets one arrival when every MMA issued so far by
+// this thread has completed (implies tcgen05.fence::before_thread_sync).
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread t of the warp gets row (lane base + t).
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t *v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor, K-major, 128-byte swizzle (cute::UMMA::SmemDescriptor:
+// start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout=SWIZZLE_128B(2) [61,64)).
+// Rows are 128 B apart, 8-row swizzle atoms 1024 B apart (SBO); LBO is unused for swizzled K-major.
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3ffff) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6)=1, A=tf32 [7,10)=2, B=tf32 [10,13)=2,
+// A,B K-major (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29).
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+// byte offset of element (row, k) inside an operand buffer of `rows` rows (K-major, SW128, 2 panels)
+__device__ __forceinline__ uint32_t sw128_off(int rows, int row, int k) {
+  const int panel = k >> 5, kc = (k & 31) >> 2;
+  return (uint32_t)(panel * rows * 128 + row * 128 + (((kc ^ (row & 7)) << 4) | ((k & 3) << 2)));
+}
+
+__device__ __forceinline__ float tf32_hi(float x) {
+  return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+
+// ------------------------------------------------------------ work items ----
+// Every role walks the same deterministic sequence of (tile, segment piece) items.
+struct PieceIter {
+  const int64_t *__restrict__ seg_ptrs;
+  int num_segs;
+  int64_t M, row, row_stop;  // rows [row, row_stop) remain for this CTA
+  int s;
+
+  __device__ PieceIter(const int64_t *sp, int ns, int64_t m, int64_t tile_begin, int64_t tile_end)
+      : seg_ptrs(sp), num_segs(ns), M(m) {
+    row = tile_begin * TM;
+    row_stop = tile_end * TM < m ? tile_end * TM : m;
+    s = 0;
+    if (row < row_stop) {
+      s = segment_of(seg_ptrs, num_segs, row);
+      while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
+    }
+  }
+  // next piece: rows [p0, p1) of tile starting at tile_row0, segment seg
+  __device__ bool next(int64_t &tile_row0, int64_t &p0, int64_t &p1, int &seg) {
+    if (row >= row_stop) return false;
+    tile_row0 = (row / TM) * TM;
+    int64_t tile_end = tile_row0 + TM;
+    if (tile_end > M) tile_end = M;
+    const int64_t seg_end = (s + 1 < num_segs) ? __ldg(seg_ptrs + s + 1) : M;
+    p0 = row;
+    p1 = seg_end < tile_end ? seg_end : tile_end;
+    seg = s;
+    row = p1;
+    if (row == seg_end && row < row_stop) {
+      ++s;
+      while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
+    }
+    return true;
+  }
+};
+
+// --------------------------------------------------------------- kernel ----
+__global__ void __launch_bounds__(kThreads, 1)
+    segmm_tc_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx,
+                    const float *__restrict__ W, float *__restrict__ Y,
+                    const int64_t *__restrict__ c_idx, const int64_t *__restrict__ seg_ptrs, int num_segs,
+                    int64_t M, int H, int K, int N, int bmode, int accumulate) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SW128 atoms need 1024 B alignment
+  uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t epi_base = base + kStages * kStageBytes;
+  const uint32_t bar_base = epi_base + kEpiBytes;
+  // barriers: full[2], empty[2], tmem_full[2], tmem_empty[2], then the TMEM base address
+  auto full_bar = [&](int i) { return bar_base + 8u * i; };
+  auto empty_bar = [&](int i) { return bar_base + 16u + 8u * i; };
+  auto tfull_bar = [&](int i) { return bar_base + 32u + 8u * i; };
+  auto tempty_bar = [&](int i) { return bar_base + 48u + 8u * i; };
+  const uint32_t tmem_slot = bar_base + 64u;
+  volatile uint32_t *tmem_slot_g = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == kEpiWarps) {
+    if (lane == 0) {
+      for (int i = 0; i < kStages; ++i) {
+        mbar_init(full_bar(i), kProdThreads);
+        mbar_init(empty_bar(i), 1);
+        mbar_init(tfull_bar(i), 1);
+        mbar_init(tempty_bar(i), kEpiWarps * 32);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 2 * NN);  // two 64-column accumulator stages
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_g;
+
+  const int64_t num_tiles = ceil_div64(M, TM);
+  const int64_t tile_begin = num_tiles * blockIdx.x / gridDim.x;
+  const int64_t tile_end = num_tiles * (blockIdx.x + 1) / gridDim.x;
+  PieceIter it(seg_ptrs, num_segs, M, tile_begin, tile_end);
+  int64_t tile_row0, p0, p1;
+  int seg;
+
+  if (warp > kEpiWarps) {
+    // ===================== producers =====================
+    const int p = threadIdx.x - (kEpiWarps + 1) * 32;  // 0..255
+    const int chunk = p & 15;                          // 16-byte chunk of the 256 B row
+    const int panel = chunk >> 3, kc = chunk & 7;
+    const int r_in = p >> 4;                           // rows r_in + 16*i
+    int stage_seg[kStages] = {-1, -1};
+    uint32_t n = 0;
+    while (it.next(tile_row0, p0, p1, seg)) {
+      const int stage = n & 1;
+      const uint32_t phase = (n >> 1) & 1;
+      mbar_wait(empty_bar(stage), phase ^ 1);
+      const uint32_t sbase = base + stage * kStageBytes;
+      uint8_t *gs = gbase + stage * kStageBytes;
+      // ---- A rows: gather, split, store swizzled ----
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = r_in + 16 * i;
+        const int64_t gr = tile_row0 + r;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gr < M) {
+          const int64_t ar = a_idx ? __ldg(a_idx + gr) : gr;
+          v[i] = ldg4(A + ar * KK + chunk * 4);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = r_in + 16 * i;
+        const uint32_t off = (uint32_t)(panel * kPanelA + r * 128 + ((kc ^ (r & 7)) << 4));
+        const float4 hi = make_float4(tf32_hi(v[i].x), tf32_hi(v[i].y), tf32_hi(v[i].z), tf32_hi(v[i].w));
+        const float4 lo = make_float4(v[i].x - hi.x, v[i].y - hi.y, v[i].z - hi.z, v[i].w - hi.w);
+        *reinterpret_cast<float4 *>(gs + off) = hi;
+        *reinterpret_cast<float4 *>(gs + kOffAlo + off) = lo;
+      }
+      // ---- B_s: transposed ([n][k], K-major), only when this stage holds another segment ----
+      if (stage_seg[stage] != seg) {
+        stage_seg[stage] = seg;
+        const float *Ws = W + (int64_t)seg * H * K * N;
+        for (int e = p; e < KK * NN; e += kProdThreads) {
+          const int kk = e / NN, nn = e % NN;  // consecutive threads -> consecutive nn (coalesced reads)
+          float w;
+          if (bmode == kDense)            // W[s][nn/N][kk][nn%N]
+            w = __ldg(Ws + ((int64_t)(nn / N) * K + kk) * N + (nn % N));
+          else if (bmode == kBlockDiag)   // W[s][h][kk%K][nn%N] on the diagonal blocks
+            w = (kk / K == nn / N) ? __ldg(Ws + ((int64_t)(kk / K) * K + (kk % K)) * N + (nn % N)) : 0.f;
+          else                            // W[s][kk/K][kk%K][nn]
+            w = __ldg(Ws + (int64_t)kk * N + nn);
+          const float hi = tf32_hi(w);
+          const uint32_t off = sw128_off(NN, nn, kk);
+          *reinterpret_cast<float *>(gs + kOffBhi + off) = hi;
+          *reinterpret_cast<float *>(gs + kOffBlo + off) = w - hi;
+        }
+      }
+      (void)sbase;
+      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+      mbar_arrive(full_bar(stage));
+      ++n;
+    }
+  } else if (warp == kEpiWarps) {
+    // ===================== MMA issuer =====================
+    uint32_t n = 0;
+    while (it.next(tile_row0, p0, p1, seg)) {
+      const int stage = n & 1;
+      const uint32_t phase = (n >> 1) & 1;
+      mbar_wait(tempty_bar(stage), phase ^ 1);  // accumulator stage drained by the epilogue
+      mbar_wait(full_bar(stage), phase);        // operands landed
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sbase = base + stage * kStageBytes;
+        const uint32_t d = tmem_base + (uint32_t)(stage * NN);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int j = 0; j < KK / 8; ++j) {
+          const uint32_t ka = (uint32_t)((j >> 2) * kPanelA + (j & 3) * 32);
+          const uint32_t kb = (uint32_t)((j >> 2) * kPanelB + (j & 3) * 32);
+          const uint64_t a_hi = make_desc_sw128(sbase + ka), a_lo = make_desc_sw128(sbase + kOffAlo + ka);
+          const uint64_t b_hi = make_desc_sw128(sbase + kOffBhi + kb), b_lo = make_desc_sw128(sbase + kOffBlo + kb);
+          umma_tf32(d, a_lo, b_hi, kIdesc, acc);
+          umma_tf32(d, a_hi, b_lo, kIdesc, 1);
+          umma_tf32(d, a_hi, b_hi, kIdesc, 1);
+          acc = 1;
+        }
+        umma_commit(empty_bar(stage));  // operands may be overwritten once these MMAs retire
+        umma_commit(tfull_bar(stage));  // accumulator ready for the epilogue
+      }
+      __syncwarp();
+      ++n;
+    }
+  } else {
+    // ===================== epilogue =====================
+    uint8_t *stg = gbase + kStages * kStageBytes + warp * (32 * NN * 4);  // this warp's 32 rows x 256 B
+    uint32_t n = 0;
+    while (it.next(tile_row0, p0, p1, seg)) {
+      const int stage = n & 1;
+      const uint32_t phase = (n >> 1) & 1;
+      mbar_wait(tfull_bar(stage), phase);
+      tc_fence_after();
+      uint32_t v[64];
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(stage * NN);
+      tmem_ld32(taddr, v);
+      tmem_ld32(taddr + 32, v + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(tempty_bar(stage));  // TMEM stage free: the next MMA may start
+      // registers (thread = row) -> swizzled staging -> 16 lanes per row
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const int pc = (c & 8) | ((c & 7) ^ (lane & 7));
+        *reinterpret_cast<uint4 *>(stg + lane * 256 + pc * 16) = make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+      }
+      __syncwarp();
+      const int c = lane & 15;
+#pragma unroll 4
+      for (int i = 0; i < 16; ++i) {
+        const int lr = i * 2 + (lane >> 4);  // row within this warp's 32
+        const int64_t gr = tile_row0 + warp * 32 + lr;
+        if (gr >= p0 && gr < p1) {
+          const int pc = (c & 8) | ((c & 7) ^ (lr & 7));
+          const float4 val = *reinterpret_cast<const float4 *>(stg + lr * 256 + pc * 16);
+          const int64_t cr = c_idx ? __ldg(c_idx + gr) : gr;
+          float *dst = Y + cr * NN + c * 4;
+          if (accumulate) red_add4(dst, val);
+          else st4(dst, val);
+        }
+      }
+      __syncwarp();
+      ++n;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kEpiWarps) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * NN);
+  }
+}
+
+}  // namespace tc
+}  // namespace hetb
+
+using namespace hetb;
+
+// Returns HETB_EUNSUPPORTED when the shape is outside the tensor-core path; the caller
+// (hetb_segment_mm) then uses the SIMT kernels.
+int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
+                       const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
+                       int64_t num_rows, int H, int K, int N, int accumulate, void *stream) {
+  int bmode;
+  if (a_heads == H && c_heads == H && H * K == tc::KK && H * N == tc::NN)
+    bmode = (H == 1) ? tc::kDense : tc::kBlockDiag;
+  else if (a_heads == 1 && c_heads == H && K == tc::KK && H * N == tc::NN)
+    bmode = tc::kDense;
+  else if (a_heads == H && c_heads == 1 && accumulate && H * K == tc::KK && N == tc::NN)
+    bmode = tc::kStacked;
+  else
+    return HETB_EUNSUPPORTED;
+  if (num_segs > INT32_MAX) return HETB_EUNSUPPORTED;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t ce = cudaFuncSetAttribute(tc::segmm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)tc::kSmemBytes);
+    if (ce != cudaSuccess) return (int)ce;
+    attr_set = true;
+  }
+  const int64_t tiles = ceil_div64(num_rows, tc::TM);
+  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+  tc::segmm_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, (cudaStream_t)stream>>>(
+      A, a_idx, W, Y, c_idx, seg_ptrs, (int)num_segs, num_rows, H, K, N, bmode, accumulate);
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}

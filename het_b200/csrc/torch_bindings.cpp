@@ -612,9 +612,14 @@ std::vector<Tensor> hetb200_stable_sort_by_key(Tensor key, int64_t num_keys,
   return unstage(s, sort_by_key(s.dev[0], num_keys, pl, op));
 }
 
+void hetb200_set_segment_mm_impl(int64_t impl) {
+  check_rc(hetb_set_segment_mm_impl((int)impl), "hetb200_set_segment_mm_impl");
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
+  m.def("hetb200_set_segment_mm_impl", hetb200_set_segment_mm_impl);
   m.def("build_debug_info", build_debug_info);
   m.def("hetb200_launch_count", hetb200_launch_count);
   m.def("hetb200_stable_sort_by_key", hetb200_stable_sort_by_key);

@@ -66,6 +66,11 @@ int hetb_segment_mm(const float *A, const int64_t *a_idx, int a_heads,
                     int64_t num_rows, int H, int K, int N, int accumulate,
                     void *stream);
 
+/* Implementation switch for hetb_segment_mm (testing / A-B measurement): 0 = automatic
+ * (tcgen05 tensor-core kernel when the shape allows, else SIMT), 1 = SIMT kernels only,
+ * 2 = tensor-core kernel only (HETB_EUNSUPPORTED if the shape is outside it). */
+int hetb_set_segment_mm_impl(int impl);
+
 /* dW[s, h, :, :] += Σ_{i in segment s} A[a_idx?[i], (a_heads==1?0:h), :]^T
  *                                     · G[g_idx?[i], (g_heads==1?0:h), :]
  *   A : [*, a_heads, K]   G : [*, g_heads, N]   dW : [S, H, K, N] (caller

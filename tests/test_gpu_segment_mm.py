@@ -78,3 +78,76 @@ def test_ops_reject_cpu_tensors():
     with pytest.raises(RuntimeError, match="CUDA"):
         K.rgnn_relational_matmul_no_scatter_gather_list(offs, torch.zeros(1, 1, 4, 4), torch.zeros(4, 4),
                                                         torch.zeros(4, 4))
+
+
+# ---------------------------------------------------------------------------
+# tcgen05 tensor-core path (csrc/segment_mm_tc.cu), forced with impl=2 so that small
+# test sizes do not fall back to the SIMT kernels. Same fp32 tolerance (3xTF32 split).
+# ---------------------------------------------------------------------------
+TC_SHAPES = [
+    # (nodes, edges, relations, heads, K, N, input_num_head_one)
+    (300, 5000, 3, 1, 64, 64, True),      # dense 64x64, tiles straddle segments
+    (300, 4097, 40, 1, 64, 64, True),     # many small segments, ragged last tile
+    (200, 3000, 5, 4, 64, 16, True),      # RGAT multi-head: one input row, 4 heads out
+    (200, 3000, 8, 4, 16, 16, False),     # HGT per-head 16x16 -> block-diagonal B
+    (100, 130, 2, 2, 32, 32, False),      # two heads, barely more than one tile
+    (64, 7, 3, 1, 64, 64, True),          # fewer rows than a tile
+]
+
+
+@pytest.fixture
+def force_tc():
+    from het_b200.kernels import K
+    K.hetb200_set_segment_mm_impl(2)
+    yield
+    K.hetb200_set_segment_mm_impl(0)
+
+
+@pytest.mark.parametrize("n,e,r,H,Kd,Nd,head_one", TC_SHAPES)
+def test_tensor_core_segment_mm(cuda, force_tc, n, e, r, H, Kd, Nd, head_one):
+    from het_b200.kernels import K
+    g = build(cuda, n, e, r, seed=e + Kd + 1)
+    sc = g.get_separate_coo_original()
+    torch.manual_seed(Kd * Nd + e)
+    a_heads = 1 if head_one else H
+    W = torch.randn(r, H, Kd, Nd, device=cuda) / Kd ** 0.5
+    for gather_name in ("row_indices", "eids"):
+        gather = sc[gather_name]
+        rows_in = n if gather_name == "row_indices" else e
+        X = torch.randn(rows_in, a_heads, Kd, device=cuda)
+        args = {"separate_coo_rel_ptrs": sc["rel_ptrs"], "separate_coo_node_indices": gather,
+                "separate_coo_eids": sc["eids"]}
+        ret = torch.full((e, H, Nd), float("nan"), device=cuda)
+        K.rgnn_relational_matmul(args, 0, W, X, ret, head_one)
+        want = R.segment_mm(X.cpu(), gather.cpu(), W.cpu(), sc["eids"].cpu(), sc["rel_ptrs"].cpu(), e, a_heads)
+        close(ret, want, f"tc fwd/{gather_name}")
+        # delta-input half of the backward runs the same kernel (accumulating, stacked B)
+        gout = torch.randn(e, H, Nd, device=cuda)
+        gX, gW = torch.zeros_like(X), torch.zeros_like(W)
+        K.backward_rgnn_relational_matmul(args, 0, W.transpose(2, 3).contiguous(), X, gout, gX, gW, head_one)
+        gX_ref, gW_ref = R.segment_mm_bwd(X.cpu(), gather.cpu(), W.cpu(), sc["eids"].cpu(), sc["rel_ptrs"].cpu(),
+                                          gout.cpu(), a_heads)
+        close(gX, gX_ref, f"tc grad_input/{gather_name}")
+        close(gW, gW_ref, f"tc grad_weight/{gather_name}", rtol=2e-4, atol=2e-5)
+
+
+def test_tensor_core_matches_simt_bitwise_close(cuda):
+    """A/B: the tcgen05 kernel and the SIMT kernel agree to fp32 rounding on a graph big
+    enough for the automatic dispatch to pick the tensor-core path."""
+    from het_b200.kernels import K
+    g = build(cuda, 5000, 60000, 11, seed=5)
+    sc = g.get_separate_coo_original()
+    torch.manual_seed(3)
+    W = torch.randn(11, 1, 64, 64, device=cuda) / 8
+    X = torch.randn(5000, 1, 64, device=cuda)
+    args = {"separate_coo_rel_ptrs": sc["rel_ptrs"], "separate_coo_node_indices": sc["row_indices"],
+            "separate_coo_eids": sc["eids"]}
+    outs = []
+    for impl in (1, 2, 0):
+        K.hetb200_set_segment_mm_impl(impl)
+        ret = torch.full((60000, 1, 64), float("nan"), device=cuda)
+        K.rgnn_relational_matmul(args, 0, W, X, ret, True)
+        outs.append(ret)
+    K.hetb200_set_segment_mm_impl(0)
+    close(outs[1], outs[0], "tc vs simt", rtol=1e-5, atol=1e-6)
+    assert torch.equal(outs[2], outs[1]), "automatic dispatch should have used the tensor-core kernel"
