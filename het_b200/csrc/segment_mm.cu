@@ -392,12 +392,12 @@ using namespace hetb;
 // defined in segment_mm_tc.cu (tcgen05 path)
 int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
                        const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
-                       int64_t num_rows, int H, int K, int N, int accumulate, void *stream);
+                       int64_t num_rows, int H, int K, int N, int accumulate, int passes, void *stream);
 
-static int g_segmm_impl = 0;  // 0 auto, 1 SIMT only, 2 tensor core only
+static int g_segmm_impl = 0;  // 0 auto, 1 SIMT only, 2 tensor core only (3xTF32), 3 TC 1xTF32, 4 TC pipeline without MMAs (timing probe)
 
 extern "C" int hetb_set_segment_mm_impl(int impl) {
-  if (impl < 0 || impl > 2) return HETB_EINVAL;
+  if (impl < 0 || impl > 4096) return HETB_EINVAL;
   g_segmm_impl = impl;
   return HETB_OK;
 }
@@ -422,10 +422,12 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
   // useful size (a tile pays one pass per segment piece it straddles).
   if (g_segmm_impl != 1) {
     const bool worth = num_rows >= 4096 && num_rows / num_segs >= 16;
-    if (g_segmm_impl == 2 || worth) {
+    if (g_segmm_impl >= 2 || worth) {
+      // impl >= 16: timing probes, (impl >> 4) = probe mask << 4 | passes
+      const int passes = g_segmm_impl >= 16 ? (g_segmm_impl >> 4) : (g_segmm_impl == 3 ? 1 : (g_segmm_impl == 4 ? 0 : 3));
       const int rc = hetb_segment_mm_tc(A, a_idx, a_heads, W, Y, c_idx, c_heads, seg_ptrs, num_segs,
-                                        num_rows, H, K, N, accumulate, stream);
-      if (rc != HETB_EUNSUPPORTED || g_segmm_impl == 2) return rc;
+                                        num_rows, H, K, N, accumulate, passes, stream);
+      if (rc != HETB_EUNSUPPORTED || g_segmm_impl >= 2) return rc;
     }
   }
 

@@ -14,13 +14,13 @@
 // (3xTF32): relative error ~2^-21, inside the 1e-4 parity bar. The kernel is HBM
 // bound (16 FLOP/B), so the 3x MMA count costs nothing.
 //
-// Structure (persistent, one CTA per SM, warp specialised, 416 threads):
+// Structure (persistent, one CTA per SM, warp specialised, 672 threads):
 //   warps 0-3   epilogue : tcgen05.ld the 128x64 accumulator, stage through
 //                          swizzled shared memory, 128-bit coalesced row stores
 //                          (scatter through c_idx, or vector reductions)
 //   warp  4     MMA      : one elected lane issues 24 tcgen05.mma.kind::tf32
 //                          (M128 N64 K8) per work item, commits to mbarriers
-//   warps 5-12  producers: gather A rows with 128-bit loads (16 lanes per 256 B
+//   warps 5-20  producers: gather A rows with 128-bit loads (16 lanes per 256 B
 //                          row), split hi/lo, store into the 128B-swizzled K-major
 //                          layout the UMMA descriptors expect; stage B_s transposed
 // Two shared-memory stages (A_hi, A_lo, B_hi, B_lo = 96 KB each) and two TMEM
@@ -44,6 +44,7 @@ constexpr int KK = 64;   // contraction width
 constexpr int NN = 64;   // output width (UMMA N)
 constexpr int kEpiWarps = 4;
 constexpr int kProdWarps = 8;
+constexpr int kSets = 2;        // producer register sets (work items of row data in flight)
 constexpr int kProdThreads = kProdWarps * 32;
 constexpr int kThreads = (kEpiWarps + 1 + kProdWarps) * 32;  // 416
 constexpr int kStages = 2;
@@ -52,10 +53,14 @@ constexpr uint32_t kPanelA = TM * 128;            // one 32-float K panel of A: 
 constexpr uint32_t kPanelB = NN * 128;            // 8 KB
 constexpr uint32_t kBytesA = 2 * kPanelA;         // 32 KB (hi or lo)
 constexpr uint32_t kBytesB = 2 * kPanelB;         // 16 KB
-constexpr uint32_t kStageBytes = 2 * kBytesA + 2 * kBytesB;  // 96 KB
-constexpr uint32_t kOffAlo = kBytesA, kOffBhi = 2 * kBytesA, kOffBlo = 2 * kBytesA + kBytesB;
+constexpr uint32_t kStageBytes = 2 * kBytesA;     // A_hi + A_lo: 64 KB per stage
+constexpr uint32_t kOffAlo = kBytesA;
+constexpr uint32_t kBBufBytes = 2 * kBytesB;      // B_hi + B_lo: 32 KB per buffer, ring of 2
+constexpr uint32_t kOffBlo = kBytesB;
 constexpr uint32_t kEpiBytes = TM * NN * 4;       // 32 KB
-constexpr uint32_t kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t kOffB = kStages * kStageBytes;
+constexpr uint32_t kOffEpi = kOffB + 2 * kBBufBytes;
+constexpr uint32_t kSmemBytes = kOffEpi + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 // B_s index maps (see header)
 enum BMode : int { kDense = 0, kBlockDiag = 1, kStacked = 2 };
@@ -205,11 +210,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     segmm_tc_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx,
                     const float *__restrict__ W, float *__restrict__ Y,
                     const int64_t *__restrict__ c_idx, const int64_t *__restrict__ seg_ptrs, int num_segs,
-                    int64_t M, int H, int K, int N, int bmode, int accumulate) {
+                    int64_t M, int H, int K, int N, int bmode, int accumulate, int passes, int probe) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SW128 atoms need 1024 B alignment
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const uint32_t epi_base = base + kStages * kStageBytes;
+  const uint32_t epi_base = base + kOffEpi;
   const uint32_t bar_base = epi_base + kEpiBytes;
   // barriers: full[2], empty[2], tmem_full[2], tmem_empty[2], then the TMEM base address
   auto full_bar = [&](int i) { return bar_base + 8u * i; };
@@ -248,74 +253,132 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp > kEpiWarps) {
     // ===================== producers =====================
-    const int p = threadIdx.x - (kEpiWarps + 1) * 32;  // 0..255
+    // The gather is latency bound (random 256 B rows), so what matters is bytes in
+    // flight per SM. The producer threads keep kSets work items of row data in
+    // registers: right after item n has been split and stored, its register set is
+    // re-used for the row loads of item n+kSets, so every load has kSets pipeline steps
+    // to land; gather indices are fetched a further kSets items ahead. The loop is
+    // unrolled kSets ways so the sets rotate by name (a register copy of an in-flight
+    // load would stall on it).
+    const int p = threadIdx.x - (kEpiWarps + 1) * 32;
     const int chunk = p & 15;                          // 16-byte chunk of the 256 B row
     const int panel = chunk >> 3, kc = chunk & 7;
-    const int r_in = p >> 4;                           // rows r_in + 16*i
-    int stage_seg[kStages] = {-1, -1};
+    const int r_in = p >> 4;                           // rows r_in + kRowStep*i, i < RP
+    constexpr int kRowStep = kProdThreads / 16;
+    constexpr int RP = TM / kRowStep;                  // rows per thread
+    int cur_seg = -1, bsel = 1;
     uint32_t n = 0;
-    while (it.next(tile_row0, p0, p1, seg)) {
+    PieceIter it_ix = it;  // runs kSets..2*kSets items ahead of `it`
+
+    auto issue_idx = [&](int *ix) {
+      int64_t t0, a0, a1;
+      int sg;
+      const bool valid = it_ix.next(t0, a0, a1, sg);
+#pragma unroll
+      for (int i = 0; i < RP; ++i) {
+        const int64_t gr = t0 + r_in + kRowStep * i;
+        ix[i] = -1;
+        // a row index fits 31 bits: 2^31 rows of 256 B would be 550 GB
+        if (valid && gr < M) ix[i] = a_idx ? (int)__ldg(a_idx + gr) : (int)gr;
+      }
+    };
+    auto issue_rows = [&](const int *ix, float4 *v) {
+#pragma unroll
+      for (int i = 0; i < RP; ++i) {
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ix[i] >= 0 && !(probe & 2)) v[i] = ldg4(A + (int64_t)ix[i] * KK + chunk * 4);
+      }
+    };
+    // one pipeline step: split + store item n from rS, then re-use rS / ixS for the
+    // row loads of item n+kSets and the index loads of item n+2*kSets.
+    auto step = [&](float4 *rS, int *ixS) -> bool {
+      if (!it.next(tile_row0, p0, p1, seg)) return false;
       const int stage = n & 1;
       const uint32_t phase = (n >> 1) & 1;
       mbar_wait(empty_bar(stage), phase ^ 1);
-      const uint32_t sbase = base + stage * kStageBytes;
       uint8_t *gs = gbase + stage * kStageBytes;
-      // ---- A rows: gather, split, store swizzled ----
-      float4 v[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int r = r_in + 16 * i;
-        const int64_t gr = tile_row0 + r;
-        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gr < M) {
-          const int64_t ar = a_idx ? __ldg(a_idx + gr) : gr;
-          v[i] = ldg4(A + ar * KK + chunk * 4);
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int r = r_in + 16 * i;
+      for (int i = 0; i < RP; ++i) {
+        const int r = r_in + kRowStep * i;
         const uint32_t off = (uint32_t)(panel * kPanelA + r * 128 + ((kc ^ (r & 7)) << 4));
-        const float4 hi = make_float4(tf32_hi(v[i].x), tf32_hi(v[i].y), tf32_hi(v[i].z), tf32_hi(v[i].w));
-        const float4 lo = make_float4(v[i].x - hi.x, v[i].y - hi.y, v[i].z - hi.z, v[i].w - hi.w);
-        *reinterpret_cast<float4 *>(gs + off) = hi;
-        *reinterpret_cast<float4 *>(gs + kOffAlo + off) = lo;
-      }
-      // ---- B_s: transposed ([n][k], K-major), only when this stage holds another segment ----
-      if (stage_seg[stage] != seg) {
-        stage_seg[stage] = seg;
-        const float *Ws = W + (int64_t)seg * H * K * N;
-        for (int e = p; e < KK * NN; e += kProdThreads) {
-          const int kk = e / NN, nn = e % NN;  // consecutive threads -> consecutive nn (coalesced reads)
-          float w;
-          if (bmode == kDense)            // W[s][nn/N][kk][nn%N]
-            w = __ldg(Ws + ((int64_t)(nn / N) * K + kk) * N + (nn % N));
-          else if (bmode == kBlockDiag)   // W[s][h][kk%K][nn%N] on the diagonal blocks
-            w = (kk / K == nn / N) ? __ldg(Ws + ((int64_t)(kk / K) * K + (kk % K)) * N + (nn % N)) : 0.f;
-          else                            // W[s][kk/K][kk%K][nn]
-            w = __ldg(Ws + (int64_t)kk * N + nn);
-          const float hi = tf32_hi(w);
-          const uint32_t off = sw128_off(NN, nn, kk);
-          *reinterpret_cast<float *>(gs + kOffBhi + off) = hi;
-          *reinterpret_cast<float *>(gs + kOffBlo + off) = w - hi;
+        const float4 x = rS[i];
+        const float4 hi = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
+        const float4 lo = make_float4(x.x - hi.x, x.y - hi.y, x.z - hi.z, x.w - hi.w);
+        if (!(probe & 8)) {
+          *reinterpret_cast<float4 *>(gs + off) = hi;
+          *reinterpret_cast<float4 *>(gs + kOffAlo + off) = lo;
         }
       }
-      (void)sbase;
+      issue_rows(ixS, rS);  // item n + kSets (its indices arrived kSets steps ago)
+      issue_idx(ixS);       // item n + 2*kSets
+      // ---- B_s: transposed ([n][k], K-major) into the B ring, once per segment change.
+      // The buffer being replaced was last read by MMAs two segment runs back, which
+      // retired before empty[stage] completed (tcgen05.commit covers all earlier MMAs).
+      if (seg != cur_seg) {
+        cur_seg = seg;
+        bsel ^= 1;
+        uint8_t *gb = gbase + kOffB + bsel * kBBufBytes;
+        const float *Ws = W + (int64_t)seg * H * K * N;
+        for (int e = p; e < KK * NN / 4; e += kProdThreads) {
+          const int kk = e >> 4, nn = (e & 15) << 2;
+          float4 wv;
+          if (bmode == kStacked) {
+            wv = ldg4(Ws + (int64_t)kk * N + nn);
+          } else {
+            const int h = nn / N;
+            const bool live = (bmode == kDense) || (kk / K == h);
+            const int kr = (bmode == kDense) ? kk : kk % K;
+            wv = live ? ldg4(Ws + ((int64_t)h * K + kr) * N + (nn % N)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const float w4[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float hi = tf32_hi(w4[t]);
+            const uint32_t off = sw128_off(NN, nn + t, kk);
+            *reinterpret_cast<float *>(gb + off) = hi;
+            *reinterpret_cast<float *>(gb + kOffBlo + off) = w4[t] - hi;
+          }
+        }
+      }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       mbar_arrive(full_bar(stage));
       ++n;
+      return true;
+    };
+
+    static_assert(kSets == 2 || kSets == 3, "producer register sets");
+    int ix0[RP], ix1[RP], ix2[RP];
+    float4 r0[RP], r1[RP], r2[RP];
+    issue_idx(ix0);
+    issue_idx(ix1);
+    if (kSets == 3) issue_idx(ix2);
+    issue_rows(ix0, r0);
+    issue_idx(ix0);
+    issue_rows(ix1, r1);
+    issue_idx(ix1);
+    if (kSets == 3) {
+      issue_rows(ix2, r2);
+      issue_idx(ix2);
+    }
+    for (;;) {
+      if (!step(r0, ix0)) break;
+      if (!step(r1, ix1)) break;
+      if (kSets == 3 && !step(r2, ix2)) break;
     }
   } else if (warp == kEpiWarps) {
     // ===================== MMA issuer =====================
     uint32_t n = 0;
+    int cur_seg = -1, bsel = 1;
     while (it.next(tile_row0, p0, p1, seg)) {
       const int stage = n & 1;
       const uint32_t phase = (n >> 1) & 1;
+      if (seg != cur_seg) { cur_seg = seg; bsel ^= 1; }
       mbar_wait(tempty_bar(stage), phase ^ 1);  // accumulator stage drained by the epilogue
       mbar_wait(full_bar(stage), phase);        // operands landed
       tc_fence_after();
       if (lane == 0) {
         const uint32_t sbase = base + stage * kStageBytes;
+        const uint32_t bbase = base + kOffB + bsel * kBBufBytes;
         const uint32_t d = tmem_base + (uint32_t)(stage * NN);
         uint32_t acc = 0;
 #pragma unroll
@@ -323,10 +386,14 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t ka = (uint32_t)((j >> 2) * kPanelA + (j & 3) * 32);
           const uint32_t kb = (uint32_t)((j >> 2) * kPanelB + (j & 3) * 32);
           const uint64_t a_hi = make_desc_sw128(sbase + ka), a_lo = make_desc_sw128(sbase + kOffAlo + ka);
-          const uint64_t b_hi = make_desc_sw128(sbase + kOffBhi + kb), b_lo = make_desc_sw128(sbase + kOffBlo + kb);
-          umma_tf32(d, a_lo, b_hi, kIdesc, acc);
-          umma_tf32(d, a_hi, b_lo, kIdesc, 1);
-          umma_tf32(d, a_hi, b_hi, kIdesc, 1);
+          const uint64_t b_hi = make_desc_sw128(bbase + kb), b_lo = make_desc_sw128(bbase + kOffBlo + kb);
+          if (passes == 3) {
+            umma_tf32(d, a_lo, b_hi, kIdesc, acc);
+            umma_tf32(d, a_hi, b_lo, kIdesc, 1);
+            umma_tf32(d, a_hi, b_hi, kIdesc, 1);
+          } else if (passes == 1) {
+            umma_tf32(d, a_hi, b_hi, kIdesc, acc);
+          }
           acc = 1;
         }
         umma_commit(empty_bar(stage));  // operands may be overwritten once these MMAs retire
@@ -337,36 +404,46 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   } else {
     // ===================== epilogue =====================
-    uint8_t *stg = gbase + kStages * kStageBytes + warp * (32 * NN * 4);  // this warp's 32 rows x 256 B
+    uint8_t *stg = gbase + kOffEpi + warp * (32 * NN * 4);  // this warp's 32 rows x 256 B
     uint32_t n = 0;
     while (it.next(tile_row0, p0, p1, seg)) {
       const int stage = n & 1;
       const uint32_t phase = (n >> 1) & 1;
+      // destination row of this lane's tile row (lane j <-> row warp*32 + j), fetched early
+      const int64_t my_gr = tile_row0 + warp * 32 + lane;
+      int64_t my_cr = my_gr;
+      if (c_idx && my_gr >= p0 && my_gr < p1) my_cr = __ldg(c_idx + my_gr);
       mbar_wait(tfull_bar(stage), phase);
       tc_fence_after();
-      uint32_t v[64];
       const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(stage * NN);
-      tmem_ld32(taddr, v);
-      tmem_ld32(taddr + 32, v + 32);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(tempty_bar(stage));  // TMEM stage free: the next MMA may start
-      // registers (thread = row) -> swizzled staging -> 16 lanes per row
+      // registers (thread = row) -> swizzled staging, 32 columns at a time
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const int pc = (c & 8) | ((c & 7) ^ (lane & 7));
-        *reinterpret_cast<uint4 *>(stg + lane * 256 + pc * 16) = make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld32(taddr + 32 * half, v);
+        tmem_ld_wait();
+        if (half == 1) {
+          tc_fence_before();
+          mbar_arrive(tempty_bar(stage));  // TMEM stage free: the next MMA may start
+        }
+#pragma unroll
+        for (int c8 = 0; c8 < 8; ++c8) {
+          const int c = half * 8 + c8;
+          const int pc = (c & 8) | ((c & 7) ^ (lane & 7));
+          *reinterpret_cast<uint4 *>(stg + lane * 256 + pc * 16) =
+              make_uint4(v[4 * c8], v[4 * c8 + 1], v[4 * c8 + 2], v[4 * c8 + 3]);
+        }
       }
       __syncwarp();
       const int c = lane & 15;
-#pragma unroll 4
+#pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int lr = i * 2 + (lane >> 4);  // row within this warp's 32
         const int64_t gr = tile_row0 + warp * 32 + lr;
-        if (gr >= p0 && gr < p1) {
+        const int64_t cr = __shfl_sync(0xffffffffu, my_cr, lr);
+        if (gr >= p0 && gr < p1 && !(probe & 4)) {
           const int pc = (c & 8) | ((c & 7) ^ (lr & 7));
           const float4 val = *reinterpret_cast<const float4 *>(stg + lr * 256 + pc * 16);
-          const int64_t cr = c_idx ? __ldg(c_idx + gr) : gr;
           float *dst = Y + cr * NN + c * 4;
           if (accumulate) red_add4(dst, val);
           else st4(dst, val);
@@ -394,8 +471,10 @@ using namespace hetb;
 // (hetb_segment_mm) then uses the SIMT kernels.
 int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
                        const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
-                       int64_t num_rows, int H, int K, int N, int accumulate, void *stream) {
+                       int64_t num_rows, int H, int K, int N, int accumulate, int passes, void *stream) {
   int bmode;
+  const int probe = passes >> 4;
+  passes &= 15;
   if (a_heads == H && c_heads == H && H * K == tc::KK && H * N == tc::NN)
     bmode = (H == 1) ? tc::kDense : tc::kBlockDiag;
   else if (a_heads == 1 && c_heads == H && K == tc::KK && H * N == tc::NN)
@@ -404,7 +483,7 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
     bmode = tc::kStacked;
   else
     return HETB_EUNSUPPORTED;
-  if (num_segs > INT32_MAX) return HETB_EUNSUPPORTED;
+  if (num_segs > INT32_MAX || (N % 4) != 0) return HETB_EUNSUPPORTED;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(tc::segmm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -415,7 +494,7 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
   const int64_t tiles = ceil_div64(num_rows, tc::TM);
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   tc::segmm_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, (cudaStream_t)stream>>>(
-      A, a_idx, W, Y, c_idx, seg_ptrs, (int)num_segs, num_rows, H, K, N, bmode, accumulate);
+      A, a_idx, W, Y, c_idx, seg_ptrs, (int)num_segs, num_rows, H, K, N, bmode, accumulate, passes, probe);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
