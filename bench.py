@@ -340,7 +340,8 @@ def main():
 
     kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
     coo, scale = _make_graph(args)
-    use_graph = not args.no_graph
+    # whole-step CUDA-graph capture; with NCCL collectives inside only when asked for (HETB_GRAPH_MULTI=1)
+    use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "0") == "1")
     trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
                                cuda_graph=use_graph)
 

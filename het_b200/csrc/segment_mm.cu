@@ -379,6 +379,74 @@ __global__ void __launch_bounds__(kMMThreads)
   }
 }
 
+// ---------------------------------------------------------------------------
+// Weight gradient of the attention-vector products (N == 1 or K == 1):
+//   dW[s, c] += sum_{i in segment s} S[s_idx[i], c / hw4] * V[v_idx[i], c]     c < D = H*F
+// i.e. a segment sum of head-scaled rows. A CTA owns a contiguous row range and walks
+// it segment piece by piece: its 256/LPR lane groups stride the piece's rows with
+// 128-bit loads, partial sums are combined in shared memory, and ONE group issues the
+// vector reductions, so global atomics are (#CTAs + #segments) * D.
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kMMThreads)
+    gradw_rowscale_kernel(const float *__restrict__ V, const int64_t *__restrict__ v_idx,
+                          const float *__restrict__ S, const int64_t *__restrict__ s_idx,
+                          float *__restrict__ dW, const int64_t *__restrict__ seg_ptrs, int num_segs,
+                          int64_t M, int H, int hw, int64_t rows_per_cta) {
+  constexpr int GROUPS = kMMThreads / LPR;
+  constexpr int D = LPR * 4;
+  __shared__ float4 part[GROUPS][LPR];
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int h = l / hw;
+  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t row1 = (row0 + rows_per_cta < M) ? row0 + rows_per_cta : M;
+  if (row0 >= row1) return;
+  int s = segment_of(seg_ptrs, num_segs, row0);
+  while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row0) ++s;
+  int64_t a = row0;
+  while (a < row1) {
+    const int64_t seg_end = (s + 1 < num_segs) ? __ldg(seg_ptrs + s + 1) : M;
+    const int64_t b = seg_end < row1 ? seg_end : row1;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    int64_t i = a + g;
+    for (; i + 3 * GROUPS < b; i += 4 * GROUPS) {  // 4 rows in flight per group
+      float sc[4];
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int64_t r = i + j * GROUPS;
+        const int64_t vr = v_idx ? __ldg(v_idx + r) : r;
+        const int64_t sr = s_idx ? __ldg(s_idx + r) : r;
+        sc[j] = __ldg(S + sr * H + h);
+        v[j] = ldcs4(V + vr * D + 4 * l);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) fma4(acc, sc[j], v[j]);
+    }
+    for (; i < b; i += GROUPS) {
+      const int64_t vr = v_idx ? __ldg(v_idx + i) : i;
+      const int64_t sr = s_idx ? __ldg(s_idx + i) : i;
+      fma4(acc, __ldg(S + sr * H + h), ldcs4(V + vr * D + 4 * l));
+    }
+    part[g][l] = acc;
+    __syncthreads();
+    for (int stride = GROUPS / 2; stride > 0; stride >>= 1) {
+      if (g < stride) {
+        const float4 x = part[g][l], y = part[g + stride][l];
+        part[g][l] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+      }
+      __syncthreads();
+    }
+    if (g == 0) red_add4(dW + (int64_t)s * D + 4 * l, part[0][l]);
+    __syncthreads();
+    a = b;
+    if (a == seg_end && a < row1) {
+      ++s;
+      while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= a) ++s;
+    }
+  }
+}
+
 static int pick_lpr(int d) {
   if (d % 4) return 0;
   const int v = d / 4;
@@ -530,6 +598,32 @@ extern "C" int hetb_segment_mm_grad_w(const float *A, const int64_t *a_idx,
   cudaStream_t st = (cudaStream_t)stream;
   const int S = (int)num_segs;
   const int AK = a_heads * K, GN = g_heads * N;
+  // Attention-vector gradients: N == 1 (dW = sum G[i,h] * A[i,h,:]) or K == 1 (dW = sum A[i,h] * G[i,h,:]).
+  if ((N == 1 || K == 1) && !(N == 1 && K == 1) && a_heads == H && g_heads == H) {
+    const int F = (N == 1) ? K : N;
+    const int lpr = (is_pow2(H) && is_pow2(F) && F >= 4) ? pick_lpr(H * F) : 0;
+    if (lpr) {
+      const float *V = (N == 1) ? A : G;
+      const int64_t *vi = (N == 1) ? a_idx : g_idx;
+      const float *Sc = (N == 1) ? G : A;
+      const int64_t *si = (N == 1) ? g_idx : a_idx;
+      int64_t ctas = kNumSMs * 4;
+      int64_t rows_per_cta = ceil_div64(num_rows, ctas);
+      if (rows_per_cta < 256) rows_per_cta = 256;
+      ctas = ceil_div64(num_rows, rows_per_cta);
+      switch (lpr) {
+#define ROWSCALE(L)                                                                        \
+  case L:                                                                                  \
+    gradw_rowscale_kernel<L><<<(unsigned)ctas, kMMThreads, 0, st>>>(                       \
+        V, vi, Sc, si, dW, seg_ptrs, S, num_rows, H, F / 4, rows_per_cta);                 \
+    break;
+        ROWSCALE(4) ROWSCALE(8) ROWSCALE(16) ROWSCALE(32)
+#undef ROWSCALE
+      }
+      HETB_LAUNCH_OK();
+      return HETB_OK;
+    }
+  }
   const int tiles = (K % 4 == 0 && N % 4 == 0) ? H * (K / 4) * (N / 4) : 0;
   const size_t smem = (size_t)kGWRows * (AK + GN) * sizeof(float);
   if (tiles > 0 && tiles <= 4 * kMMThreads && smem <= 96 * 1024 &&
