@@ -462,6 +462,10 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
                        const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
                        int64_t num_rows, int H, int K, int N, int accumulate, int passes, void *stream);
 
+int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads, const float *G,
+                              const int64_t *g_idx, int g_heads, float *dW, const int64_t *seg_ptrs,
+                              int64_t num_segs, int64_t num_rows, int H, int K, int N, int probe, void *stream);
+
 static int g_segmm_impl = 0;  // 0 auto, 1 SIMT only, 2 tensor core only (3xTF32), 3 TC 1xTF32, 4 TC pipeline without MMAs (timing probe)
 
 extern "C" int hetb_set_segment_mm_impl(int impl) {
@@ -598,6 +602,13 @@ extern "C" int hetb_segment_mm_grad_w(const float *A, const int64_t *a_idx,
   cudaStream_t st = (cudaStream_t)stream;
   const int S = (int)num_segs;
   const int AK = a_heads * K, GN = g_heads * N;
+  // Tensor-core path (tcgen05/TMEM, 3xTF32, contraction over the rows): 64-wide rows on both sides.
+  if (g_segmm_impl != 1 && (g_segmm_impl >= 2 || num_rows >= 2048)) {
+    const int probe = g_segmm_impl >= 16 ? (g_segmm_impl >> 8) : 0;
+    const int rc = hetb_segment_mm_grad_w_tc(A, a_idx, a_heads, G, g_idx, g_heads, dW, seg_ptrs, num_segs,
+                                             num_rows, H, K, N, probe, stream);
+    if (rc != HETB_EUNSUPPORTED) return rc;
+  }
   // Attention-vector gradients: N == 1 (dW = sum G[i,h] * A[i,h,:]) or K == 1 (dW = sum A[i,h] * G[i,h,:]).
   if ((N == 1 || K == 1) && !(N == 1 && K == 1) && a_heads == H && g_heads == H) {
     const int F = (N == 1) ? K : N;
