@@ -64,7 +64,7 @@ def build_kernels(force: bool = False) -> Path:
         o = OBJ / (s.stem + ".o")
         objs.append(o)
         if force or _stale(o, [s] + headers):
-            jobs.append([nvcc, *NVCC_FLAGS, "-c", str(s), "-o", str(o)])
+            jobs.append([nvcc, *NVCC_FLAGS, *os.environ.get("HETB_NVCC_EXTRA", "").split(), "-c", str(s), "-o", str(o)])
     with ThreadPoolExecutor(max_workers=4) as ex:
         list(ex.map(_run, jobs))
     out = LIB / "libhetb200.so"

@@ -469,7 +469,7 @@ int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads,
 static int g_segmm_impl = 0;  // 0 auto, 1 SIMT only, 2 tensor core only (3xTF32), 3 TC 1xTF32, 4 TC pipeline without MMAs (timing probe)
 
 extern "C" int hetb_set_segment_mm_impl(int impl) {
-  if (impl < 0 || impl > 4096) return HETB_EINVAL;
+  if (impl < 0 || impl > 65535) return HETB_EINVAL;
   g_segmm_impl = impl;
   return HETB_OK;
 }

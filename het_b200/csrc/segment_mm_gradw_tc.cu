@@ -16,27 +16,31 @@
 // 16-byte cp.async per chunk, swizzled destination) and the tensor core contracts over the row
 // index — no transpose anywhere.
 //
-// Precision: 3xTF32 (tc has no fp32 MMA). Each value is split into hi (tf32) + lo (exact
-// remainder). The hi and lo copies of X are stacked as ONE M = 128 operand
-// [X_hi f0-31 | X_hi f32-63 | X_lo f0-31 | X_lo f32-63], so two MMAs per 8 rows
-//   D[0:64]   = X_hi^T G_hi + X_hi^T G_lo
-//   D[64:128] = X_lo^T G_hi + X_lo^T G_lo
-// give all four partial products (one more than 3xTF32 needs) and the two halves of D are summed
-// by the reductions into dW.
+// Precision: split-tf32 (the tensor core has no fp32 MMA). x = hi + lo with hi = x truncated to
+// tf32 and lo the exact remainder. The tensor core ignores the low 13 mantissa bits of a tf32
+// operand, so the raw fp32 row IS the hi operand and only lo is computed. hi and lo are stacked
+// into ONE M = 128 operand [X f0-31 | X f32-63 | X_lo f0-31 | X_lo f32-63] and ONE N = 128
+// operand [G | G_lo], so a single MMA per 8 rows yields all four partial products
+//   D[0:64, 0:64] = X_hi^T G_hi     D[0:64, 64:128] = X_hi^T G_lo
+//   D[64:128, 0:64] = X_lo^T G_hi   D[64:128, 64:128] = X_lo^T G_lo
+// which the flush adds into the same dW block (error vs the fp64 oracle ~1e-6 relative).
 //
-// Structure (persistent, one CTA per SM, 544 threads, warp specialised, mbarrier pipeline):
-//   warps 0-3   flush    : at the end of a segment run, tcgen05.ld the 128 x 64 accumulator and
+// Structure (persistent, one CTA per SM, 512 threads, warp specialised, mbarrier pipeline):
+//   warps 0-3   flush    : at the end of a segment run, tcgen05.ld the 128 x 128 accumulator and
 //                          red.add.v4 it into dW[s] (only the live blocks for per-head weights)
-//   warp  4     MMA      : one lane issues 2 tcgen05.mma.kind::tf32 (M128 N64 K8, A and B MN-major)
-//                          per 8 rows; the accumulator stays in TMEM across the CTA's whole run of
-//                          a segment (two accumulators, so a flush overlaps the next segment)
-//   warps 5-8   loaders  : each takes every 4th stage: 32 rows x (X row + G row) as 16-byte
+//   warp  4     MMA      : one lane issues tcgen05.mma.kind::tf32 (M128 N128 K8, A and B MN-major),
+//                          one per 8 rows; the accumulator stays in TMEM across the CTA's whole run
+//                          of a segment (two accumulators, so a flush overlaps the next segment).
+//                          MN-major tf32 MMAs run at about half rate and the issue queue is
+//                          shallow, so this warp does nothing else: what to issue comes from a
+//                          one-word stage descriptor the split warps leave in shared memory.
+//   warps 5-7   loaders  : each takes every 3rd stage: SR rows x (X row + G row) as 16-byte
 //                          cp.async (zero fill past the end of a piece), completion signalled
 //                          through cp.async.mbarrier.arrive; gather indices are fetched one own
-//                          stage (= 4 stages) ahead. Nothing waits on a global load.
-//   warps 9-16  split    : LDS the raw rows, write hi in place and lo beside it, proxy fence
+//                          stage (= 3 stages) ahead. Nothing waits on a global load.
+//   warps 8-15  split    : LDS the raw rows, write lo beside them, proxy fence, one arrival per warp
 // A CTA owns a contiguous row range; its stages are cut at segment boundaries, so an accumulator
-// only ever holds rows of one segment. Six 32 KB stages = 96 KB of raw rows in flight per SM.
+// only ever holds rows of one segment.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -45,85 +49,123 @@ namespace tcgw {
 
 using namespace tc;
 
-constexpr int SR = 32;       // rows per stage = 4 MMA k-steps
-constexpr int kStages = 6;
+#ifndef HETB_GW_SR
+#define HETB_GW_SR 64
+#endif
+constexpr int SR = HETB_GW_SR;     // rows per stage (8 per MMA k-step)
+constexpr int kStages = 192 / SR;  // 192 KB of stages: 96 KB of raw rows in flight per SM
 constexpr int kEpiWarps = 4;
-constexpr int kLoadWarps = 4;
-constexpr int kConvWarps = 8;
-constexpr int kConvThreads = kConvWarps * 32;
-constexpr int kThreads = (kEpiWarps + 1 + kLoadWarps + kConvWarps) * 32;  // 544
+#ifndef HETB_GW_PW
+#define HETB_GW_PW 8
+#endif
+constexpr int kProdWarps = HETB_GW_PW;
+constexpr int kThreads = (kEpiWarps + 1 + kProdWarps) * 32;  // 416 with 8 producer warps
+static_assert(SR == 32 || SR == 64, "stage rows");
 
-constexpr uint32_t kAtom = SR * 128;  // SR rows of one 32-feature panel: 4 KB
-constexpr uint32_t kOffXhi = 0, kOffXlo = 2 * kAtom, kOffGhi = 4 * kAtom, kOffGlo = 6 * kAtom;
-constexpr uint32_t kStageBytes = 8 * kAtom;  // 32 KB
-constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t kAtom = SR * 128;  // SR rows of one 32-feature panel
+constexpr uint32_t kOffX = 0, kOffXlo = 2 * kAtom, kOffG = 4 * kAtom, kOffGlo = 6 * kAtom;
+constexpr uint32_t kStageBytes = 8 * kAtom;  // 1 KB per row
+constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 512 /*barriers, stage words*/;
 
-// D = f32, A = B = tf32, A and B MN-major (bits 15, 16), N = 64, M = 128
+// D = f32, A = B = tf32, A and B MN-major (bits 15, 16), N = 128, M = 128
 constexpr uint32_t kIdescMN =
-    (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
+    (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+constexpr uint32_t kAccCols = 128;  // TMEM columns per accumulator
 
 // The CTA's rows cut into stages of at most SR rows that never cross a segment boundary.
-// Every role walks the same sequence.
+// Positions are 32-bit offsets from the CTA's first row (64-bit compare/select chains cost
+// ~200 cycles per call), and the segment table is only touched when a segment ends.
 struct RowItems {
   const int64_t *__restrict__ seg_ptrs;
-  int num_segs;
-  int64_t M, row, row_stop, seg_end;
-  int s;
+  int64_t row_base;  // first row of the CTA
+  int num_segs, n, rel, seg_end, s;  // rows of the CTA, position, end of segment s (clamped to n)
 
-  __device__ RowItems(const int64_t *sp, int ns, int64_t m, int64_t r0, int64_t r1)
-      : seg_ptrs(sp), num_segs(ns), M(m), row(r0), row_stop(r1), seg_end(0), s(0) {
-    if (row < row_stop) {
-      s = segment_of(seg_ptrs, num_segs, row);
+  __device__ RowItems(const int64_t *sp, int ns, int64_t r0, int64_t r1)
+      : seg_ptrs(sp), row_base(r0), num_segs(ns), n(r1 > r0 ? (int)(r1 - r0) : 0), rel(0), seg_end(0), s(0) {
+    if (n > 0) {
+      s = segment_of(seg_ptrs, num_segs, r0);
       skip_empty();
     }
   }
   __device__ void skip_empty() {
+    const int64_t row = row_base + rel;
     while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
-    seg_end = (s + 1 < num_segs) ? __ldg(seg_ptrs + s + 1) : M;
+    int64_t e = n;
+    if (s + 1 < num_segs) {
+      const int64_t se = __ldg(seg_ptrs + s + 1) - row_base;
+      if (se < e) e = se;
+    }
+    seg_end = (int)e;
   }
-  // rows [r0, r0 + nrows) of segment seg; last = the accumulator of this segment run is complete
-  __device__ bool next(int64_t &r0, int &nrows, int &seg, bool &last) {
-    if (row >= row_stop) return false;
-    int64_t stop = row + SR;
-    if (seg_end < stop) stop = seg_end;
-    if (row_stop < stop) stop = row_stop;
-    r0 = row;
-    nrows = (int)(stop - row);
+  // rows [rel0, rel0 + nrows) (relative to row_base) of segment seg; last = the accumulator of
+  // this segment run is complete
+  __device__ __forceinline__ bool next(int &rel0, int &nrows, int &seg, bool &last) {
+    if (rel >= n) return false;
+    const int stop = min(rel + SR, seg_end);
+    rel0 = rel;
+    nrows = stop - rel;
     seg = s;
-    row = stop;
-    last = (row == seg_end) || (row >= row_stop);
-    if (row == seg_end && row < row_stop) {
+    rel = stop;
+    last = (stop == seg_end);
+    if (last && stop < n) {
       ++s;
       skip_empty();
     }
     return true;
   }
+  // number of stages the whole range yields (walks segments, not stages)
+  __device__ int count() const {
+    RowItems c = *this;
+    int items = 0;
+    while (c.rel < c.n) {
+      items += (c.seg_end - c.rel + SR - 1) / SR;
+      c.rel = c.seg_end;
+      if (c.rel < c.n) {
+        ++c.s;
+        c.skip_empty();
+      }
+    }
+    return items;
+  }
 };
+
+#define HETB_WAIT(acc, bar, par)       \
+  do {                                 \
+    if (dbg) {                         \
+      const long long t__ = clock64(); \
+      mbar_wait(bar, par);             \
+      acc += clock64() - t__;          \
+    } else {                           \
+      mbar_wait(bar, par);             \
+    }                                  \
+  } while (0)
 
 __global__ void __launch_bounds__(kThreads, 1)
     gradw_tc_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx, int a_heads,
                     const float *__restrict__ G, const int64_t *__restrict__ g_idx, float *__restrict__ dW,
                     const int64_t *__restrict__ seg_ptrs, int num_segs, int64_t M, int H, int K, int N,
-                    int64_t rows_per_cta, int probe) {
+                    int64_t rows_per_cta, int probe, long long *__restrict__ dbg) {
+  const long long t_start = dbg ? clock64() : 0;
+  long long w0 = 0, w1 = 0, w2 = 0, w3 = 0;  // cycles this warp's lane 0 spent in barrier waits etc. (dbg only)
   extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SW128 atoms need 1024 B alignment
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle atoms: 1024 B alignment
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t bar_base = base + kStages * kStageBytes;
-  auto full_bar = [&](int i) { return bar_base + 8u * i; };                   // cp.async landed
-  auto conv_bar = [&](int i) { return bar_base + 8u * (kStages + i); };       // hi/lo written
+  auto full_bar = [&](int i) { return bar_base + 8u * i; };                   // rows and lo parts stored
   auto empty_bar = [&](int i) { return bar_base + 8u * (2 * kStages + i); };  // MMAs retired
   auto tfull_bar = [&](int i) { return bar_base + 8u * (3 * kStages + i); };
   auto tempty_bar = [&](int i) { return bar_base + 8u * (3 * kStages + 2 + i); };
   const uint32_t tmem_slot = bar_base + 8u * (3 * kStages + 4);
   volatile uint32_t *tmem_slot_g = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_slot - base));
+  // one word per stage, written by the split warps before they arrive: k-steps | last << 8
+  volatile uint32_t *stage_word = tmem_slot_g + 2;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == kEpiWarps) {
     if (lane == 0) {
       for (int i = 0; i < kStages; ++i) {
-        mbar_init(full_bar(i), 32);  // the 32 lanes of the loader warp that owns the stage
-        mbar_init(conv_bar(i), kConvThreads);
+        mbar_init(full_bar(i), kProdWarps);
         mbar_init(empty_bar(i), 1);
       }
       for (int i = 0; i < 2; ++i) {
@@ -133,7 +175,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       fence_barrier_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, 128);  // two 64-column accumulators
+    tmem_alloc(tmem_slot, 2 * kAccCols);  // two accumulators
   }
   tc_fence_before();
   __syncthreads();
@@ -142,132 +184,156 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
   const int64_t row1 = (row0 + rows_per_cta < M) ? row0 + rows_per_cta : M;
-  RowItems it(seg_ptrs, num_segs, M, row0, row1);
-  int64_t r0;
-  int nrows, seg;
+  RowItems it(seg_ptrs, num_segs, row0, row1);
+  int r0, nrows, seg;
   bool last;
 
-  if (warp > kEpiWarps + kLoadWarps) {
-    // ===================== split hi / lo =====================
-    const int c = threadIdx.x - (kEpiWarps + 1 + kLoadWarps) * 32;
+  if (warp > kEpiWarps) {
+    // ===================== producers: gather rows, split, store =====================
+    // The gather is latency bound, so what matters is bytes in flight: every producer thread
+    // keeps two stages of rows in registers (16 x 16 B). Right after stage n has been split and
+    // stored, its registers are re-used for the row loads of stage n+2 (whose indices arrived two
+    // steps ago) and its index registers for the index loads of stage n+4. The loop is unrolled
+    // two ways so the register sets rotate by name.
+    const int pw = warp - kEpiWarps - 1;          // rows pw, pw + 8, ...
+    const int mat = lane >> 4, ch = lane & 15;    // lanes 0-15: X chunks, 16-31: G chunks
+    constexpr int RP = SR / kProdWarps;           // rows per thread and stage
+    const float *srcbase = (mat ? G : A) + ch * 4;
+    const int64_t *idxbase = mat ? g_idx : a_idx;
+    const uint32_t dst_lane = (uint32_t)(mat * (4 * kAtom) + (ch >> 3) * kAtom);
+    RowItems it_ix = it;  // runs 2..4 stages ahead of `it`
     uint32_t n = 0;
-    while (it.next(r0, nrows, seg, last)) {
-      const uint32_t stage = n % kStages, phase = (n / kStages) & 1;
-      mbar_wait(full_bar(stage), phase);
-      uint8_t *sb = gbase + stage * kStageBytes;
+
+    // Predicated, not branched (a branch per slot costs more than the load), and the load writes
+    // the index register directly: anything computed from the loaded value here would stall this
+    // step for a full memory latency.
+    const bool ident = (idxbase == nullptr);
+    auto issue_idx = [&](int *ix) {
+      int q0, qn, qs;
+      bool ql;
+      const bool valid = it_ix.next(q0, qn, qs, ql);
+      const int lim = (valid && !(probe & 4)) ? qn : 0;  // probe 4: no global traffic
+      const int64_t rb = row0 + q0 + pw;
 #pragma unroll
-      for (int j = 0; j < SR * 32 / kConvThreads; ++j) {
-        const int id = c + kConvThreads * j;
-        const int row = id >> 5, q = id & 31, mat = q >> 4, ch = q & 15;
-        const uint32_t off = (uint32_t)(mat * (4 * kAtom) + (ch >> 3) * kAtom) + mn32b_off(row, ch & 7);
-        const float4 x = *reinterpret_cast<const float4 *>(sb + off);
+      for (int i = 0; i < RP; ++i) {
+        const bool ok = pw + kProdWarps * i < lim;
+        const int64_t r = rb + kProdWarps * i;
+        // a row index fits 31 bits: 2^31 rows of 256 B would be 550 GB
+        int v = ok ? (int)r : -1;
+        if (ok && !ident) v = (int)__ldg(idxbase + r);
+        ix[i] = v;
+      }
+    };
+    auto issue_rows = [&](const int *ix, float4 *v) {
+#pragma unroll
+      for (int i = 0; i < RP; ++i) {
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ix[i] >= 0) v[i] = ldg4(srcbase + (int64_t)ix[i] * 64);
+      }
+    };
+    auto step = [&](float4 *rS, int *ixS) -> bool {
+      if (!it.next(r0, nrows, seg, last)) return false;
+      const uint32_t stage = n % kStages, phase = (n / kStages) & 1;
+      HETB_WAIT(w0, empty_bar(stage), phase ^ 1);
+      uint8_t *sb = gbase + stage * kStageBytes + dst_lane;
+      long long t1 = dbg ? clock64() : 0;
+#pragma unroll
+      for (int i = 0; i < RP; ++i) {
+        const uint32_t off = mn32b_off(pw + kProdWarps * i, ch & 7);
+        const float4 x = rS[i];
         const float4 hi = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
         const float4 lo = make_float4(x.x - hi.x, x.y - hi.y, x.z - hi.z, x.w - hi.w);
-        if (!(probe & 1)) *reinterpret_cast<float4 *>(sb + off) = hi;
-        *reinterpret_cast<float4 *>(sb + off + 2 * kAtom) = lo;
+        if (!(probe & 8)) {
+          // the tensor core ignores the low 13 mantissa bits: the raw row is the hi operand
+          *reinterpret_cast<float4 *>(sb + off) = x;
+          *reinterpret_cast<float4 *>(sb + off + 2 * kAtom) = lo;
+        }
       }
-      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
-      mbar_arrive(conv_bar(stage));
+      long long t2 = dbg ? clock64() : 0;
+      issue_rows(ixS, rS);  // stage n + 2
+      issue_idx(ixS);       // stage n + 4
+      long long t3 = dbg ? clock64() : 0;
+      if (pw == 0 && lane == 0) stage_word[stage] = (uint32_t)((nrows + 7) >> 3) | (last ? 256u : 0u);
+      if (!(probe & 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full_bar(stage));  // one arrival per warp
+      if (dbg) {
+        w1 += t2 - t1;             // wait for the rows + split + store
+        w2 += t3 - t2;             // issue loads
+        w3 += clock64() - t3;      // fence + arrive
+      }
       ++n;
-    }
-  } else if (warp > kEpiWarps) {
-    // ===================== loaders =====================
-    const int lw = warp - kEpiWarps - 1;
-    RowItems itp = it;  // walks ahead: (pr0, pn) is this warp's next stage
-    int64_t pr0 = 0;
-    int pn = 0, ps;
-    bool pl, pvalid = true;
-    for (int i = 0; i <= lw && pvalid; ++i) pvalid = itp.next(pr0, pn, ps, pl);
-    auto fetch_idx = [&](const int64_t *idx, int64_t rbase, int cnt) -> int {
-      // a row index fits 31 bits: 2^31 rows of 256 B would be 550 GB
-      if (lane >= cnt) return 0;
-      return idx ? (int)__ldg(idx + rbase + lane) : (int)(rbase + lane);
+      return true;
     };
-    int ia = 0, ig = 0;
-    if (pvalid) {
-      ia = fetch_idx(a_idx, pr0, pn);
-      ig = fetch_idx(g_idx, pr0, pn);
-    }
-    const int cl = lane & 15;
-    const float *srcbase = (lane < 16) ? A : G;
-    const uint32_t dst_lane = (lane < 16 ? kOffXhi : kOffGhi) + (uint32_t)(cl >> 3) * kAtom;
-    uint32_t n = (uint32_t)lw;
-    while (pvalid) {
-      const int cur_n = pn, cia = ia, cig = ig;
-      for (int i = 0; i < kLoadWarps && pvalid; ++i) pvalid = itp.next(pr0, pn, ps, pl);
-      if (pvalid) {  // indices of this warp's next stage: four stages of time to land
-        ia = fetch_idx(a_idx, pr0, pn);
-        ig = fetch_idx(g_idx, pr0, pn);
-      }
-      const uint32_t stage = n % kStages, phase = (n / kStages) & 1;
-      mbar_wait(empty_bar(stage), phase ^ 1);
-      const uint32_t sb = base + stage * kStageBytes + dst_lane;
-#pragma unroll 8
-      for (int i = 0; i < SR; ++i) {
-        const int ra = __shfl_sync(0xffffffffu, cia, i), rg = __shfl_sync(0xffffffffu, cig, i);
-        const bool ok = i < cur_n;
-        const int r = (lane < 16) ? ra : rg;
-        const float *src = ok ? srcbase + (int64_t)r * 64 + cl * 4 : srcbase;
-        cp_async16(sb + mn32b_off(i, cl & 7), src, ok ? 16u : 0u);
-      }
-      cp_async_arrive_noinc(full_bar(stage));
-      n += kLoadWarps;
+
+    int ix0[RP], ix1[RP];
+    float4 v0[RP], v1[RP];
+    issue_idx(ix0);
+    issue_idx(ix1);
+    issue_rows(ix0, v0);
+    issue_idx(ix0);
+    issue_rows(ix1, v1);
+    issue_idx(ix1);
+    for (;;) {
+      if (!step(v0, ix0)) break;
+      if (!step(v1, ix1)) break;
     }
   } else if (warp == kEpiWarps) {
     // ===================== MMA issuer =====================
-    uint32_t n = 0, f = 0;
+    const int items = it.count();
+    uint32_t f = 0, stage = 0, phase = 0;
     bool fresh = true;
-    while (it.next(r0, nrows, seg, last)) {
-      const uint32_t stage = n % kStages, phase = (n / kStages) & 1;
-      if (fresh) mbar_wait(tempty_bar(f & 1), ((f >> 1) & 1) ^ 1);  // accumulator drained by the flush warps
-      mbar_wait(conv_bar(stage), phase);
+    const uint64_t desc0 = make_desc_mn_sw128_32b(base, kAtom);  // + byte offset >> 4 in the low word
+    for (int n = 0; n < items; ++n) {
+      if (fresh) HETB_WAIT(w0, tempty_bar(f & 1), ((f >> 1) & 1) ^ 1);  // accumulator drained by the flush warps
+      HETB_WAIT(w0, full_bar(stage), phase);
+      const uint32_t word = stage_word[stage];
       tc_fence_after();
+      const bool lastf = (word & 256u) != 0;
       if (lane == 0) {
-        const uint32_t sb = base + stage * kStageBytes;
-        const uint32_t d = tmem_base + (f & 1) * 64u;
-        const int nk = (nrows + 7) >> 3;
-        for (int j = 0; j < nk; ++j) {
-          const uint64_t a = make_desc_mn_sw128_32b(sb + kOffXhi + j * 1024, kAtom);
-          const uint64_t bh = make_desc_mn_sw128_32b(sb + kOffGhi + j * 1024, kAtom);
-          const uint64_t bl = make_desc_mn_sw128_32b(sb + kOffGlo + j * 1024, kAtom);
-          umma_tf32(d, a, bh, kIdescMN, (fresh && j == 0) ? 0u : 1u);
-          umma_tf32(d, a, bl, kIdescMN, 1u);
-        }
-        umma_commit(empty_bar(stage));
-        if (last) umma_commit(tfull_bar(f & 1));
+        const uint32_t d = tmem_base + (f & 1) * kAccCols;
+        const int nk = (probe & 2) ? 0 : (int)(word & 255u);  // probe 2: pipeline without MMAs
+        const uint64_t da = desc0 + ((stage * kStageBytes + kOffX) >> 4);
+        const uint64_t db = desc0 + ((stage * kStageBytes + kOffG) >> 4);  // [G | G_lo], N = 128
+        for (int j = 0; j < nk; ++j)
+          umma_tf32(d, da + (uint64_t)(j * (1024 >> 4)), db + (uint64_t)(j * (1024 >> 4)), kIdescMN,
+                    (fresh && j == 0) ? 0u : 1u);
+        if (probe & 64) mbar_arrive(empty_bar(stage));  // probe 64 (with 2): plain arrive instead of tcgen05.commit
+        else umma_commit(empty_bar(stage));
+        if (lastf) umma_commit(tfull_bar(f & 1));
       }
       __syncwarp();
-      fresh = false;
-      if (last) {
-        ++f;
-        fresh = true;
+      fresh = lastf;
+      f += lastf ? 1u : 0u;
+      if (++stage == kStages) {
+        stage = 0;
+        phase ^= 1;
       }
-      ++n;
     }
   } else {
     // ===================== flush =====================
     uint32_t f = 0;
-    const int m = warp * 32 + lane;  // accumulator row: feature (m & 63) of X_hi (m < 64) or X_lo
+    const int m = warp * 32 + lane;  // accumulator row: feature (m & 63) of X (m < 64) or X_lo
     const int kf = m & 63;
     const int kk = kf % K;
     while (it.next(r0, nrows, seg, last)) {
       if (!last) continue;
       const uint32_t acc = f & 1;
-      mbar_wait(tfull_bar(acc), (f >> 1) & 1);
+      mbar_wait_relaxed(tfull_bar(acc), (f >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * 64u;
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * kAccCols;
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
+      for (int part = 0; part < 4; ++part) {
         uint32_t v[32];
-        tmem_ld32(taddr + 32 * half, v);
+        tmem_ld32(taddr + 32 * part, v);
         tmem_ld_wait();
-        if (half == 1) {
+        if (part == 3) {
           tc_fence_before();
           mbar_arrive(tempty_bar(acc));  // accumulator free: the next segment run may start
         }
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
-          const int col = half * 32 + c4 * 4;
+          const int col = (part & 1) * 32 + c4 * 4;  // columns 64..127: the G_lo products of the same dW column
           const int h = col / N, nn = col % N;
           if (a_heads == 1 || kf / K == h) {
             float *dst = dW + (((int64_t)seg * H + h) * K + kk) * N + nn;
@@ -280,11 +346,19 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   }
 
+  if (dbg && lane == 0) {  // per warp: total cycles, cycles in barrier waits
+    long long *o = dbg + ((int64_t)blockIdx.x * (kThreads / 32) + warp) * 5;
+    o[0] = clock64() - t_start;
+    o[1] = w0;
+    o[2] = w1;
+    o[3] = w2;
+    o[4] = w3;
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == kEpiWarps) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
+    tmem_dealloc(tmem_base, 2 * kAccCols);
   }
 }
 
@@ -292,6 +366,13 @@ __global__ void __launch_bounds__(kThreads, 1)
 }  // namespace hetb
 
 using namespace hetb;
+
+static long long *g_gradw_dbg = nullptr;
+// Debug: per-warp cycle counters ([CTAs][17 warps][2] int64) written by the next launches.
+extern "C" int hetb_debug_set_gradw_buffer(void *p) {
+  g_gradw_dbg = (long long *)p;
+  return HETB_OK;
+}
 
 // Returns HETB_EUNSUPPORTED when the shape is outside the tensor-core path; the caller
 // (hetb_segment_mm_grad_w) then uses the SIMT kernels.
@@ -311,9 +392,11 @@ int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads,
   int64_t ctas = ceil_div64(num_rows, 8 * tcgw::SR);
   if (ctas > kNumSMs) ctas = kNumSMs;
   const int64_t rows_per_cta = ceil_div64(num_rows, ctas);
+  if (rows_per_cta > INT32_MAX) return HETB_EUNSUPPORTED;
   ctas = ceil_div64(num_rows, rows_per_cta);
   tcgw::gradw_tc_kernel<<<(unsigned)ctas, tcgw::kThreads, tcgw::kSmemBytes, (cudaStream_t)stream>>>(
-      A, a_idx, a_heads, G, g_idx, dW, seg_ptrs, (int)num_segs, num_rows, H, K, N, rows_per_cta, probe);
+      A, a_idx, a_heads, G, g_idx, dW, seg_ptrs, (int)num_segs, num_rows, H, K, N, rows_per_cta, probe,
+      g_gradw_dbg);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

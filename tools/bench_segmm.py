@@ -54,6 +54,27 @@ def case(name, N, E, R, H, Kd, Nd, head_one, zipf=1.0):
         K.hetb200_set_segment_mm_impl(impl)
         ms = timeit(lambda: K.backward_rgnn_relational_matmul(args, 0, WT, X, gout, gX, gW, head_one))
         print(f"{name:28s} bwd {nm:5s} {ms:8.4f} ms")
+    # the two halves of the backward on their own, through the C ABI (ctypes on libhetb200.so)
+    import ctypes
+    from het_b200.kernels import KERNEL_LIB
+    lib = ctypes.CDLL(str(KERNEL_LIB))
+    vp, i64, ci = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+    lib.hetb_segment_mm_grad_w.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, i64, i64, ci, ci, ci, vp]
+    lib.hetb_segment_mm.argtypes = [vp, vp, ci, vp, vp, vp, ci, vp, i64, i64, ci, ci, ci, ci, vp]
+    st = torch.cuda.current_stream().cuda_stream
+    rows_bytes = E * (a_heads * Kd + H * Nd) * 4
+    for impl, nm in ((1, "simt"), (2, "tc"), (304, "tc raw-hi"), (48 + 512, "tc noMMA"), (48 + 1024, "tc noLoad"),
+                     (48 + 2048, "tc noSplit"), (48 + 256 * 14, "tc skeleton"), (48 + 256 * 30, "tc skel-nocp"), (48 + 256 * 16, "tc nocp")):
+        K.hetb200_set_segment_mm_impl(impl)
+        ms = timeit(lambda: lib.hetb_segment_mm_grad_w(X.data_ptr(), gather.data_ptr(), a_heads, gout.data_ptr(),
+                                                       eids.data_ptr(), H, gW.data_ptr(), rel_ptrs.data_ptr(), R, E,
+                                                       H, Kd, Nd, st))
+        print(f"{name:28s} dW  {nm:10s} {ms:8.4f} ms  {rows_bytes / ms / 1e6:8.1f} GB/s (rows read: gathered X + dY)")
+    for impl, nm in ((1, "simt"), (2, "tc")):
+        K.hetb200_set_segment_mm_impl(impl)
+        ms = timeit(lambda: lib.hetb_segment_mm(gout.data_ptr(), eids.data_ptr(), H, WT.data_ptr(), gX.data_ptr(),
+                                                gather.data_ptr(), a_heads, rel_ptrs.data_ptr(), R, E, H, Nd, Kd, 1, st))
+        print(f"{name:28s} dX  {nm:10s} {ms:8.4f} ms")
     K.hetb200_set_segment_mm_impl(0)
     # reference point: a plain copy of the output-sized tensor (read + write E*D*4 each)
     src = torch.empty(E, H * Nd, device=dev)

@@ -35,9 +35,16 @@ for r in (0, 1, 9, 31):
     X = torch.zeros(32, 64, device=dev); G = torch.zeros(32, 64, device=dev)
     X[r] = f; G[r] = f * 64
     report(f"row {r} only", run(X, G), X.t() @ G)
+for rows, r in ((64, 5), (64, 40), (64, 63), (128, 70), (256, 200), (512, 300)):
+    X = torch.zeros(rows, 64, device=dev); G = torch.zeros(rows, 64, device=dev)
+    X[r] = f; G[r] = f * 64
+    report(f"{rows} rows, row {r} only", run(X, G), X.t() @ G)
 X = torch.zeros(32, 64, device=dev); G = torch.zeros(32, 64, device=dev)
 X[:, 5] = 1.0; G[:, 7] = 1.0
 report("col 5 x col 7 ones", run(X, G), X.t() @ G)
 torch.manual_seed(0)
+for rows in (64, 128, 192, 256, 512, 1024):
+    X = torch.randn(rows, 64, device=dev); G = torch.randn(rows, 64, device=dev)
+    report(f"random {rows}", run(X, G), (X.double().t() @ G.double()).float())
 X = torch.randn(4000, 64, device=dev); G = torch.randn(4000, 64, device=dev)
 report("random 4000", run(X, G), (X.double().t() @ G.double()).float())
