@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--compact", action="store_true",
+                    help="the reference's compact_as_of_node_flag: X.W_r once per unique (relation, node) pair")
     return ap.parse_args()
 
 
@@ -343,7 +345,7 @@ def main():
     # whole-step CUDA-graph capture; with NCCL collectives inside only when asked for (HETB_GRAPH_MULTI=1)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "0") == "1")
     trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
-                               cuda_graph=use_graph)
+                               cuda_graph=use_graph, compact_as_of_node=args.compact)
 
     def barrier():
         if world > 1:
@@ -413,7 +415,7 @@ def main():
                         f"{heads} head(s), {coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
             "parallelism": "single GPU" if world == 1 else f"destination-range shards x{world}, NCCL all-gather of "
                            "source rows per layer, reduce-scatter in backward, all-reduce of weight grads",
-            "cuda_graph": use_graph,
+            "cuda_graph": use_graph, "compact_as_of_node": bool(args.compact),
             "l2": "inputs larger than L2: per-edge tensors of one step total "
                   f"{coo.num_edges // world * 64 * 4 * 6 / 1e6:.0f} MB per GPU vs 126 MB L2 (no flush between steps)",
             "edges_per_step": coo.num_edges * layers,

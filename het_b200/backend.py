@@ -81,10 +81,45 @@ class RgnnInnerProductEdgeAndNode(th.autograd.Function):
         return None, None, None, None, grad_left, grad_right, None
 
 
+# ----- rgnn_layers_and_funcs.py:122-200 (compact-as-of-node: one output row per unique (rel, node)) -----
+class RgnnRelationalMatmulCompactAsOfNode(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, unique_rel_ptrs, unique_node_indices, weights, inputs, ret, input_num_head_one_flag):
+        ctx.save_for_backward(unique_rel_ptrs, unique_node_indices, weights, inputs)
+        ctx.input_num_head_one_flag = input_num_head_one_flag
+        ctx.mark_dirty(ret)
+        K.rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": unique_rel_ptrs,
+             "unique_srcs_and_dests_node_indices": unique_node_indices},
+            1, weights, inputs, ret, input_num_head_one_flag)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        unique_rel_ptrs, unique_node_indices, weights, inputs = ctx.saved_tensors
+        grad_weight = th.zeros_like(weights, memory_format=th.contiguous_format)
+        grad_input = th.zeros_like(inputs, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": unique_rel_ptrs,
+             "unique_srcs_and_dests_node_indices": unique_node_indices},
+            1, th.transpose(weights, 2, 3).contiguous(), inputs, gradout.contiguous(),
+            grad_input, grad_weight, ctx.input_num_head_one_flag)
+        return None, None, grad_weight, grad_input, None, None
+
+
 def rgnn_relational_matmul(arg_tensor_dict, weights, inputs, input_num_head_one_flag, compact_as_of_node_kind):
-    """rgnn_layers_and_funcs.py:420-470 (kind 0; compact kinds are a later row)."""
+    """rgnn_layers_and_funcs.py:420-470. Kind 0: one output row per edge; kind 1
+    (CompactAsOfNodeKind::Enabled): one output row per unique (relation, node) pair."""
+    if compact_as_of_node_kind == 1:
+        ret = th.empty(
+            (arg_tensor_dict["unique_srcs_and_dests_node_indices"].numel(), weights.size(1), weights.size(3)),
+            dtype=weights.dtype, device=weights.device)
+        return RgnnRelationalMatmulCompactAsOfNode.apply(
+            arg_tensor_dict["unique_srcs_and_dests_rel_ptrs"],
+            arg_tensor_dict["unique_srcs_and_dests_node_indices"], weights.contiguous(), inputs.contiguous(),
+            ret, input_num_head_one_flag)
     if compact_as_of_node_kind != 0:
-        raise NotImplementedError("CompactAsOfNodeKind != Disabled")
+        raise NotImplementedError("CompactAsOfNodeKind > 1 for the relational matmul")
     ret = th.empty(
         (arg_tensor_dict["separate_coo_node_indices"].numel(), weights.size(1), weights.size(3)),
         dtype=weights.dtype, device=weights.device)
@@ -102,12 +137,46 @@ def rgnn_relational_matmul_no_scatter_gather_list(ntype_offset_ptrs, weights, in
         ntype_offset_ptrs, weights.contiguous(), inputs.contiguous(), ret)
 
 
+# ----- rgnn_layers_and_funcs.py:202-348 (left data compact, addressed by direct indexing) -----
+class RgnnInnerProductNodeCompactAndNode(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, edata_idx_to_inverse_idx, rel_ptrs, eids, row_indices, col_indices, left_node_compact_data,
+                right_node_vectors, ret):
+        ctx.save_for_backward(edata_idx_to_inverse_idx, rel_ptrs, eids, row_indices, col_indices,
+                              left_node_compact_data, right_node_vectors)
+        ctx.mark_dirty(ret)
+        K.rgnn_inner_product_right_node_separatecoo(
+            {"edata_idx_to_inverse_idx": edata_idx_to_inverse_idx}, 2, rel_ptrs, eids, row_indices, col_indices,
+            left_node_compact_data, right_node_vectors, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        inv, rel_ptrs, eids, row_indices, col_indices, left, right = ctx.saved_tensors
+        grad_left = th.zeros_like(left, memory_format=th.contiguous_format)
+        grad_right = th.zeros_like(right, memory_format=th.contiguous_format)
+        K.backward_inner_product_right_node_separatecoo(
+            {"edata_idx_to_inverse_idx": inv}, 2, rel_ptrs, eids, row_indices, col_indices, left, right,
+            gradout.contiguous(), grad_left, grad_right)
+        return None, None, None, None, None, grad_left, grad_right, None
+
+
 def rgnn_inner_product_right_node(graph, left_side_data, right_node_vectors, compact_as_of_node_kind,
                                   left_mapper_suffix=None):
-    """rgnn_layers_and_funcs.py:498-530 (kind 0)."""
-    if compact_as_of_node_kind != 0:
-        raise NotImplementedError("CompactAsOfNodeKind != Disabled")
+    """rgnn_layers_and_funcs.py:498-530. Kind 0: left is per-edge; kind 2: left is compact
+    ([unique (rel, node), H, F]) and addressed through inverse_idx<left_mapper_suffix>. Kind 1
+    (binary search in the unique lists) is not built."""
     coo = graph.get_separate_coo_original()
+    if compact_as_of_node_kind == 2:
+        uniq = graph.get_separate_unique_node_indices_single_sided()
+        ret = th.empty([coo["eids"].numel(), right_node_vectors.size(1)], dtype=right_node_vectors.dtype,
+                       device=right_node_vectors.device)
+        return RgnnInnerProductNodeCompactAndNode.apply(
+            uniq["inverse_idx" + (left_mapper_suffix or "_col")], coo["rel_ptrs"], coo["eids"],
+            coo["row_indices"], coo["col_indices"], left_side_data.contiguous(),
+            right_node_vectors.contiguous(), ret)
+    if compact_as_of_node_kind != 0:
+        raise NotImplementedError("CompactAsOfNodeKind 1 (binary search) for the inner product")
     ret = th.empty([coo["eids"].numel(), right_node_vectors.size(1)], dtype=right_node_vectors.dtype,
                    device=right_node_vectors.device)
     return RgnnInnerProductEdgeAndNode.apply(
@@ -248,3 +317,95 @@ def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(graph, message_
         outcsr["row_ptrs"], outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"],
         unnormalized_attn_score.contiguous(), mu.contiguous(), ssum, t, norm,
         message_per_edge.contiguous(), new_h)
+
+
+# ----- hetb200 extensions: compact-as-of-node (direct indexing) forms of the in-CSR ops -----
+class RelationalFusedGatCSRCompact(th.autograd.Function):
+    """relational_fused_gat_csr with feat_src / el compact by (relation, source) and er compact by
+    (relation, destination); the reference offers this only for its edge-parallel COO kernel
+    (rgat_layers_and_funcs.py:325-470, relational_fused_gat_compact_as_of_node_separate_coo_single_sided)."""
+
+    @staticmethod
+    def forward(ctx, incsr_row_ptr, incsr_eids, outcsr_col_indices, outcsr_eids, inverse_row, inverse_col,
+                feat_compact, el_compact, er_compact, s, exp, ret, slope):
+        ctx.mark_dirty(ret)
+        K.hetb200_relational_fused_gat_csr_compact(
+            incsr_row_ptr, incsr_eids, inverse_row, inverse_col, feat_compact, el_compact, er_compact, s, exp,
+            ret, slope)
+        ctx.save_for_backward(outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat_compact,
+                              el_compact, er_compact, s, exp, ret)
+        ctx.slope = slope
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        (outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat, el, er, s, exp, ret) = ctx.saved_tensors
+        grad_el = th.zeros_like(el, memory_format=th.contiguous_format)
+        grad_er = th.zeros_like(er, memory_format=th.contiguous_format)
+        grad_feat = th.zeros_like(feat, memory_format=th.contiguous_format)
+        K.hetb200_backward_relational_fused_gat_csr_compact(
+            outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat, el, er, s, exp, ret,
+            gradout.contiguous(), grad_feat, grad_el, grad_er, ctx.slope)
+        return (None,) * 6 + (grad_feat, grad_el, grad_er, None, None, None, None)
+
+
+def relational_fused_gat_csr_compact(graph, feat_compact, el_compact, er_compact, slope):
+    incsr, outcsr = graph.get_in_csr(), graph.get_out_csr()
+    uniq = graph.get_separate_unique_node_indices_single_sided()
+    h = el_compact.size(1)
+    exp = el_compact.new_empty([graph.get_num_edges(), h, 1])
+    s = el_compact.new_empty([graph.get_num_nodes(), h])
+    ret = el_compact.new_empty([graph.get_num_nodes()] + list(feat_compact.size()[1:]))
+    return RelationalFusedGatCSRCompact.apply(
+        incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["inverse_idx_row"],
+        uniq["inverse_idx_col"], feat_compact.contiguous(), el_compact.contiguous(), er_compact.contiguous(),
+        s, exp, ret, slope)
+
+
+class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact(th.autograd.Function):
+    """hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr with the messages compact by
+    (relation, source): V[src]·W_msg[r] is computed once per unique pair, not once per edge."""
+
+    @staticmethod
+    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, outcsr_col_indices,
+                outcsr_eids, outcsr_reltypes, msg_idx, unnormalized_attn_score, mu, ssum, t, norm,
+                message_compact, new_h):
+        ctx.mark_dirty(new_h)
+        K.hgt_full_graph_edge_softmax_ops_csr(
+            incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, unnormalized_attn_score, mu, ssum, t,
+            norm)
+        K.hetb200_hgt_message_aggregation_csr_compact(
+            incsr_row_ptrs, incsr_eids, msg_idx, message_compact, t, ssum, new_h)
+        ctx.save_for_backward(outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx,
+                              unnormalized_attn_score, mu, norm, message_compact, new_h)
+        return new_h
+
+    @staticmethod
+    def backward(ctx, gradout):
+        (outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx, unnormalized_attn_score, mu, norm,
+         message_compact, new_h) = ctx.saved_tensors
+        gradout = gradout.contiguous()
+        grad_message = th.zeros_like(message_compact, memory_format=th.contiguous_format)
+        K.hetb200_backward_hgt_message_aggregation_csr_compact(
+            outcsr_col_indices, outcsr_eids, msg_idx, norm, gradout, grad_message)
+        grad_attn_score = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+        grad_mu = th.zeros_like(mu, memory_format=th.contiguous_format)
+        K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
+            outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx, message_compact, unnormalized_attn_score,
+            norm, new_h, gradout, mu, grad_attn_score, grad_mu)
+        return (None,) * 8 + (grad_attn_score, grad_mu, None, None, None, grad_message, None)
+
+
+def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(graph, message_compact,
+                                                                         unnormalized_attn_score, mu):
+    incsr, outcsr = graph.get_in_csr(), graph.get_out_csr()
+    uniq = graph.get_separate_unique_node_indices_single_sided()
+    n, h = graph.get_num_nodes(), mu.size(1)
+    new_h = message_compact.new_empty(n, h, message_compact.size(2))
+    ssum = message_compact.new_empty(n, h)
+    t = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    norm = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    return HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact.apply(
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["col_indices"],
+        outcsr["eids"], outcsr["rel_types"], uniq["inverse_idx_row"], unnormalized_attn_score.contiguous(),
+        mu.contiguous(), ssum, t, norm, message_compact.contiguous(), new_h)

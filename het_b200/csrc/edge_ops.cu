@@ -90,7 +90,12 @@ __global__ void __launch_bounds__(kThreads)
                            const float *__restrict__ wb,  // er | unused
                            float *__restrict__ sum, float *__restrict__ exp_out,
                            float *__restrict__ ret, int H, int hw, float slope,
-                           int divide) {
+                           int divide,
+                           // compact-as-of-node with direct indexing (all indexed by edge id,
+                           // NULL = the tensor is per-edge): row of feat / wa / wb to read
+                           const int64_t *__restrict__ fidx,
+                           const int64_t *__restrict__ waidx,
+                           const int64_t *__restrict__ wbidx) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -157,11 +162,14 @@ __global__ void __launch_bounds__(kThreads)
       for (int j = 0; j < 4; ++j) e[j] = __ldg(eids + p + j);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (MODE == 0)
-          w[j] = __ldg(wa + e[j] * H + h) + __ldg(wb + e[j] * H + h);
-        else
-          w[j] = __ldg(wa + e[j] * H + h) * inv_d;
-        v[j] = ldcs4(feat + e[j] * D + 4 * l);
+        const int64_t ea = waidx ? __ldg(waidx + e[j]) : e[j];
+        if (MODE == 0) {
+          const int64_t eb = wbidx ? __ldg(wbidx + e[j]) : e[j];
+          w[j] = __ldg(wa + ea * H + h) + __ldg(wb + eb * H + h);
+        } else {
+          w[j] = __ldg(wa + ea * H + h) * inv_d;
+        }
+        v[j] = fidx ? ldg4(feat + __ldg(fidx + e[j]) * D + 4 * l) : ldcs4(feat + e[j] * D + 4 * l);
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -175,14 +183,16 @@ __global__ void __launch_bounds__(kThreads)
     }
     for (; p < stop; ++p) {
       const int64_t e = __ldg(eids + p);
+      const int64_t ea = waidx ? __ldg(waidx + e) : e;
       float w;
       if (MODE == 0) {
-        w = leaky_exp(__ldg(wa + e * H + h) + __ldg(wb + e * H + h), slope);
+        const int64_t eb = wbidx ? __ldg(wbidx + e) : e;
+        w = leaky_exp(__ldg(wa + ea * H + h) + __ldg(wb + eb * H + h), slope);
         if (leader) exp_out[e * H + h] = w;
       } else {
-        w = __ldg(wa + e * H + h) * inv_d;
+        w = __ldg(wa + ea * H + h) * inv_d;
       }
-      fma4(acc, w, ldcs4(feat + e * D + 4 * l));
+      fma4(acc, w, fidx ? ldg4(feat + __ldg(fidx + e) * D + 4 * l) : ldcs4(feat + e * D + 4 * l));
       s += w;
     }
   }
@@ -322,7 +332,8 @@ __global__ void __launch_bounds__(kThreads)
 template <int LPR>
 __global__ void __launch_bounds__(kThreads)
     inner_product_fwd_kernel(const int64_t *__restrict__ eids,
-                             const int64_t *__restrict__ row_idx, int64_t E,
+                             const int64_t *__restrict__ row_idx,
+                             const int64_t *__restrict__ left_idx, int64_t E,
                              const float *__restrict__ left,
                              const float *__restrict__ right,
                              float *__restrict__ out, int H, int hw) {
@@ -342,7 +353,12 @@ __global__ void __launch_bounds__(kThreads)
     if (ok) {
       e = __ldg(eids + i);
       const int64_t r = __ldg(row_idx + i);
-      v = dot4(ldcs4(left + e * D + 4 * l), ldg4(right + r * D + 4 * l));
+      // compact-as-of-node with direct indexing: the left row is shared by the edges of one
+      // (relation, node) pair, so it is a gather like the right row, not a stream
+      if (left_idx)
+        v = dot4(ldg4(left + __ldg(left_idx + e) * D + 4 * l), ldg4(right + r * D + 4 * l));
+      else
+        v = dot4(ldcs4(left + e * D + 4 * l), ldg4(right + r * D + 4 * l));
     }
     v = group_sum(v, hw);
     if (ok && leader) out[e * H + h] = v;
@@ -352,7 +368,8 @@ __global__ void __launch_bounds__(kThreads)
 template <int LPR>
 __global__ void __launch_bounds__(kThreads)
     inner_product_bwd_kernel(const int64_t *__restrict__ eids,
-                             const int64_t *__restrict__ row_idx, int64_t E,
+                             const int64_t *__restrict__ row_idx,
+                             const int64_t *__restrict__ left_idx, int64_t E,
                              const float *__restrict__ left,
                              const float *__restrict__ right,
                              const float *__restrict__ gout,
@@ -367,10 +384,14 @@ __global__ void __launch_bounds__(kThreads)
     const int64_t e = __ldg(eids + i);
     const int64_t r = __ldg(row_idx + i);
     const float gg = __ldg(gout + e * H + h);
-    const float4 lv = ldcs4(left + e * D + 4 * l);
+    const int64_t le = left_idx ? __ldg(left_idx + e) : e;
+    const float4 lv = left_idx ? ldg4(left + le * D + 4 * l) : ldcs4(left + e * D + 4 * l);
     const float4 rv = ldg4(right + r * D + 4 * l);
-    stcs4(grad_left + e * D + 4 * l,
-          make_float4(gg * rv.x, gg * rv.y, gg * rv.z, gg * rv.w));
+    const float4 gl = make_float4(gg * rv.x, gg * rv.y, gg * rv.z, gg * rv.w);
+    if (left_idx)
+      red_add4(grad_left + le * D + 4 * l, gl);  // compact row: summed over its edges
+    else
+      stcs4(grad_left + e * D + 4 * l, gl);
     red_add4(grad_right + r * D + 4 * l,
              make_float4(gg * lv.x, gg * lv.y, gg * lv.z, gg * lv.w));
   }
@@ -387,7 +408,9 @@ __global__ void __launch_bounds__(kThreads)
                     const float *__restrict__ ret,
                     const float *__restrict__ gout,
                     float *__restrict__ grad_feat, float *__restrict__ grad_el,
-                    float *__restrict__ grad_er, int H, int hw, float slope) {
+                    float *__restrict__ grad_er, int H, int hw, float slope,
+                    const int64_t *__restrict__ fidx, const int64_t *__restrict__ elidx,
+                    const int64_t *__restrict__ eridx) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -406,21 +429,26 @@ __global__ void __launch_bounds__(kThreads)
       const int64_t d = __ldg(dst_idx + i);
       const float sd = __ldg(sum + d * H + h);
       a = sd != 0.f ? __ldg(exp_in + e * H + h) / sd : 0.f;
-      const float x = __ldg(el + e * H + h) + __ldg(er + e * H + h);
+      const int64_t ea = elidx ? __ldg(elidx + e) : e, eb = eridx ? __ldg(eridx + e) : e;
+      const float x = __ldg(el + ea * H + h) + __ldg(er + eb * H + h);
       slope_g = x > 0.f ? 1.f : slope;
       const float4 go = ldg4(gout + d * D + 4 * l);
       const float4 rv = ldg4(ret + d * D + 4 * l);
-      const float4 fv = ldcs4(feat + e * D + 4 * l);
-      stcs4(grad_feat + e * D + 4 * l,
-            make_float4(a * go.x, a * go.y, a * go.z, a * go.w));
+      const int64_t ef = fidx ? __ldg(fidx + e) : e;
+      const float4 fv = fidx ? ldg4(feat + ef * D + 4 * l) : ldcs4(feat + e * D + 4 * l);
+      const float4 gf = make_float4(a * go.x, a * go.y, a * go.z, a * go.w);
+      if (fidx) red_add4(grad_feat + ef * D + 4 * l, gf);  // compact row: summed over its edges
+      else stcs4(grad_feat + e * D + 4 * l, gf);
       t = go.x * (fv.x - rv.x) + go.y * (fv.y - rv.y) + go.z * (fv.z - rv.z) +
           go.w * (fv.w - rv.w);
     }
     t = group_sum(t, hw);
     if (ok && leader) {
       const float v = t * a * slope_g;
-      grad_el[e * H + h] = v;
-      grad_er[e * H + h] = v;
+      if (elidx) atomicAdd(grad_el + __ldg(elidx + e) * H + h, v);
+      else grad_el[e * H + h] = v;
+      if (eridx) atomicAdd(grad_er + __ldg(eridx + e) * H + h, v);
+      else grad_er[e * H + h] = v;
     }
   }
 }
@@ -431,7 +459,8 @@ __global__ void __launch_bounds__(kThreads)
                              const int64_t *__restrict__ eids, int64_t E,
                              const float *__restrict__ norm,
                              const float *__restrict__ gout,
-                             float *__restrict__ grad_msg, int H, int hw) {
+                             float *__restrict__ grad_msg, int H, int hw,
+                             const int64_t *__restrict__ midx) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -442,8 +471,9 @@ __global__ void __launch_bounds__(kThreads)
     const int64_t d = __ldg(dst_idx + i);
     const float a = __ldg(norm + e * H + h);
     const float4 go = ldg4(gout + d * D + 4 * l);
-    stcs4(grad_msg + e * D + 4 * l,
-          make_float4(a * go.x, a * go.y, a * go.z, a * go.w));
+    const float4 gm = make_float4(a * go.x, a * go.y, a * go.z, a * go.w);
+    if (midx) red_add4(grad_msg + __ldg(midx + e) * D + 4 * l, gm);  // compact row: summed
+    else stcs4(grad_msg + e * D + 4 * l, gm);
   }
 }
 
@@ -464,7 +494,7 @@ __global__ void __launch_bounds__(kThreads)
                            const float *__restrict__ mu,
                            float *__restrict__ grad_attn,
                            float *__restrict__ grad_mu, int H, int hw,
-                           int use_smem) {
+                           int use_smem, const int64_t *__restrict__ midx) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   extern __shared__ float mu_acc[];
@@ -489,7 +519,7 @@ __global__ void __launch_bounds__(kThreads)
       const int64_t d = __ldg(dst_idx + i);
       const float4 go = ldg4(gout + d * D + 4 * l);
       const float4 ov = ldg4(out + d * D + 4 * l);
-      const float4 mv = ldcs4(msg + e * D + 4 * l);
+      const float4 mv = midx ? ldg4(msg + __ldg(midx + e) * D + 4 * l) : ldcs4(msg + e * D + 4 * l);
       s = go.x * (mv.x - ov.x) + go.y * (mv.y - ov.y) + go.z * (mv.z - ov.z) +
           go.w * (mv.w - ov.w);
     }
@@ -598,10 +628,12 @@ extern "C" int hetb_rgat_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
                                  const float *feat, const float *el,
                                  const float *er, float *sum, float *exp_out,
                                  float *ret, int H, int F, float slope,
-                                 void *stream) {
+                                 const hetb_compact_idx *cidx, void *stream) {
   HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0);
   if (num_rows == 0) return HETB_OK;
   HETB_CHECK_ARG(row_ptr && sum && ret);
+  const hetb_compact_idx none = {nullptr, nullptr, nullptr};
+  const hetb_compact_idx ci = cidx ? *cidx : none;
   HETB_CHECK_ARG(num_edges == 0 || (eids && feat && el && er && exp_out));
   const int lpr = lanes_per_row(H, F);
   if (!lpr) return HETB_EUNSUPPORTED;
@@ -615,7 +647,7 @@ extern "C" int hetb_rgat_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
   const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
   DISPATCH_LPR(lpr, (chunk_aggregate_kernel<L, 0><<<(unsigned)grid, kThreads, 0, st>>>(
                         row_ptr, eids, num_rows, num_edges, feat, el, er, sum,
-                        exp_out, ret, H, F / 4, slope, 0)));
+                        exp_out, ret, H, F / 4, slope, 0, ci.feat_idx, ci.el_idx, ci.er_idx)));
   HETB_LAUNCH_OK();
   DISPATCH_LPR(lpr, (agg_normalize_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
                         row_ptr, num_rows, sum, ret, H, F / 4)));
@@ -628,7 +660,8 @@ extern "C" int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr,
                                           int64_t num_edges, const float *msg,
                                           const float *score, const float *sum,
                                           float *ret, int H, int F,
-                                          int divide_by_sum, void *stream) {
+                                          int divide_by_sum,
+                                          const int64_t *msg_idx, void *stream) {
   HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0);
   if (num_rows == 0) return HETB_OK;
   HETB_CHECK_ARG(row_ptr && ret && (!divide_by_sum || sum));
@@ -646,7 +679,7 @@ extern "C" int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr,
   DISPATCH_LPR(lpr, (chunk_aggregate_kernel<L, 1><<<(unsigned)grid, kThreads, 0, st>>>(
                         row_ptr, eids, num_rows, num_edges, msg, score, nullptr,
                         const_cast<float *>(sum), nullptr, ret, H, F / 4, 0.f,
-                        divide_by_sum)));
+                        divide_by_sum, msg_idx, nullptr, nullptr)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -690,7 +723,8 @@ extern "C" int hetb_hgt_edge_softmax_fwd_csr(
 }
 
 extern "C" int hetb_inner_product_fwd(const int64_t *eids,
-                                      const int64_t *row_idx, int64_t num_edges,
+                                      const int64_t *row_idx,
+                                      const int64_t *left_idx, int64_t num_edges,
                                       const float *left, const float *right,
                                       float *out, int H, int F, void *stream) {
   HETB_CHECK_ARG(num_edges >= 0);
@@ -701,13 +735,14 @@ extern "C" int hetb_inner_product_fwd(const int64_t *eids,
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = edge_grid(num_edges, kThreads / lpr);
   DISPATCH_LPR(lpr, (inner_product_fwd_kernel<L><<<grid, kThreads, 0, st>>>(
-                        eids, row_idx, num_edges, left, right, out, H, F / 4)));
+                        eids, row_idx, left_idx, num_edges, left, right, out, H, F / 4)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
 
 extern "C" int hetb_inner_product_bwd(const int64_t *eids,
-                                      const int64_t *row_idx, int64_t num_edges,
+                                      const int64_t *row_idx,
+                                      const int64_t *left_idx, int64_t num_edges,
                                       const float *left, const float *right,
                                       const float *grad_out, float *grad_left,
                                       float *grad_right, int H, int F,
@@ -721,7 +756,7 @@ extern "C" int hetb_inner_product_bwd(const int64_t *eids,
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = edge_grid(num_edges, kThreads / lpr);
   DISPATCH_LPR(lpr, (inner_product_bwd_kernel<L><<<grid, kThreads, 0, st>>>(
-                        eids, row_idx, num_edges, left, right, grad_out,
+                        eids, row_idx, left_idx, num_edges, left, right, grad_out,
                         grad_left, grad_right, H, F / 4)));
   HETB_LAUNCH_OK();
   return HETB_OK;
@@ -733,9 +768,11 @@ extern "C" int hetb_rgat_bwd(const int64_t *dst_idx, const int64_t *eids,
                              const float *exp_in, const float *ret,
                              const float *gout, float *grad_feat,
                              float *grad_el, float *grad_er, int H, int F,
-                             float slope, void *stream) {
+                             float slope, const hetb_compact_idx *cidx, void *stream) {
   HETB_CHECK_ARG(num_edges >= 0);
   if (num_edges == 0) return HETB_OK;
+  const hetb_compact_idx none = {nullptr, nullptr, nullptr};
+  const hetb_compact_idx ci = cidx ? *cidx : none;
   HETB_CHECK_ARG(dst_idx && eids && feat && el && er && sum && exp_in && ret &&
                  gout && grad_feat && grad_el && grad_er);
   const int lpr = lanes_per_row(H, F);
@@ -745,7 +782,7 @@ extern "C" int hetb_rgat_bwd(const int64_t *dst_idx, const int64_t *eids,
   DISPATCH_LPR(lpr, (rgat_bwd_kernel<L><<<grid, kThreads, 0, st>>>(
                         dst_idx, eids, num_edges, feat, el, er, sum, exp_in,
                         ret, gout, grad_feat, grad_el, grad_er, H, F / 4,
-                        slope)));
+                        slope, ci.feat_idx, ci.el_idx, ci.er_idx)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -754,7 +791,7 @@ extern "C" int hetb_hgt_aggregate_bwd(const int64_t *dst_idx,
                                       const int64_t *eids, int64_t num_edges,
                                       const float *norm, const float *gout,
                                       float *grad_msg, int H, int F,
-                                      void *stream) {
+                                      const int64_t *msg_idx, void *stream) {
   HETB_CHECK_ARG(num_edges >= 0);
   if (num_edges == 0) return HETB_OK;
   HETB_CHECK_ARG(dst_idx && eids && norm && gout && grad_msg);
@@ -764,7 +801,7 @@ extern "C" int hetb_hgt_aggregate_bwd(const int64_t *dst_idx,
   const int grid = edge_grid(num_edges, kThreads / lpr);
   DISPATCH_LPR(lpr, (hgt_aggregate_bwd_kernel<L><<<grid, kThreads, 0, st>>>(
                         dst_idx, eids, num_edges, norm, gout, grad_msg, H,
-                        F / 4)));
+                        F / 4, msg_idx)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -773,7 +810,7 @@ extern "C" int hetb_hgt_edge_softmax_bwd(
     const int64_t *dst_idx, const int64_t *eids, const int64_t *rel,
     int64_t num_edges, int64_t num_rels, const float *msg, const float *attn,
     const float *norm, const float *out, const float *gout, const float *mu,
-    float *grad_attn, float *grad_mu, int H, int F, void *stream) {
+    float *grad_attn, float *grad_mu, int H, int F, const int64_t *msg_idx, void *stream) {
   HETB_CHECK_ARG(num_edges >= 0 && num_rels >= 0);
   if (num_edges == 0) return HETB_OK;
   HETB_CHECK_ARG(dst_idx && eids && rel && msg && attn && norm && out && gout &&
@@ -789,7 +826,7 @@ extern "C" int hetb_hgt_edge_softmax_bwd(
   DISPATCH_LPR(lpr, (hgt_softmax_bwd_kernel<L><<<grid, kThreads, smem, st>>>(
                         dst_idx, eids, rel, num_edges, (int)num_rels, msg, attn,
                         norm, out, gout, mu, grad_attn, grad_mu, H, F / 4,
-                        use_smem)));
+                        use_smem, msg_idx)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -227,14 +227,21 @@ void rgnn_inner_product_right_node_separatecoo(
     Tensor &row_indices, Tensor &col_indices, Tensor &left_side_data,
     Tensor &right_node_vectors, Tensor &edge_inner_product) {
   const char *op = "rgnn_inner_product_right_node_separatecoo";
-  (void)args; (void)rel_ptrs; (void)col_indices;
-  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  (void)rel_ptrs; (void)col_indices;
+  // kind 0: per-edge left data; kind 2 (EnabledWithDirectIndexing): compact left rows addressed
+  // through args["edata_idx_to_inverse_idx"]; kind 1 (binary search in the unique lists) is not built
+  if (kind != 0 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
+  const int64_t *left_idx = nullptr;
+  if (kind == 2) {
+    TORCH_CHECK(args.contains("edata_idx_to_inverse_idx"), op, ": kind 2 needs args[edata_idx_to_inverse_idx]");
+    left_idx = i64(args.at("edata_idx_to_inverse_idx"), op, "edata_idx_to_inverse_idx");
+  }
   TORCH_CHECK(right_node_vectors.dim() == 3, op,
               ": right_node_vectors must be [N,H,F]");
   const int H = (int)right_node_vectors.size(1), F = (int)right_node_vectors.size(2);
   c10::cuda::CUDAGuard guard(edge_inner_product.device());
   check_rc(hetb_inner_product_fwd(
-               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"),
+               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"), left_idx,
                eids.numel(), f32(left_side_data, op, "left_side_data"),
                f32(right_node_vectors, op, "right_node_vectors"),
                f32w(edge_inner_product, op, "edge_inner_product"), H, F,
@@ -249,12 +256,17 @@ void backward_inner_product_right_node_separatecoo(
     Tensor &right_node_vectors, Tensor &grad_inner_product,
     Tensor &grad_left_side_data, Tensor &grad_right_node_vectors) {
   const char *op = "backward_inner_product_right_node_separatecoo";
-  (void)args; (void)rel_ptrs; (void)col_indices;
-  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
+  (void)rel_ptrs; (void)col_indices;
+  if (kind != 0 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
+  const int64_t *left_idx = nullptr;
+  if (kind == 2) {
+    TORCH_CHECK(args.contains("edata_idx_to_inverse_idx"), op, ": kind 2 needs args[edata_idx_to_inverse_idx]");
+    left_idx = i64(args.at("edata_idx_to_inverse_idx"), op, "edata_idx_to_inverse_idx");
+  }
   const int H = (int)right_node_vectors.size(1), F = (int)right_node_vectors.size(2);
   c10::cuda::CUDAGuard guard(grad_inner_product.device());
   check_rc(hetb_inner_product_bwd(
-               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"),
+               i64(eids, op, "eids"), i64(row_indices, op, "row_indices"), left_idx,
                eids.numel(), f32(left_side_data, op, "left_side_data"),
                f32(right_node_vectors, op, "right_node_vectors"),
                f32(grad_inner_product, op, "grad_inner_product"),
@@ -276,6 +288,8 @@ void relational_fused_gat_csr(Tensor &incsr_row_ptr, Tensor &incsr_col_indices,
   const char *op = "relational_fused_gat_csr";
   (void)incsr_col_indices; (void)incsr_reltypes; (void)unique_rel_ptrs;
   (void)unique_node_indices;
+  // the binary-search compact form (unique lists) is not built; the direct-indexing form is
+  // hetb200_relational_fused_gat_csr_compact below
   if (compact_as_of_node) check_rc(HETB_EUNSUPPORTED, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(feat_src) / H);
@@ -286,7 +300,46 @@ void relational_fused_gat_csr(Tensor &incsr_row_ptr, Tensor &incsr_col_indices,
                              f32(feat_src, op, "feat_src"), f32(el, op, "el"),
                              f32(er, op, "er"), f32w(sum, op, "sum"),
                              f32w(exp, op, "exp"), f32w(ret, op, "ret"), H, F,
-                             (float)slope, stream_of(ret)),
+                             (float)slope, nullptr, stream_of(ret)),
+           op);
+}
+
+// hetb200 extension: relational_fused_gat_csr with compact-as-of-node inputs addressed by
+// direct indexing (the single-sided lists of RGAT/models.py:152-263, CompactAsOfNodeKind 4):
+// feat_src / el hold one row per unique (relation, source), er one per unique (relation,
+// destination); inverse_row / inverse_col map an edge id to its row. exp stays per edge.
+void hetb200_relational_fused_gat_csr_compact(
+    Tensor &incsr_row_ptr, Tensor &incsr_eids, Tensor &inverse_row, Tensor &inverse_col,
+    Tensor &feat_src, Tensor &el, Tensor &er, Tensor &sum, Tensor &exp, Tensor &ret, double slope) {
+  const char *op = "hetb200_relational_fused_gat_csr_compact";
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  const int64_t *ir = i64(inverse_row, op, "inverse_row"), *ic = i64(inverse_col, op, "inverse_col");
+  const hetb_compact_idx ci = {ir, ir, ic};
+  check_rc(hetb_rgat_fwd_csr(i64(incsr_row_ptr, op, "incsr_row_ptr"), i64(incsr_eids, op, "incsr_eids"),
+                             incsr_row_ptr.numel() - 1, incsr_eids.numel(), f32(feat_src, op, "feat_src"),
+                             f32(el, op, "el"), f32(er, op, "er"), f32w(sum, op, "sum"), f32w(exp, op, "exp"),
+                             f32w(ret, op, "ret"), H, F, (float)slope, &ci, stream_of(ret)),
+           op);
+}
+
+// grad_feat_src / grad_el / grad_er are compact and must arrive zero-filled (summed into).
+void hetb200_backward_relational_fused_gat_csr_compact(
+    Tensor &outcsr_col_indices, Tensor &outcsr_eids, Tensor &inverse_row, Tensor &inverse_col,
+    Tensor &feat_src, Tensor &el, Tensor &er, Tensor &sum, Tensor &exp, Tensor &ret, Tensor &gradout,
+    Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope) {
+  const char *op = "hetb200_backward_relational_fused_gat_csr_compact";
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  const int64_t *ir = i64(inverse_row, op, "inverse_row"), *ic = i64(inverse_col, op, "inverse_col");
+  const hetb_compact_idx ci = {ir, ir, ic};
+  check_rc(hetb_rgat_bwd(i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
+                         outcsr_eids.numel(), f32(feat_src, op, "feat_src"), f32(el, op, "el"), f32(er, op, "er"),
+                         f32(sum, op, "sum"), f32(exp, op, "exp"), f32(ret, op, "ret"), f32(gradout, op, "gradout"),
+                         f32w(grad_feat_src, op, "grad_feat_src"), f32w(grad_el, op, "grad_el"),
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, &ci, stream_of(gradout)),
            op);
 }
 
@@ -313,7 +366,7 @@ void backward_relational_fused_gat_csr(
                          f32(ret, op, "ret"), f32(gradout, op, "gradout"),
                          f32w(grad_feat_src, op, "grad_feat_src"),
                          f32w(grad_el, op, "grad_el"),
-                         f32w(grad_er, op, "grad_er"), H, F, (float)slope,
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, nullptr,
                          stream_of(gradout)),
            op);
 }
@@ -360,7 +413,7 @@ void backward_relational_fused_gat_separate_coo(
                          f32(gradout, op, "gradout"),
                          f32w(grad_feat_src, op, "grad_feat_src"),
                          f32w(grad_el, op, "grad_el"),
-                         f32w(grad_er, op, "grad_er"), H, F, (float)slope,
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, nullptr,
                          stream_of(gradout)),
            op);
 }
@@ -409,7 +462,25 @@ void hgt_full_graph_message_mean_aggregation_csr(
                incsr_eids.numel(), f32(edge_messages, op, "edge_messages"),
                f32(edge_attn_score, op, "edge_attn_score"),
                f32(edgesoftmax_sum_per_node, op, "edgesoftmax_sum_per_node"),
-               f32w(ret, op, "ret"), H, F, 1, stream_of(ret)),
+               f32w(ret, op, "ret"), H, F, 1, nullptr, stream_of(ret)),
+           op);
+}
+
+// hetb200 extension: the same aggregation with edge_messages holding one row per unique
+// (relation, source) pair (compact-as-of-node, direct indexing: msg_idx[eid] is the row).
+void hetb200_hgt_message_aggregation_csr_compact(
+    Tensor &incsr_row_ptrs, Tensor &incsr_eids, Tensor &msg_idx, Tensor &messages_compact,
+    Tensor &edge_attn_score, Tensor &edgesoftmax_sum_per_node, Tensor &ret) {
+  const char *op = "hetb200_hgt_message_aggregation_csr_compact";
+  const int H = (int)xlen(edge_attn_score);
+  const int F = (int)(xlen(messages_compact) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_hgt_aggregate_fwd_csr(
+               i64(incsr_row_ptrs, op, "incsr_row_ptrs"), i64(incsr_eids, op, "incsr_eids"),
+               incsr_row_ptrs.numel() - 1, incsr_eids.numel(), f32(messages_compact, op, "messages_compact"),
+               f32(edge_attn_score, op, "edge_attn_score"),
+               f32(edgesoftmax_sum_per_node, op, "edgesoftmax_sum_per_node"), f32w(ret, op, "ret"), H, F, 1,
+               i64(msg_idx, op, "msg_idx"), stream_of(ret)),
            op);
 }
 
@@ -429,7 +500,23 @@ void backward_hgt_full_graph_message_mean_aggregation_csr(
                i64(outcsr_eids, op, "outcsr_eids"), outcsr_eids.numel(),
                f32(normalized_attn_score, op, "normalized_attn_score"),
                f32(gradout, op, "gradout"), f32w(grad_message, op, "grad_message"),
-               H, F, stream_of(gradout)),
+               H, F, nullptr, stream_of(gradout)),
+           op);
+}
+
+// hetb200 extension: grad_message is compact ([unique (rel, src), H, F], zero-filled on entry)
+void hetb200_backward_hgt_message_aggregation_csr_compact(
+    Tensor &outcsr_col_indices, Tensor &outcsr_eids, Tensor &msg_idx, Tensor &normalized_attn_score,
+    Tensor &gradout, Tensor &grad_message_compact) {
+  const char *op = "hetb200_backward_hgt_message_aggregation_csr_compact";
+  const int H = (int)xlen(normalized_attn_score);
+  const int F = (int)(xlen(grad_message_compact) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_aggregate_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
+               outcsr_eids.numel(), f32(normalized_attn_score, op, "normalized_attn_score"),
+               f32(gradout, op, "gradout"), f32w(grad_message_compact, op, "grad_message_compact"), H, F,
+               i64(msg_idx, op, "msg_idx"), stream_of(gradout)),
            op);
 }
 
@@ -453,7 +540,27 @@ void backward_hgt_full_graph_edge_softmax_ops_csr(
                f32(normalized_attn_score, op, "normalized_attn_score"),
                f32(out, op, "out"), f32(gradout, op, "gradout"),
                f32(mu, op, "mu"), f32w(grad_attn_score, op, "grad_attn_score"),
-               f32w(grad_mu, op, "grad_mu"), H, F, stream_of(gradout)),
+               f32w(grad_mu, op, "grad_mu"), H, F, nullptr, stream_of(gradout)),
+           op);
+}
+
+// hetb200 extension: message is compact (see hetb200_hgt_message_aggregation_csr_compact)
+void hetb200_backward_hgt_edge_softmax_ops_csr_compact(
+    Tensor &outcsr_col_indices, Tensor &outcsr_eids, Tensor &outcsr_reltypes, Tensor &msg_idx,
+    Tensor &messages_compact, Tensor &unnormalized_attn_score, Tensor &normalized_attn_score, Tensor &out,
+    Tensor &gradout, Tensor &mu, Tensor &grad_attn_score, Tensor &grad_mu) {
+  const char *op = "hetb200_backward_hgt_edge_softmax_ops_csr_compact";
+  const int H = (int)xlen(unnormalized_attn_score);
+  const int F = (int)(xlen(messages_compact) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_edge_softmax_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
+               i64(outcsr_reltypes, op, "outcsr_reltypes"), outcsr_eids.numel(), mu.size(0),
+               f32(messages_compact, op, "messages_compact"),
+               f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
+               f32(normalized_attn_score, op, "normalized_attn_score"), f32(out, op, "out"),
+               f32(gradout, op, "gradout"), f32(mu, op, "mu"), f32w(grad_attn_score, op, "grad_attn_score"),
+               f32w(grad_mu, op, "grad_mu"), H, F, i64(msg_idx, op, "msg_idx"), stream_of(gradout)),
            op);
 }
 
@@ -658,6 +765,12 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("backward_relational_fused_gat_separate_coo",
         backward_relational_fused_gat_separate_coo);
   // HGT (OpExport/HGTOps.inc.h:656-674)
+  m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);
+  m.def("hetb200_backward_relational_fused_gat_csr_compact", hetb200_backward_relational_fused_gat_csr_compact);
+  m.def("hetb200_hgt_message_aggregation_csr_compact", hetb200_hgt_message_aggregation_csr_compact);
+  m.def("hetb200_backward_hgt_message_aggregation_csr_compact",
+        hetb200_backward_hgt_message_aggregation_csr_compact);
+  m.def("hetb200_backward_hgt_edge_softmax_ops_csr_compact", hetb200_backward_hgt_edge_softmax_ops_csr_compact);
   m.def("hgt_full_graph_edge_softmax_ops_csr",
         hgt_full_graph_edge_softmax_ops_csr);
   m.def("hgt_full_graph_message_mean_aggregation_csr",

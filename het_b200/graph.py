@@ -85,9 +85,41 @@ class HetGraph:
         return self.node_type_offsets
 
     def get_separate_unique_node_indices(self):
-        # compact-as-of-node lists (kinds 1-4) are a later §8(f) row; the
+        # the double-sided lists (binary-search compact kinds) are not built; the
         # non-compact ops ignore these tensors.
         return {"rel_ptrs": self._empty, "node_indices": self._empty}
+
+    def get_separate_unique_node_indices_single_sided(self):
+        """Compact-as-of-node lists, one side at a time (reference:
+        generate_separate_unique_node_indices_single_sided_for_each_etype,
+        hrt/python/utils_lite/mydgl_graph_methods.py:11-157 — per relation
+        ``torch.unique(row or col, return_inverse=True)``, concatenated with the running
+        offsets). Built on the GPU from the relation-sorted COO in one pass per side:
+        the key (relation, node) is already grouped by relation, so a sorted unique of
+        ``rel * N + node`` yields the per-relation sorted node lists back to back.
+
+        ``rel_ptrs_<side>``      [R+1]  segment of relation r inside the compact list
+        ``node_indices_<side>``  [U]    node id of every unique (relation, node) pair
+        ``inverse_idx_<side>``   [E]    compact row of edge id e ("edata_idx_to_inverse_idx";
+                                         edge ids are separate-COO positions after canonicalisation)
+        with side ``row`` = sources, ``col`` = destinations."""
+        if getattr(self, "_unique_single_sided", None) is None:
+            coo = self.separate_coo
+            dev = coo["rel_ptrs"].device
+            counts = coo["rel_ptrs"][1:] - coo["rel_ptrs"][:-1]
+            rel_of_edge = torch.repeat_interleave(torch.arange(self.num_rels, device=dev), counts)
+            out = {}
+            for side, nodes, n in (("row", coo["row_indices"], self.num_src_nodes),
+                                   ("col", coo["col_indices"], self.num_nodes)):
+                key = rel_of_edge * n + nodes
+                uniq, inverse = torch.unique(key, sorted=True, return_inverse=True)
+                bounds = torch.arange(self.num_rels + 1, device=dev, dtype=torch.int64) * n
+                out["rel_ptrs_" + side] = torch.searchsorted(uniq, bounds).contiguous()
+                out["node_indices_" + side] = (uniq % n).contiguous()
+                # eids are 0..E-1 in separate-COO order, so position == edge id
+                out["inverse_idx_" + side] = inverse.contiguous()
+            self._unique_single_sided = out
+        return self._unique_single_sided
 
     def get_num_nodes(self):
         return self.num_nodes

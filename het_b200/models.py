@@ -29,8 +29,10 @@ class HET_RelGraphEmbed(nn.Module):
 
 class HET_RGATLayer(nn.Module):
     def __init__(self, in_feat, out_feat, num_rels, num_heads, *, bias=True, activation=None,
-                 self_loop=False, gat_edge_parallel_flag=False, dropout=0.0, leaky_relu_slope=0.2):
+                 self_loop=False, gat_edge_parallel_flag=False, dropout=0.0, leaky_relu_slope=0.2,
+                 compact_as_of_node_flag=False):
         super().__init__()
+        self.compact_as_of_node_flag = compact_as_of_node_flag
         assert out_feat % num_heads == 0, "out_feat must be a multiple of num_heads"
         self.in_feat, self.out_feat = in_feat, out_feat
         self.num_rels, self.num_heads = num_rels, num_heads
@@ -62,6 +64,9 @@ class HET_RGATLayer(nn.Module):
         tensor) by destination ids — they differ only on a destination-range shard."""
         if inputs_dst is None:
             inputs_dst = inputs
+        if self.compact_as_of_node_flag:
+            h = self._forward_compact(g, inputs, inputs_dst)
+            return self._epilogue(h, inputs_dst)
         coo = g.get_separate_coo_original()
 
         def mm(gather, w, x, head_one):
@@ -77,6 +82,31 @@ class HET_RGATLayer(nn.Module):
             h = B.relational_fused_gat_separate_coo(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
         else:
             h = B.relational_fused_gat_csr(g, feat_src_per_edge, el, er, self.leaky_relu_slope)
+        return self._epilogue(h, inputs_dst)
+
+    def _forward_compact(self, g, inputs, inputs_dst):
+        """compact_as_of_node_flag (hrt/python/RGAT/models.py:151-263): X·W_r is computed once per
+        unique (relation, source) and once per unique (relation, destination) pair instead of once
+        per edge; the logits are one row-dot per compact row; the edge phase reads the compact rows
+        through the direct-indexing maps. The reference runs its edge-parallel COO kernel here
+        (the in-CSR compact kernel "not implemented the singe side unique node idex", :254-257);
+        this uses the in-CSR walker with the same maps."""
+        u = g.get_separate_unique_node_indices_single_sided()
+        row = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
+               "unique_srcs_and_dests_node_indices": u["node_indices_row"]}
+        col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
+               "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
+        feat_compact = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
+        feat_compact_dst = B.rgnn_relational_matmul(col, self.conv_weights, inputs_dst, True, 1)
+        el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
+            u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
+        er_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
+            u["rel_ptrs_col"], self.attn_r.unsqueeze(-1), feat_compact_dst.view(feat_compact_dst.size(0), -1))
+        return B.relational_fused_gat_csr_compact(
+            g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
+            self.leaky_relu_slope)
+
+    def _epilogue(self, h, inputs_dst):
         h = h.view(-1, self.out_feat)
         if self.self_loop:
             h = h + th.matmul(inputs_dst, self.loop_weight)
@@ -106,8 +136,14 @@ class HET_RGATModel(nn.Module):
 
 
 class HET_HGTLayerHetero(nn.Module):
-    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0):
+    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
+                 compact_as_of_node_flag=False, compact_direct_indexing_flag=True):
         super().__init__()
+        # compact_as_of_node_flag (hrt/python/HGT/models.py:177-208): W_att·Q is computed once per
+        # unique (relation, destination) pair; here the same is also done for W_msg·V per unique
+        # (relation, source) pair (a hetb200 extension, same maths). Only direct indexing is built.
+        self.compact_as_of_node_flag = compact_as_of_node_flag
+        self.compact_direct_indexing_flag = compact_direct_indexing_flag
         self.in_dim, self.out_dim = in_dim, out_dim
         self.num_ntypes, self.num_relations = num_ntypes, num_rels
         self.num_heads = num_heads
@@ -145,11 +181,25 @@ class HET_HGTLayerHetero(nn.Module):
                 {"separate_coo_rel_ptrs": coo["rel_ptrs"], "separate_coo_node_indices": idx,
                  "separate_coo_eids": coo["eids"]}, w, x, False, 0)
 
-        attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
-        attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")
-        message_per_edge = mm(coo["row_indices"], self.relation_msg, v)
-        new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(
-            G, message_per_edge, attn_score, self.relation_pri / self.sqrt_dk)
+        if self.compact_as_of_node_flag:
+            if not self.compact_direct_indexing_flag:
+                raise NotImplementedError("compact_as_of_node without direct indexing (binary search)")
+            u = G.get_separate_unique_node_indices_single_sided()
+            attn_weight_dst_product_compact = B.rgnn_relational_matmul(
+                {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
+                 "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, self.relation_att, q, False, 1)
+            attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k, 2, "_col")
+            message_compact = B.rgnn_relational_matmul(
+                {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
+                 "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, self.relation_msg, v, False, 1)
+            new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(
+                G, message_compact, attn_score, self.relation_pri / self.sqrt_dk)
+        else:
+            attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
+            attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")
+            message_per_edge = mm(coo["row_indices"], self.relation_msg, v)
+            new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(
+                G, message_per_edge, attn_score, self.relation_pri / self.sqrt_dk)
         new_h = B.rgnn_relational_matmul_no_scatter_gather_list(
             offs, th.sigmoid(self.skip) * self.a_linears, new_h.view(-1, self.out_dim))
         return new_h
@@ -160,11 +210,11 @@ class HET_HGT_DGLHetero(nn.Module):
     (hrt/python/HGT/models.py:312-330, second layer commented out); the
     BASELINE "HGT 2-layer" config stacks it with ``num_layers=2``."""
 
-    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, num_layers=1, dropout=0.0):
+    def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, num_layers=1, dropout=0.0, **kw):
         super().__init__()
         dims = [in_dim] + [out_dim] * num_layers
         self.layers = nn.ModuleList(
-            HET_HGTLayerHetero(num_ntypes, num_rels, dims[i], dims[i + 1], num_heads, dropout)
+            HET_HGTLayerHetero(num_ntypes, num_rels, dims[i], dims[i + 1], num_heads, dropout, **kw)
             for i in range(num_layers))
 
     def forward(self, G, h, gather=None):

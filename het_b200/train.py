@@ -30,7 +30,8 @@ from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel
 
 class FullGraphTrainer:
     def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
-                 layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0):
+                 layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0,
+                 compact_as_of_node=False):
         assert kind in ("rgat", "hgt")
         self.kind, self.device, self.rank, self.world, self.group = kind, torch.device(device), rank, world, group
         self.num_nodes_total = coo.num_nodes
@@ -45,12 +46,16 @@ class FullGraphTrainer:
             self.g = HetGraph(coo, self.device)
             self.n_local, self.lo = coo.num_nodes, 0
         self.num_edges_local = self.g.num_edges
+        if compact_as_of_node:  # build the unique (relation, node) lists now, outside any graph capture
+            self.g.get_separate_unique_node_indices_single_sided()
 
         torch.manual_seed(seed)  # identical replicated weights on every rank
         if kind == "rgat":
-            self.model = HET_RGATModel(coo.num_rels, hidden, hidden, out_dim, heads, layers).to(self.device)
+            self.model = HET_RGATModel(coo.num_rels, hidden, hidden, out_dim, heads, layers,
+                                       compact_as_of_node_flag=compact_as_of_node).to(self.device)
         else:
-            self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers).to(self.device)
+            self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
+                                           compact_as_of_node_flag=compact_as_of_node).to(self.device)
         gen = torch.Generator().manual_seed(seed + 1)
         embed_full = torch.rand(coo.num_nodes, hidden, generator=gen) * 2 - 1
         labels_full = torch.randint(0, out_dim, (coo.num_nodes,), generator=gen)

@@ -87,21 +87,29 @@ int hetb_segment_mm_grad_w(const float *A, const int64_t *a_idx, int a_heads,
  * Edge-wise inner product (HGT attention score)
  * ---------------------------------------------------------------------- */
 
-/* out[eids[i], h] = Σ_f left[eids[i], h, f] · right[row_idx[i], h, f]
- * Replaces rgnn_inner_product_right_node_separatecoo, kind 0
+/* out[eids[i], h] = Σ_f left[L(i), h, f] · right[row_idx[i], h, f]
+ * with L(i) = eids[i] (kind 0: left is per-edge data) or left_idx[eids[i]] when
+ * left_idx != NULL (CompactAsOfNodeKind::EnabledWithDirectIndexing, kind 2: left
+ * holds one row per unique (relation, node) pair and left_idx is the reference's
+ * "edata_idx_to_inverse_idx", kernel_enums.h:6-119).
+ * Replaces rgnn_inner_product_right_node_separatecoo, kinds 0 and 2
  * (RGNNOps.inc.h:609-658 → RGNN/InnerProductEdgeParallel.cu.h:13-113). */
 int hetb_inner_product_fwd(const int64_t *eids, const int64_t *row_idx,
+                           const int64_t *left_idx,
                            int64_t num_edges, const float *left,
                            const float *right, float *out, int H, int F,
                            void *stream);
 
-/* grad_left[eids[i],h,:]  = g[eids[i],h] · right[row_idx[i],h,:]
- * grad_right[row_idx[i],h,:] += g[eids[i],h] · left[eids[i],h,:]   (summed —
+/* grad_left[L(i),h,:]  (=|+=) g[eids[i],h] · right[row_idx[i],h,:]   (plain store for
+ *   per-edge left data; summed into the compact row, which must arrive zero-filled,
+ *   when left_idx != NULL)
+ * grad_right[row_idx[i],h,:] += g[eids[i],h] · left[L(i),h,:]   (summed —
  * the reference stores instead of accumulating, InnerProductEdgeParallel.cu.h:180-183,
  * a known bug we do not reproduce).  grad_right must arrive zero-filled.
  * Replaces backward_inner_product_right_node_separatecoo
  * (RGNNOps.inc.h:1131-1181 → InnerProductEdgeParallel.cu.h:119-202). */
 int hetb_inner_product_bwd(const int64_t *eids, const int64_t *row_idx,
+                           const int64_t *left_idx,
                            int64_t num_edges, const float *left,
                            const float *right, const float *grad_out,
                            float *grad_left, float *grad_right, int H, int F,
@@ -110,6 +118,17 @@ int hetb_inner_product_bwd(const int64_t *eids, const int64_t *row_idx,
 /* ------------------------------------------------------------------------
  * RGAT edge attention pipeline (logits → edge softmax → aggregation)
  * ---------------------------------------------------------------------- */
+
+/* Compact-as-of-node with direct indexing (CompactAsOfNodeKind 2 / 4,
+ * hrt/include/kernel_enums.h:6-48; "edata_idx_to_inverse_idx[_row|_col]"): when a
+ * pointer is non-NULL the corresponding tensor holds one row per unique
+ * (relation, node) pair instead of one per edge, and row X_idx[e] is the one edge id e
+ * uses. Gradients of a compact tensor are SUMMED into it (it must arrive zero-filled). */
+typedef struct hetb_compact_idx {
+  const int64_t *feat_idx; /* feat / grad_feat rows  (by source:      ..._row) */
+  const int64_t *el_idx;   /* el / grad_el rows      (by source:      ..._row) */
+  const int64_t *er_idx;   /* er / grad_er rows      (by destination: ..._col) */
+} hetb_compact_idx;
 
 /* Over in-CSR rows d (destinations), positions p in [row_ptr[d], row_ptr[d+1]):
  *   e = eids[p];  x = el[e,h] + er[e,h];
@@ -123,6 +142,7 @@ int hetb_rgat_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
                       int64_t num_rows, int64_t num_edges, const float *feat,
                       const float *el, const float *er, float *sum,
                       float *exp_out, float *ret, int H, int F, float slope,
+                      const hetb_compact_idx *cidx /* NULL: per-edge inputs */,
                       void *stream);
 
 /* Edge-parallel twin over a COO (dst = col_idx[i], e = eids[i]); same outputs.
@@ -150,6 +170,7 @@ int hetb_rgat_bwd(const int64_t *dst_idx, const int64_t *eids,
                   const float *er, const float *sum, const float *exp_in,
                   const float *ret, const float *gout, float *grad_feat,
                   float *grad_el, float *grad_er, int H, int F, float slope,
+                  const hetb_compact_idx *cidx /* NULL: per-edge tensors */,
                   void *stream);
 
 /* ------------------------------------------------------------------------
@@ -176,7 +197,9 @@ int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
                                int64_t num_rows, int64_t num_edges,
                                const float *msg, const float *score,
                                const float *sum, float *ret, int H, int F,
-                               int divide_by_sum, void *stream);
+                               int divide_by_sum,
+                               const int64_t *msg_idx /* NULL, or compact msg row per edge id */,
+                               void *stream);
 
 /* grad_msg[e,h,:] = norm[e,h] · gout[dst_idx[p],h,:]
  * Replaces backward_hgt_full_graph_message_mean_aggregation_csr
@@ -184,6 +207,7 @@ int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
 int hetb_hgt_aggregate_bwd(const int64_t *dst_idx, const int64_t *eids,
                            int64_t num_edges, const float *norm,
                            const float *gout, float *grad_msg, int H, int F,
+                           const int64_t *msg_idx /* non-NULL: grad_msg is compact, summed */,
                            void *stream);
 
 /* s = Σ_f gout[d,h,f]·(msg[e,h,f] − out[d,h,f]) · norm[e,h]
@@ -199,7 +223,9 @@ int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
                               const float *attn, const float *norm,
                               const float *out, const float *gout,
                               const float *mu, float *grad_attn,
-                              float *grad_mu, int H, int F, void *stream);
+                              float *grad_mu, int H, int F,
+                              const int64_t *msg_idx /* NULL, or compact msg row per edge id */,
+                              void *stream);
 
 /* ------------------------------------------------------------------------
  * Relation sort / CSR construction (bit-exact integer work, on the GPU)

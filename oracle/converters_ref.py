@@ -92,3 +92,25 @@ def canonicalize_eids(separate_coo_eids, *other_eid_arrays):
     remap = np.empty(separate_coo_eids.size, dtype=I64)
     remap[separate_coo_eids] = np.arange(separate_coo_eids.size, dtype=I64)
     return (np.arange(separate_coo_eids.size, dtype=I64),) + tuple(remap[a] for a in other_eid_arrays)
+
+
+def unique_node_indices_single_sided_ref(rel_ptrs, row_indices, col_indices):
+    """generate_separate_unique_node_indices_single_sided_for_each_etype
+    (hrt/python/utils_lite/mydgl_graph_methods.py:11-157): for every relation, the sorted unique
+    sources (``_row``) / destinations (``_col``) of its edges with the inverse map, concatenated
+    with running offsets. Edge ids are separate-COO positions (canonicalised), so the inverse map
+    in COO order is the reference's ``edata_idx_to_inverse_idx``."""
+    out = {}
+    R = len(rel_ptrs) - 1
+    for side, nodes in (("row", row_indices), ("col", col_indices)):
+        ptrs, lists, inv = [0], [], np.empty(len(nodes), dtype=np.int64)
+        for r in range(R):
+            a, b = int(rel_ptrs[r]), int(rel_ptrs[r + 1])
+            uniq, inverse = np.unique(nodes[a:b], return_inverse=True)
+            inv[a:b] = inverse + ptrs[-1]
+            lists.append(uniq)
+            ptrs.append(ptrs[-1] + len(uniq))
+        out["rel_ptrs_" + side] = np.asarray(ptrs, dtype=np.int64)
+        out["node_indices_" + side] = (np.concatenate(lists) if lists else np.empty(0)).astype(np.int64)
+        out["inverse_idx_" + side] = inv
+    return out

@@ -22,14 +22,18 @@ def _coo_t(coo):
     return torch.from_numpy(coo.src), torch.from_numpy(coo.dst), torch.from_numpy(coo.etype)
 
 
-@pytest.mark.parametrize("shape,scale,heads,edge_parallel", [
-    ("aifb", 1.0, 1, False), ("bgs", 0.1, 1, False), ("bgs", 0.05, 4, False), ("aifb", 0.5, 1, True),
+@pytest.mark.parametrize("shape,scale,heads,edge_parallel,compact", [
+    ("aifb", 1.0, 1, False, False), ("bgs", 0.1, 1, False, False), ("bgs", 0.05, 4, False, False),
+    ("aifb", 0.5, 1, True, False),
+    # compact_as_of_node_flag: X.W_r once per unique (relation, node) pair, direct indexing
+    ("aifb", 1.0, 1, False, True), ("bgs", 0.1, 1, False, True), ("bgs", 0.05, 4, False, True),
 ])
-def test_rgat_layer_fwd_bwd(cuda, shape, scale, heads, edge_parallel):
+def test_rgat_layer_fwd_bwd(cuda, shape, scale, heads, edge_parallel, compact):
     from het_b200.models import HET_RGATLayer
     coo, g = _graph(cuda, shape, scale)
     torch.manual_seed(0)
-    layer = HET_RGATLayer(64, 64, coo.num_rels, heads, gat_edge_parallel_flag=edge_parallel).to(cuda)
+    layer = HET_RGATLayer(64, 64, coo.num_rels, heads, gat_edge_parallel_flag=edge_parallel,
+                          compact_as_of_node_flag=compact).to(cuda)
     with torch.no_grad():
         layer.h_bias.uniform_(-0.1, 0.1)
     x = (torch.rand(coo.num_nodes, 64, device=cuda) * 2 - 1).requires_grad_(True)
@@ -48,12 +52,16 @@ def test_rgat_layer_fwd_bwd(cuda, shape, scale, heads, edge_parallel):
         close(v.grad, p[k].grad, f"rgat grad {k}", rtol=5e-4, atol=5e-5)
 
 
-@pytest.mark.parametrize("scale,heads,layers", [(0.002, 4, 1), (0.005, 1, 1), (0.002, 4, 2)])
-def test_hgt_layer_fwd_bwd(cuda, scale, heads, layers):
+@pytest.mark.parametrize("scale,heads,layers,compact", [
+    (0.002, 4, 1, False), (0.005, 1, 1, False), (0.002, 4, 2, False),
+    (0.002, 4, 1, True), (0.005, 1, 1, True), (0.002, 4, 2, True),   # compact_as_of_node_flag
+])
+def test_hgt_layer_fwd_bwd(cuda, scale, heads, layers, compact):
     from het_b200.models import HET_HGT_DGLHetero
     coo, g = _graph(cuda, "mag", scale)
     torch.manual_seed(1)
-    model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, 64, 64, heads, num_layers=layers).to(cuda)
+    model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, 64, 64, heads, num_layers=layers,
+                              compact_as_of_node_flag=compact).to(cuda)
     with torch.no_grad():
         for layer in model.layers:
             layer.relation_pri.uniform_(0.5, 1.5)
@@ -79,3 +87,17 @@ def test_hgt_layer_fwd_bwd(cuda, scale, heads, layers):
     for layer, p in zip(model.layers, ps):
         for k, v in layer.named_parameters():
             close(v.grad, p[k].grad, f"hgt grad {k}", rtol=1e-3, atol=1e-4)
+
+
+def test_unique_node_indices_single_sided(cuda):
+    """The compact-as-of-node lists (per relation: sorted unique sources / destinations, and the
+    edge -> compact row map) are bit-exact against the numpy restatement of the reference's
+    per-relation torch.unique (hrt/python/utils_lite/mydgl_graph_methods.py:11-157)."""
+    from oracle import converters_ref as C
+    coo, g = _graph(cuda, "bgs", 0.05)
+    u = g.get_separate_unique_node_indices_single_sided()
+    sc = g.get_separate_coo_original()
+    ref = C.unique_node_indices_single_sided_ref(sc["rel_ptrs"].cpu().numpy(), sc["row_indices"].cpu().numpy(),
+                                                 sc["col_indices"].cpu().numpy())
+    for k, v in ref.items():
+        assert torch.equal(u[k].cpu(), torch.from_numpy(v)), k
