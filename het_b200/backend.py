@@ -409,3 +409,29 @@ def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(graph, 
         incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["col_indices"],
         outcsr["eids"], outcsr["rel_types"], uniq["inverse_idx_row"], unnormalized_attn_score.contiguous(),
         mu.contiguous(), ssum, t, norm, message_compact.contiguous(), new_h)
+
+
+class SoftmaxCrossEntropy(th.autograd.Function):
+    """loss = nll_loss(log_softmax(logits), labels, reduction="sum") / denom in one pass
+    (the loss of HET_RGNN_train, hrt/python/RGNNUtils/RGNNUtils.py:291-345)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, denom):
+        logits = logits.contiguous()
+        lse = logits.new_empty(logits.size(0))
+        loss = logits.new_empty(())
+        K.hetb200_softmax_cross_entropy(logits, labels, float(denom), lse, loss)
+        ctx.save_for_backward(logits, labels, lse)
+        ctx.denom = float(denom)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        logits, labels, lse = ctx.saved_tensors
+        grad = th.empty_like(logits)
+        K.hetb200_backward_softmax_cross_entropy(logits, labels, lse, grad_loss.contiguous(), ctx.denom, grad)
+        return grad, None, None
+
+
+def softmax_cross_entropy(logits, labels, denom):
+    return SoftmaxCrossEntropy.apply(logits, labels, denom)

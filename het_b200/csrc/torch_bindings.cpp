@@ -564,6 +564,27 @@ void hetb200_backward_hgt_edge_softmax_ops_csr_compact(
            op);
 }
 
+// ---------------------------------------------------------------- loss ---
+// hetb200 extension: fused log_softmax + nll_loss (sum / denom) of the training step.
+void hetb200_softmax_cross_entropy(Tensor &logits, Tensor &labels, double denom, Tensor &lse, Tensor &loss) {
+  const char *op = "hetb200_softmax_cross_entropy";
+  TORCH_CHECK(logits.dim() == 2, op, ": logits must be [N,C]");
+  c10::cuda::CUDAGuard guard(logits.device());
+  check_rc(hetb_softmax_xent_fwd(f32(logits, op, "logits"), i64(labels, op, "labels"), logits.size(0),
+                                 (int)logits.size(1), (float)denom, f32w(lse, op, "lse"), f32w(loss, op, "loss"),
+                                 stream_of(logits)),
+           op);
+}
+void hetb200_backward_softmax_cross_entropy(Tensor &logits, Tensor &labels, Tensor &lse, Tensor &grad_loss,
+                                            double denom, Tensor &grad_logits) {
+  const char *op = "hetb200_backward_softmax_cross_entropy";
+  c10::cuda::CUDAGuard guard(logits.device());
+  check_rc(hetb_softmax_xent_bwd(f32(logits, op, "logits"), i64(labels, op, "labels"), f32(lse, op, "lse"),
+                                 f32(grad_loss, op, "grad_loss"), logits.size(0), (int)logits.size(1),
+                                 (float)denom, f32w(grad_logits, op, "grad_logits"), stream_of(logits)),
+           op);
+}
+
 // ---------------------------------------------------------- converters ---
 // The reference requires CPU tensors (DataConverters.inc.h asserts
 // device().is_cpu()); here CPU inputs are staged to the current CUDA device,
@@ -765,6 +786,8 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("backward_relational_fused_gat_separate_coo",
         backward_relational_fused_gat_separate_coo);
   // HGT (OpExport/HGTOps.inc.h:656-674)
+  m.def("hetb200_softmax_cross_entropy", hetb200_softmax_cross_entropy);
+  m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);
   m.def("hetb200_backward_relational_fused_gat_csr_compact", hetb200_backward_relational_fused_gat_csr_compact);
   m.def("hetb200_hgt_message_aggregation_csr_compact", hetb200_hgt_message_aggregation_csr_compact);

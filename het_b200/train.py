@@ -22,6 +22,7 @@ import torch
 import torch.distributed as dist
 import torch.nn.functional as Fn
 
+from . import backend as B
 from . import parallel
 from .graph import HetGraph
 from .graphs import HeteroCOO
@@ -68,8 +69,8 @@ class FullGraphTrainer:
 
         cap = bool(cuda_graph)
         self.opt_embed = torch.optim.Adam(list(self.model.parameters()) + list(self.embed.parameters()),
-                                          lr=lr, capturable=cap)
-        self.opt_feat = torch.optim.Adam(list(self.model.parameters()), lr=lr, capturable=cap)
+                                          lr=lr, capturable=cap, fused=True)
+        self.opt_feat = torch.optim.Adam(list(self.model.parameters()), lr=lr, capturable=cap, fused=True)
         self.cuda_graph = cap
         self._graphs = {}
         self._loss = {}
@@ -89,7 +90,8 @@ class FullGraphTrainer:
         else:
             h0, labels, opt = self.x_in, self.labels_in, self.opt_feat
         logits = self.forward(h0)
-        loss = Fn.nll_loss(Fn.log_softmax(logits, dim=-1), labels, reduction="sum") / self.num_nodes_total
+        # = Fn.nll_loss(Fn.log_softmax(logits, dim=-1), labels, reduction="sum") / num_nodes_total, fused
+        loss = B.softmax_cross_entropy(logits, labels, self.num_nodes_total)
         loss.backward()
         if self.world > 1:
             parallel.all_reduce_grads(list(self.model.parameters()), self.group)

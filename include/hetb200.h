@@ -228,6 +228,21 @@ int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
                               void *stream);
 
 /* ------------------------------------------------------------------------
+ * Loss of the full-graph training step
+ * ---------------------------------------------------------------------- */
+
+/* *loss = (1/denom) Σ_i (logsumexp(logits[i,:]) − logits[i, labels[i]]);  lse[i] is saved for the
+ * backward. Equals F.nll_loss(F.log_softmax(logits), labels, reduction="sum") / denom, the loss of
+ * HET_RGNN_train (hrt/python/RGNNUtils/RGNNUtils.py:291-345). num_classes % 4 == 0. */
+int hetb_softmax_xent_fwd(const float *logits, const int64_t *labels, int64_t num_rows,
+                          int num_classes, float denom, float *lse, float *loss, void *stream);
+
+/* grad_logits[i,c] = (*grad_loss / denom) · (exp(logits[i,c] − lse[i]) − [c == labels[i]]) */
+int hetb_softmax_xent_bwd(const float *logits, const int64_t *labels, const float *lse,
+                          const float *grad_loss, int64_t num_rows, int num_classes, float denom,
+                          float *grad_logits, void *stream);
+
+/* ------------------------------------------------------------------------
  * Relation sort / CSR construction (bit-exact integer work, on the GPU)
  * ---------------------------------------------------------------------- */
 

@@ -152,3 +152,21 @@ def test_inner_product(cuda, n, e, r, H, F):
     gl_ref, gr_ref = R.inner_product_bwd(sc["eids"].cpu(), sc["row_indices"].cpu(), left.cpu(), right.cpu(), gout.cpu())
     close(gl, gl_ref, "grad_left")
     close(gr, gr_ref, "grad_right")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,c", [(1, 64), (1000, 64), (4097, 8), (300, 128)])
+def test_softmax_cross_entropy(cuda, n, c):
+    """Fused loss of the training step vs torch's nll_loss(log_softmax) in fp64 on the CPU."""
+    import torch.nn.functional as Fn
+    from het_b200 import backend as B
+    torch.manual_seed(n + c)
+    x = (torch.randn(n, c, device=cuda) * 3).requires_grad_(True)
+    y = torch.randint(0, c, (n,), device=cuda)
+    loss = B.softmax_cross_entropy(x, y, n + 7)
+    loss.backward()
+    x64 = x.detach().double().cpu().requires_grad_(True)
+    ref = Fn.nll_loss(Fn.log_softmax(x64, dim=-1), y.cpu(), reduction="sum") / (n + 7)
+    ref.backward()
+    close(loss, ref, "loss")
+    close(x.grad, x64.grad, "grad logits", rtol=1e-4, atol=1e-6)
