@@ -55,8 +55,11 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
-    ap.add_argument("--compact", action="store_true",
-                    help="the reference's compact_as_of_node_flag: X.W_r once per unique (relation, node) pair")
+    ap.add_argument("--no-compact", dest="compact", action="store_false",
+                    help="turn off the reference's compact_as_of_node_flag (default on: X.W_r is computed once "
+                         "per unique (relation, node) pair instead of once per edge; same outputs)")
+    ap.add_argument("--no-fused", dest="fused", action="store_false",
+                    help="HGT: run inner product, edge softmax and aggregation as three ops instead of one pass")
     return ap.parse_args()
 
 
@@ -278,6 +281,102 @@ def kernel_rooflines(trainer, peak_gbs, peak_src):
     return out
 
 
+def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
+    """Same as kernel_rooflines for the compact-as-of-node path (the default): the per-edge
+    [E, 64] tensors are replaced by one row per unique (relation, node) pair, U_row / U_col rows,
+    read by the edge kernels through the direct-indexing maps. Compulsory bytes count every
+    compact / node row once (unique-row granularity), every per-edge scalar and index once."""
+    import torch
+    from het_b200.kernels import K
+    g, dev = trainer.g, trainer.device
+    E, N, Ns, R = g.num_edges, g.num_nodes, g.num_src_nodes, g.num_rels
+    coo, ic, oc = g.get_separate_coo_original(), g.get_in_csr(), g.get_out_csr()
+    u = g.get_separate_unique_node_indices_single_sided()
+    Ur, Uc = int(u["node_indices_row"].numel()), int(u["node_indices_col"].numel())
+    layer = trainer.model.layers[0]
+    H, D = layer.num_heads, 64
+    F = D // H
+    flush = torch.zeros(64 * 1024 * 1024, device=dev)
+    uniq_src = int(torch.unique(coo["row_indices"]).numel())
+    uniq_dst = int(torch.unique(coo["col_indices"]).numel())
+    out = []
+
+    def leg(name, fn, nbytes, note):
+        ms = _time_kernel(torch, fn, flush)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"kernel": name, "bound": "hbm", "achieved": round(gbs, 1), "peak": peak_gbs, "unit": "GB/s",
+                    "frac": round(gbs / peak_gbs, 4), "peak_source": peak_src, "ms": round(ms, 4),
+                    "algorithmic_bytes": int(nbytes), "traffic": None, "note": note})
+
+    x = torch.rand(Ns, D, device=dev) * 2 - 1
+    d_row = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"], "unique_srcs_and_dests_node_indices": u["node_indices_row"]}
+    d_col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"], "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
+    ir, icx = u["inverse_idx_row"], u["inverse_idx_col"]
+    if trainer.kind == "rgat":
+        W = layer.conv_weights.detach().contiguous()
+        WT = W.transpose(2, 3).contiguous()
+        feat = torch.empty(Ur, H, F, device=dev)
+        leg("segment_mm_fwd(unique (rel,src) rows, X.W_r)", lambda: K.rgnn_relational_matmul(d_row, 1, W, x, feat, True),
+            uniq_src * D * 4 + Ur * D * 4 + R * D * D * 4 + Ur * 8, "X_unique*D*s + U*D*s + R*D*D*s + U*i")
+        el, er = torch.randn(Ur, H, 1, device=dev), torch.randn(Uc, H, 1, device=dev)
+        ssum, ex, ret = torch.empty(N, H, device=dev), torch.empty(E, H, 1, device=dev), torch.empty(N, H, F, device=dev)
+        leg("rgat_edge_softmax_aggregate_fwd(in-CSR, compact)",
+            lambda: K.hetb200_relational_fused_gat_csr_compact(ic["row_ptrs"], ic["eids"], ir, icx, feat, el, er, ssum, ex,
+                                                               ret, 0.2),
+            Ur * D * 4 + (Ur + Uc) * H * 4 + 3 * E * 8 + (N + 1) * 8 + E * H * 4 + N * H * 4 + N * D * 4,
+            "feat_c + el_c,er_c + eid,inv_row,inv_col + row_ptr ; exp + sum + ret")
+        gout = torch.randn(N, H, F, device=dev)
+        gf, gel, ger = torch.zeros_like(feat), torch.zeros_like(el), torch.zeros_like(er)
+        leg("rgat_edge_bwd(out-CSR, compact)",
+            lambda: K.hetb200_backward_relational_fused_gat_csr_compact(oc["col_indices"], oc["eids"], ir, icx, feat, el, er,
+                                                                        ssum, ex, ret, gout, gf, gel, ger, 0.2),
+            2 * Ur * D * 4 + 2 * (Ur + Uc) * H * 4 + E * H * 4 + N * H * 4 + 2 * N * D * 4 + 4 * E * 8,
+            "feat_c,el_c,er_c,exp,sum,ret,gout,idx ; grad_feat_c,grad_el_c,grad_er_c")
+        gx, gw = torch.zeros_like(x), torch.zeros_like(W)
+        leg("segment_mm_bwd(unique rows: dX scatter + dW)",
+            lambda: K.backward_rgnn_relational_matmul(d_row, 1, WT, x, gf, gx, gw, True),
+            Ur * D * 4 + 2 * uniq_src * D * 4 + 2 * R * D * D * 4 + Ur * 8, "dY_c + X_unique + W ; dX_unique + dW ; list")
+    else:
+        Watt = layer.relation_att.detach().contiguous()
+        q = torch.randn(N, H, F, device=dev)
+        k = torch.randn(Ns, H, F, device=dev)
+        wq = torch.empty(Uc, H, F, device=dev)
+        leg("segment_mm_fwd(unique (rel,dst) rows, q.W_att)", lambda: K.rgnn_relational_matmul(d_col, 1, Watt, q, wq, False),
+            uniq_dst * D * 4 + Uc * D * 4 + R * H * F * F * 4 + Uc * 8, "Q_unique*D*s + U*D*s + W + U*i")
+        score = torch.empty(E, H, device=dev)
+        dinv = {"edata_idx_to_inverse_idx": icx}
+        leg("inner_product_fwd(compact left)", lambda: K.rgnn_inner_product_right_node_separatecoo(
+            dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, score),
+            Uc * D * 4 + uniq_src * D * 4 + 3 * E * 8 + E * H * 4, "left_c + right_unique + eid,row,inv ; score")
+        mu = torch.ones(R, H, device=dev) / 4
+        ssum, t, norm = torch.empty(N, H, device=dev), torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
+        leg("hgt_edge_softmax_fwd(in-CSR)", lambda: K.hgt_full_graph_edge_softmax_ops_csr(
+            ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], score, mu, ssum, t, norm),
+            E * H * 4 + 2 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4, "a + eid,rel + row_ptr ; t + norm + sum")
+        msg = torch.randn(Ur, H, F, device=dev)
+        new_h = torch.empty(N, H, F, device=dev)
+        leg("hgt_aggregate_fwd(in-CSR, compact msg)", lambda: K.hetb200_hgt_message_aggregation_csr_compact(
+            ic["row_ptrs"], ic["eids"], ir, msg, t, ssum, new_h),
+            Ur * D * 4 + E * H * 4 + 2 * E * 8 + (N + 1) * 8 + N * H * 4 + N * D * 4, "msg_c + t + eid,inv + row_ptr + sum ; out")
+        gout = torch.randn(N, H, F, device=dev)
+        gs = torch.randn(E, H, device=dev)
+        gl, gr = torch.zeros_like(wq), torch.zeros_like(k)
+        leg("inner_product_bwd(compact left)", lambda: K.backward_inner_product_right_node_separatecoo(
+            dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, gs, gl, gr),
+            2 * Uc * D * 4 + 2 * uniq_src * D * 4 + 3 * E * 8 + E * H * 4,
+            "left_c + right_unique + g + idx ; grad_left_c + grad_right_unique")
+        ga, gmu = torch.empty(E, H, device=dev), torch.zeros(R, H, device=dev)
+        leg("hgt_edge_softmax_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
+            oc["col_indices"], oc["eids"], oc["rel_types"], ir, msg, score, norm, new_h, gout, mu, ga, gmu),
+            Ur * D * 4 + 2 * E * H * 4 + 2 * N * D * 4 + 4 * E * 8 + E * H * 4, "msg_c + a,norm + out,gout + idx ; grad_a")
+        gm = torch.zeros_like(msg)
+        leg("hgt_aggregate_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_message_aggregation_csr_compact(
+            oc["col_indices"], oc["eids"], ir, norm, gout, gm),
+            E * H * 4 + N * D * 4 + 3 * E * 8 + Ur * D * 4, "norm + gout + idx ; grad_msg_c")
+    del flush
+    return out
+
+
 # ---------------------------------------------------------------------------
 def _peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -345,7 +444,7 @@ def main():
     # whole-step CUDA-graph capture; with NCCL collectives inside only when asked for (HETB_GRAPH_MULTI=1)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "0") == "1")
     trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
-                               cuda_graph=use_graph, compact_as_of_node=args.compact)
+                               cuda_graph=use_graph, compact_as_of_node=args.compact, fused=args.fused)
 
     def barrier():
         if world > 1:
@@ -415,7 +514,7 @@ def main():
                         f"{heads} head(s), {coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
             "parallelism": "single GPU" if world == 1 else f"destination-range shards x{world}, NCCL all-gather of "
                            "source rows per layer, reduce-scatter in backward, all-reduce of weight grads",
-            "cuda_graph": use_graph, "compact_as_of_node": bool(args.compact),
+            "cuda_graph": use_graph, "compact_as_of_node": bool(args.compact), "fused_edge_pass": bool(args.fused and args.compact),
             "l2": "inputs larger than L2: per-edge tensors of one step total "
                   f"{coo.num_edges // world * 64 * 4 * 6 / 1e6:.0f} MB per GPU vs 126 MB L2 (no flush between steps)",
             "edges_per_step": coo.num_edges * layers,
@@ -428,7 +527,7 @@ def main():
         "clocks": clocks, "loss": final_loss, "eager_first_loss": eager_loss,
     }
     if not args.no_roofline:
-        legs = kernel_rooflines(trainer, peak, peak_src)
+        legs = (kernel_rooflines_compact if args.compact else kernel_rooflines)(trainer, peak, peak_src)
         top = max(legs, key=lambda d: d["ms"])
         line["roofline"] = {k: top[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "kernel",
                                                  "ms", "algorithmic_bytes", "peak_source")}

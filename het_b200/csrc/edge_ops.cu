@@ -200,6 +200,114 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // ---------------------------------------------------------------------------
+// HGT attention score + edge softmax + aggregation in ONE pass over the in-CSR (the same
+// edge-balanced walker): for position p of destination d with e = eids[p], r = rel[p], s = src[p]
+//   a[e,h] = Σ_f left[L(e),h,f] · kv[s,h,f]          (the inner product, InnerProductEdgeParallel.cu.h:13-113)
+//   t[e,h] = exp(a[e,h] · mu[r,h]);  sum[d,h] = Σ t    (HGTForwardKernels.cu.h:425-587)
+//   ret[d,h,:] = Σ t[e,h] · msg[Mi(e),h,:] / sum[d,h]  (HGTForwardKernels.cu.h:244-369)
+// so the per-edge score is produced, exponentiated and consumed in registers; a and t are still
+// written (16 B per edge) because the backward needs them. L(e) / Mi(e) are the compact rows
+// (direct indexing) or e itself when the pointers are NULL.
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kThreads)
+    hgt_fused_fwd_kernel(const int64_t *__restrict__ row_ptr, const int64_t *__restrict__ eids,
+                         const int64_t *__restrict__ rel, const int64_t *__restrict__ src, int64_t num_rows,
+                         int64_t E, const float *__restrict__ left, const int64_t *__restrict__ left_idx,
+                         const float *__restrict__ kv, const float *__restrict__ msg,
+                         const int64_t *__restrict__ msg_idx, const float *__restrict__ mu,
+                         float *__restrict__ attn, float *__restrict__ t_out, float *__restrict__ sum,
+                         float *__restrict__ ret, int H, int hw) {
+  constexpr int GROUPS = kThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int h = l / hw;
+  const bool leader = (l % hw) == 0;
+  const int64_t p0 = ((int64_t)blockIdx.x * GROUPS + g) * kChunk;
+  // every lane of a warp must take part in the shuffles below: lane groups past the end run
+  // the loop with an empty range instead of returning
+  const bool live = p0 < E;
+  const int64_t p1 = live ? ((p0 + kChunk < E) ? p0 + kChunk : E) : p0;
+
+  int64_t d = 0, row_start = 0, row_end = 0;
+  if (live) {
+    int64_t lo = 0, hi = num_rows;
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(row_ptr + mid) <= p0) lo = mid; else hi = mid;
+    }
+    d = lo;
+    row_start = __ldg(row_ptr + d);
+    row_end = __ldg(row_ptr + d + 1);
+  }
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float s = 0.f;
+
+  auto flush = [&]() {
+    const bool complete = row_start >= p0 && row_end <= p1;
+    if (complete) {
+      const float inv = s > 0.f ? 1.f / s : 0.f;
+      if (leader) sum[d * H + h] = s;
+      st4(ret + d * D + 4 * l, make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv));
+    } else {
+      if (leader) atomicAdd(sum + d * H + h, s);
+      red_add4(ret + d * D + 4 * l, acc);
+    }
+  };
+
+  // all lane groups of a warp iterate kChunk times so the group shuffles stay converged
+  for (int64_t q = 0; q < kChunk; q += 2) {
+    int64_t e[2], li[2], mi[2], sn[2];
+    float m_[2];
+    float4 lv[2], kvv[2], mv[2];
+    bool ok[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int64_t p = p0 + q + j;
+      ok[j] = p < p1;
+      e[j] = ok[j] ? __ldg(eids + p) : 0;
+      sn[j] = ok[j] ? __ldg(src + p) : 0;
+      m_[j] = ok[j] ? __ldg(mu + __ldg(rel + p) * H + h) : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      li[j] = left_idx ? __ldg(left_idx + e[j]) : e[j];
+      mi[j] = msg_idx ? __ldg(msg_idx + e[j]) : e[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      lv[j] = ldg4(left + li[j] * D + 4 * l);
+      kvv[j] = ldg4(kv + sn[j] * D + 4 * l);
+      mv[j] = ldg4(msg + mi[j] * D + 4 * l);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int64_t p = p0 + q + j;
+      if (ok[j] && p == row_end) {  // uniform inside the lane group
+        flush();
+        ++d;
+        while (__ldg(row_ptr + d + 1) == p) ++d;  // empty rows
+        row_start = p;
+        row_end = __ldg(row_ptr + d + 1);
+        acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        s = 0.f;
+      }
+      float a = group_sum(dot4(lv[j], kvv[j]), hw);
+      if (ok[j]) {
+        const float w = __expf(a * m_[j]);
+        if (leader) {
+          attn[e[j] * H + h] = a;
+          t_out[e[j] * H + h] = w;
+        }
+        fma4(acc, w, mv[j]);
+        s += w;
+      }
+    }
+  }
+  if (live) flush();
+}
+
+// ---------------------------------------------------------------------------
 // HGT edge softmax over an in-CSR, edge-balanced: one lane per CSR position
 // (coalesced eids / rel loads), all H heads in that lane. The destination of a
 // position is found by binary search over row_ptr (the upper levels stay in
@@ -460,7 +568,8 @@ __global__ void __launch_bounds__(kThreads)
                              const float *__restrict__ norm,
                              const float *__restrict__ gout,
                              float *__restrict__ grad_msg, int H, int hw,
-                             const int64_t *__restrict__ midx) {
+                             const int64_t *__restrict__ midx,
+                             const float *__restrict__ sum_div) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -469,7 +578,11 @@ __global__ void __launch_bounds__(kThreads)
   for (int64_t i = (int64_t)blockIdx.x * GROUPS + g; i < E; i += stride) {
     const int64_t e = __ldg(eids + i);
     const int64_t d = __ldg(dst_idx + i);
-    const float a = __ldg(norm + e * H + h);
+    float a = __ldg(norm + e * H + h);
+    if (sum_div) {  // norm holds exp(mu*score): normalise here
+      const float sd = __ldg(sum_div + d * H + h);
+      a = sd != 0.f ? a / sd : 0.f;
+    }
     const float4 go = ldg4(gout + d * D + 4 * l);
     const float4 gm = make_float4(a * go.x, a * go.y, a * go.z, a * go.w);
     if (midx) red_add4(grad_msg + __ldg(midx + e) * D + 4 * l, gm);  // compact row: summed
@@ -494,7 +607,8 @@ __global__ void __launch_bounds__(kThreads)
                            const float *__restrict__ mu,
                            float *__restrict__ grad_attn,
                            float *__restrict__ grad_mu, int H, int hw,
-                           int use_smem, const int64_t *__restrict__ midx) {
+                           int use_smem, const int64_t *__restrict__ midx,
+                           const float *__restrict__ sum_div) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   extern __shared__ float mu_acc[];
@@ -512,11 +626,11 @@ __global__ void __launch_bounds__(kThreads)
   for (int64_t it = 0; it < iters; ++it, i += stride) {
     const bool ok = i < E;
     float s = 0.f;
-    int64_t e = 0, r = 0;
+    int64_t e = 0, r = 0, d = 0;
     if (ok) {
       e = __ldg(eids + i);
       r = __ldg(rel + i);
-      const int64_t d = __ldg(dst_idx + i);
+      d = __ldg(dst_idx + i);
       const float4 go = ldg4(gout + d * D + 4 * l);
       const float4 ov = ldg4(out + d * D + 4 * l);
       const float4 mv = midx ? ldg4(msg + __ldg(midx + e) * D + 4 * l) : ldcs4(msg + e * D + 4 * l);
@@ -525,7 +639,12 @@ __global__ void __launch_bounds__(kThreads)
     }
     s = group_sum(s, hw);
     if (ok && leader) {
-      s *= __ldg(norm + e * H + h);
+      float nrm = __ldg(norm + e * H + h);
+      if (sum_div) {
+        const float sd = __ldg(sum_div + d * H + h);
+        nrm = sd != 0.f ? nrm / sd : 0.f;
+      }
+      s *= nrm;
       grad_attn[e * H + h] = s * __ldg(mu + r * H + h);
       const float gm = s * __ldg(attn + e * H + h);
       if (use_smem)
@@ -684,6 +803,35 @@ extern "C" int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr,
   return HETB_OK;
 }
 
+extern "C" int hetb_hgt_fused_fwd_csr(const int64_t *row_ptr, const int64_t *eids, const int64_t *rel,
+                                      const int64_t *src, int64_t num_rows, int64_t num_edges,
+                                      const float *left, const int64_t *left_idx, const float *kv,
+                                      const float *msg, const int64_t *msg_idx, const float *mu, float *attn,
+                                      float *t_out, float *sum, float *ret, int H, int F, void *stream) {
+  HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0);
+  if (num_rows == 0) return HETB_OK;
+  HETB_CHECK_ARG(row_ptr && sum && ret);
+  HETB_CHECK_ARG(num_edges == 0 || (eids && rel && src && left && kv && msg && mu && attn && t_out));
+  const int lpr = lanes_per_row(H, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int groups = kThreads / lpr;
+  const int64_t row_grid = ceil_div64(num_rows, groups);
+  DISPATCH_LPR(lpr, (agg_prepare_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
+                        row_ptr, num_rows, sum, ret, H, F / 4, 1)));
+  HETB_LAUNCH_OK();
+  if (num_edges == 0) return HETB_OK;
+  const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
+  DISPATCH_LPR(lpr, (hgt_fused_fwd_kernel<L><<<(unsigned)grid, kThreads, 0, st>>>(
+                        row_ptr, eids, rel, src, num_rows, num_edges, left, left_idx, kv, msg, msg_idx, mu, attn,
+                        t_out, sum, ret, H, F / 4)));
+  HETB_LAUNCH_OK();
+  DISPATCH_LPR(lpr, (agg_normalize_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
+                        row_ptr, num_rows, sum, ret, H, F / 4)));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
 extern "C" int hetb_hgt_edge_softmax_fwd_csr(
     const int64_t *row_ptr, const int64_t *eids, const int64_t *rel,
     int64_t num_rows, int64_t num_edges, const float *attn, const float *mu,
@@ -791,7 +939,7 @@ extern "C" int hetb_hgt_aggregate_bwd(const int64_t *dst_idx,
                                       const int64_t *eids, int64_t num_edges,
                                       const float *norm, const float *gout,
                                       float *grad_msg, int H, int F,
-                                      const int64_t *msg_idx, void *stream) {
+                                      const int64_t *msg_idx, const float *sum_div, void *stream) {
   HETB_CHECK_ARG(num_edges >= 0);
   if (num_edges == 0) return HETB_OK;
   HETB_CHECK_ARG(dst_idx && eids && norm && gout && grad_msg);
@@ -801,7 +949,7 @@ extern "C" int hetb_hgt_aggregate_bwd(const int64_t *dst_idx,
   const int grid = edge_grid(num_edges, kThreads / lpr);
   DISPATCH_LPR(lpr, (hgt_aggregate_bwd_kernel<L><<<grid, kThreads, 0, st>>>(
                         dst_idx, eids, num_edges, norm, gout, grad_msg, H,
-                        F / 4, msg_idx)));
+                        F / 4, msg_idx, sum_div)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -810,7 +958,8 @@ extern "C" int hetb_hgt_edge_softmax_bwd(
     const int64_t *dst_idx, const int64_t *eids, const int64_t *rel,
     int64_t num_edges, int64_t num_rels, const float *msg, const float *attn,
     const float *norm, const float *out, const float *gout, const float *mu,
-    float *grad_attn, float *grad_mu, int H, int F, const int64_t *msg_idx, void *stream) {
+    float *grad_attn, float *grad_mu, int H, int F, const int64_t *msg_idx, const float *sum_div,
+    void *stream) {
   HETB_CHECK_ARG(num_edges >= 0 && num_rels >= 0);
   if (num_edges == 0) return HETB_OK;
   HETB_CHECK_ARG(dst_idx && eids && rel && msg && attn && norm && out && gout &&
@@ -826,7 +975,7 @@ extern "C" int hetb_hgt_edge_softmax_bwd(
   DISPATCH_LPR(lpr, (hgt_softmax_bwd_kernel<L><<<grid, kThreads, smem, st>>>(
                         dst_idx, eids, rel, num_edges, (int)num_rels, msg, attn,
                         norm, out, gout, mu, grad_attn, grad_mu, H, F / 4,
-                        use_smem, msg_idx)));
+                        use_smem, msg_idx, sum_div)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -500,7 +500,7 @@ void backward_hgt_full_graph_message_mean_aggregation_csr(
                i64(outcsr_eids, op, "outcsr_eids"), outcsr_eids.numel(),
                f32(normalized_attn_score, op, "normalized_attn_score"),
                f32(gradout, op, "gradout"), f32w(grad_message, op, "grad_message"),
-               H, F, nullptr, stream_of(gradout)),
+               H, F, nullptr, nullptr, stream_of(gradout)),
            op);
 }
 
@@ -516,7 +516,7 @@ void hetb200_backward_hgt_message_aggregation_csr_compact(
                i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
                outcsr_eids.numel(), f32(normalized_attn_score, op, "normalized_attn_score"),
                f32(gradout, op, "gradout"), f32w(grad_message_compact, op, "grad_message_compact"), H, F,
-               i64(msg_idx, op, "msg_idx"), stream_of(gradout)),
+               i64(msg_idx, op, "msg_idx"), nullptr, stream_of(gradout)),
            op);
 }
 
@@ -540,7 +540,7 @@ void backward_hgt_full_graph_edge_softmax_ops_csr(
                f32(normalized_attn_score, op, "normalized_attn_score"),
                f32(out, op, "out"), f32(gradout, op, "gradout"),
                f32(mu, op, "mu"), f32w(grad_attn_score, op, "grad_attn_score"),
-               f32w(grad_mu, op, "grad_mu"), H, F, nullptr, stream_of(gradout)),
+               f32w(grad_mu, op, "grad_mu"), H, F, nullptr, nullptr, stream_of(gradout)),
            op);
 }
 
@@ -560,7 +560,53 @@ void hetb200_backward_hgt_edge_softmax_ops_csr_compact(
                f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
                f32(normalized_attn_score, op, "normalized_attn_score"), f32(out, op, "out"),
                f32(gradout, op, "gradout"), f32(mu, op, "mu"), f32w(grad_attn_score, op, "grad_attn_score"),
-               f32w(grad_mu, op, "grad_mu"), H, F, i64(msg_idx, op, "msg_idx"), stream_of(gradout)),
+               f32w(grad_mu, op, "grad_mu"), H, F, i64(msg_idx, op, "msg_idx"), nullptr, stream_of(gradout)),
+           op);
+}
+
+// hetb200 fusion: inner product + edge softmax + aggregation in one in-CSR pass, compact inputs.
+// attn / t are still written (the backward needs them); sum, ret as in the unfused ops.
+void hetb200_hgt_fused_attention_aggregation_csr(
+    Tensor &incsr_row_ptrs, Tensor &incsr_col_indices, Tensor &incsr_eids, Tensor &incsr_reltypes,
+    Tensor &left_idx, Tensor &msg_idx, Tensor &left_compact, Tensor &k, Tensor &messages_compact, Tensor &mu,
+    Tensor &attn, Tensor &t, Tensor &sum, Tensor &ret) {
+  const char *op = "hetb200_hgt_fused_attention_aggregation_csr";
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(messages_compact) / H);
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_hgt_fused_fwd_csr(
+               i64(incsr_row_ptrs, op, "incsr_row_ptrs"), i64(incsr_eids, op, "incsr_eids"),
+               i64(incsr_reltypes, op, "incsr_reltypes"), i64(incsr_col_indices, op, "incsr_col_indices"),
+               incsr_row_ptrs.numel() - 1, incsr_eids.numel(), f32(left_compact, op, "left_compact"),
+               i64(left_idx, op, "left_idx"), f32(k, op, "k"), f32(messages_compact, op, "messages_compact"),
+               i64(msg_idx, op, "msg_idx"), f32(mu, op, "mu"), f32w(attn, op, "attn"), f32w(t, op, "t"),
+               f32w(sum, op, "sum"), f32w(ret, op, "ret"), H, F, stream_of(ret)),
+           op);
+}
+
+// Backward of the softmax + aggregation half with t = exp(mu·score) and the per-node sums instead of
+// the normalised scores (norm = t / sum[d] is formed in the kernels).
+void hetb200_backward_hgt_fused_softmax_aggregation_csr(
+    Tensor &outcsr_col_indices, Tensor &outcsr_eids, Tensor &outcsr_reltypes, Tensor &msg_idx,
+    Tensor &messages_compact, Tensor &attn, Tensor &t, Tensor &sum, Tensor &out, Tensor &gradout, Tensor &mu,
+    Tensor &grad_message_compact, Tensor &grad_attn, Tensor &grad_mu) {
+  const char *op = "hetb200_backward_hgt_fused_softmax_aggregation_csr";
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(messages_compact) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_aggregate_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
+               outcsr_eids.numel(), f32(t, op, "t"), f32(gradout, op, "gradout"),
+               f32w(grad_message_compact, op, "grad_message_compact"), H, F, i64(msg_idx, op, "msg_idx"),
+               f32(sum, op, "sum"), stream_of(gradout)),
+           op);
+  check_rc(hetb_hgt_edge_softmax_bwd(
+               i64(outcsr_col_indices, op, "outcsr_col_indices"), i64(outcsr_eids, op, "outcsr_eids"),
+               i64(outcsr_reltypes, op, "outcsr_reltypes"), outcsr_eids.numel(), mu.size(0),
+               f32(messages_compact, op, "messages_compact"), f32(attn, op, "attn"), f32(t, op, "t"),
+               f32(out, op, "out"), f32(gradout, op, "gradout"), f32(mu, op, "mu"),
+               f32w(grad_attn, op, "grad_attn"), f32w(grad_mu, op, "grad_mu"), H, F,
+               i64(msg_idx, op, "msg_idx"), f32(sum, op, "sum"), stream_of(gradout)),
            op);
 }
 
@@ -786,6 +832,8 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("backward_relational_fused_gat_separate_coo",
         backward_relational_fused_gat_separate_coo);
   // HGT (OpExport/HGTOps.inc.h:656-674)
+  m.def("hetb200_hgt_fused_attention_aggregation_csr", hetb200_hgt_fused_attention_aggregation_csr);
+  m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
   m.def("hetb200_softmax_cross_entropy", hetb200_softmax_cross_entropy);
   m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);

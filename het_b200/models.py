@@ -137,13 +137,16 @@ class HET_RGATModel(nn.Module):
 
 class HET_HGTLayerHetero(nn.Module):
     def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
-                 compact_as_of_node_flag=False, compact_direct_indexing_flag=True):
+                 compact_as_of_node_flag=False, compact_direct_indexing_flag=True,
+                 fused_attention_aggregation_flag=False):
         super().__init__()
         # compact_as_of_node_flag (hrt/python/HGT/models.py:177-208): W_att·Q is computed once per
         # unique (relation, destination) pair; here the same is also done for W_msg·V per unique
         # (relation, source) pair (a hetb200 extension, same maths). Only direct indexing is built.
         self.compact_as_of_node_flag = compact_as_of_node_flag
         self.compact_direct_indexing_flag = compact_direct_indexing_flag
+        # hetb200 fusion (needs the compact flag): score, softmax and aggregation in one in-CSR pass
+        self.fused_attention_aggregation_flag = fused_attention_aggregation_flag
         self.in_dim, self.out_dim = in_dim, out_dim
         self.num_ntypes, self.num_relations = num_ntypes, num_rels
         self.num_heads = num_heads
@@ -188,12 +191,16 @@ class HET_HGTLayerHetero(nn.Module):
             attn_weight_dst_product_compact = B.rgnn_relational_matmul(
                 {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
                  "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, self.relation_att, q, False, 1)
-            attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k, 2, "_col")
             message_compact = B.rgnn_relational_matmul(
                 {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
                  "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, self.relation_msg, v, False, 1)
-            new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(
-                G, message_compact, attn_score, self.relation_pri / self.sqrt_dk)
+            if self.fused_attention_aggregation_flag:
+                new_h = B.hgt_fused_attention_and_aggregation_csr_compact(
+                    G, attn_weight_dst_product_compact, k, message_compact, self.relation_pri / self.sqrt_dk)
+            else:
+                attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k, 2, "_col")
+                new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(
+                    G, message_compact, attn_score, self.relation_pri / self.sqrt_dk)
         else:
             attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
             attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")

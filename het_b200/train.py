@@ -32,7 +32,7 @@ from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel
 class FullGraphTrainer:
     def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
                  layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0,
-                 compact_as_of_node=False):
+                 compact_as_of_node=False, fused=False):
         assert kind in ("rgat", "hgt")
         self.kind, self.device, self.rank, self.world, self.group = kind, torch.device(device), rank, world, group
         self.num_nodes_total = coo.num_nodes
@@ -56,7 +56,9 @@ class FullGraphTrainer:
                                        compact_as_of_node_flag=compact_as_of_node).to(self.device)
         else:
             self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
-                                           compact_as_of_node_flag=compact_as_of_node).to(self.device)
+                                           compact_as_of_node_flag=compact_as_of_node,
+                                           fused_attention_aggregation_flag=bool(fused and compact_as_of_node)
+                                           ).to(self.device)
         gen = torch.Generator().manual_seed(seed + 1)
         embed_full = torch.rand(coo.num_nodes, hidden, generator=gen) * 2 - 1
         labels_full = torch.randint(0, out_dim, (coo.num_nodes,), generator=gen)

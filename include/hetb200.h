@@ -208,6 +208,7 @@ int hetb_hgt_aggregate_bwd(const int64_t *dst_idx, const int64_t *eids,
                            int64_t num_edges, const float *norm,
                            const float *gout, float *grad_msg, int H, int F,
                            const int64_t *msg_idx /* non-NULL: grad_msg is compact, summed */,
+                           const float *sum_div /* non-NULL: norm holds exp(mu·score), divide by sum[d,h] */,
                            void *stream);
 
 /* s = Σ_f gout[d,h,f]·(msg[e,h,f] − out[d,h,f]) · norm[e,h]
@@ -225,7 +226,20 @@ int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
                               const float *mu, float *grad_attn,
                               float *grad_mu, int H, int F,
                               const int64_t *msg_idx /* NULL, or compact msg row per edge id */,
+                              const float *sum_div /* non-NULL: norm holds exp(mu·score), divide by sum[d,h] */,
                               void *stream);
+
+/* Attention score + edge softmax + aggregation in one pass over the in-CSR (hetb200 fusion of
+ * rgnn_inner_product_right_node + hgt_full_graph_edge_softmax_ops_csr +
+ * hgt_full_graph_message_mean_aggregation_csr; same maths, reference files as those three):
+ *   attn[e,h] = Σ_f left[L(e),h,f]·kv[src[p],h,f];  t[e,h] = exp(attn·mu[rel[p],h]);
+ *   sum[d,h] = Σ_p t;  ret[d,h,:] = Σ_p t[e,h]·msg[M(e),h,:] / sum[d,h]
+ * with L(e) = left_idx ? left_idx[e] : e and M(e) = msg_idx ? msg_idx[e] : e. */
+int hetb_hgt_fused_fwd_csr(const int64_t *row_ptr, const int64_t *eids, const int64_t *rel,
+                           const int64_t *src, int64_t num_rows, int64_t num_edges,
+                           const float *left, const int64_t *left_idx, const float *kv,
+                           const float *msg, const int64_t *msg_idx, const float *mu, float *attn,
+                           float *t_out, float *sum, float *ret, int H, int F, void *stream);
 
 /* ------------------------------------------------------------------------
  * Loss of the full-graph training step
