@@ -72,36 +72,44 @@ constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NN 
 
 // ------------------------------------------------------------ work items ----
 // Every role walks the same deterministic sequence of (tile, segment piece) items.
+// Positions are 32-bit offsets from the CTA's first row (64-bit compare/select chains and the
+// 64-bit division that maps a row to its tile cost a few hundred cycles per call, and next() sits
+// on the critical path of every role); the segment table is only touched when a segment ends.
 struct PieceIter {
   const int64_t *__restrict__ seg_ptrs;
-  int num_segs;
-  int64_t M, row, row_stop;  // rows [row, row_stop) remain for this CTA
-  int s;
+  int64_t row_base;                  // first row of the CTA (a multiple of TM)
+  int num_segs, n, rel, seg_end, s;  // rows of the CTA, position, end of segment s (clamped to n)
 
   __device__ PieceIter(const int64_t *sp, int ns, int64_t m, int64_t tile_begin, int64_t tile_end)
-      : seg_ptrs(sp), num_segs(ns), M(m) {
-    row = tile_begin * TM;
-    row_stop = tile_end * TM < m ? tile_end * TM : m;
-    s = 0;
-    if (row < row_stop) {
-      s = segment_of(seg_ptrs, num_segs, row);
-      while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
+      : seg_ptrs(sp), row_base(tile_begin * TM), num_segs(ns), n(0), rel(0), seg_end(0), s(0) {
+    int64_t stop = tile_end * TM < m ? tile_end * TM : m;
+    n = stop > row_base ? (int)(stop - row_base) : 0;
+    if (n > 0) {
+      s = segment_of(seg_ptrs, num_segs, row_base);
+      skip_empty();
     }
   }
-  // next piece: rows [p0, p1) of tile starting at tile_row0, segment seg
-  __device__ bool next(int64_t &tile_row0, int64_t &p0, int64_t &p1, int &seg) {
-    if (row >= row_stop) return false;
-    tile_row0 = (row / TM) * TM;
-    int64_t tile_end = tile_row0 + TM;
-    if (tile_end > M) tile_end = M;
-    const int64_t seg_end = (s + 1 < num_segs) ? __ldg(seg_ptrs + s + 1) : M;
-    p0 = row;
-    p1 = seg_end < tile_end ? seg_end : tile_end;
+  __device__ void skip_empty() {
+    const int64_t row = row_base + rel;
+    while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
+    int64_t e = n;
+    if (s + 1 < num_segs) {
+      const int64_t se = __ldg(seg_ptrs + s + 1) - row_base;
+      if (se < e) e = se;
+    }
+    seg_end = (int)e;
+  }
+  // next piece: rows [p0, p1) (relative to row_base) of the tile starting at t0, segment seg
+  __device__ __forceinline__ bool next(int &t0, int &p0, int &p1, int &seg) {
+    if (rel >= n) return false;
+    t0 = rel & ~(TM - 1);
+    p0 = rel;
+    p1 = min(min(t0 + TM, n), seg_end);
     seg = s;
-    row = p1;
-    if (row == seg_end && row < row_stop) {
+    rel = p1;
+    if (p1 == seg_end && p1 < n) {
       ++s;
-      while (s + 1 < num_segs && __ldg(seg_ptrs + s + 1) <= row) ++s;
+      skip_empty();
     }
     return true;
   }
@@ -131,10 +139,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (warp == kEpiWarps) {
     if (lane == 0) {
       for (int i = 0; i < kStages; ++i) {
-        mbar_init(full_bar(i), kProdThreads);
+        mbar_init(full_bar(i), kProdWarps);
         mbar_init(empty_bar(i), 1);
         mbar_init(tfull_bar(i), 1);
-        mbar_init(tempty_bar(i), kEpiWarps * 32);
+        mbar_init(tempty_bar(i), kEpiWarps);
       }
       fence_barrier_init();
     }
@@ -150,7 +158,8 @@ __global__ void __launch_bounds__(kThreads, 1)
   const int64_t tile_begin = num_tiles * blockIdx.x / gridDim.x;
   const int64_t tile_end = num_tiles * (blockIdx.x + 1) / gridDim.x;
   PieceIter it(seg_ptrs, num_segs, M, tile_begin, tile_end);
-  int64_t tile_row0, p0, p1;
+  const int64_t row_base = tile_begin * TM;
+  int tile_row0, p0, p1;  // relative to row_base
   int seg;
 
   if (warp > kEpiWarps) {
@@ -172,16 +181,22 @@ __global__ void __launch_bounds__(kThreads, 1)
     uint32_t n = 0;
     PieceIter it_ix = it;  // runs kSets..2*kSets items ahead of `it`
 
+    // Predicated loads that write the index register directly: a branch per slot costs more
+    // than the load, and anything computed from the loaded value here would stall this step for
+    // a full memory latency.
     auto issue_idx = [&](int *ix) {
-      int64_t t0, a0, a1;
-      int sg;
+      int t0, a0, a1, sg;
       const bool valid = it_ix.next(t0, a0, a1, sg);
+      const int lim = valid ? it_ix.n : 0;
 #pragma unroll
       for (int i = 0; i < RP; ++i) {
-        const int64_t gr = t0 + r_in + kRowStep * i;
-        ix[i] = -1;
+        const int rr = t0 + r_in + kRowStep * i;
+        const bool ok = valid && rr < lim;
+        const int64_t gr = row_base + rr;
         // a row index fits 31 bits: 2^31 rows of 256 B would be 550 GB
-        if (valid && gr < M) ix[i] = a_idx ? (int)__ldg(a_idx + gr) : (int)gr;
+        int v = ok ? (int)gr : -1;
+        if (ok && a_idx) v = (int)__ldg(a_idx + gr);
+        ix[i] = v;
       }
     };
     auto issue_rows = [&](const int *ix, float4 *v) {
@@ -243,7 +258,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
-      mbar_arrive(full_bar(stage));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full_bar(stage));  // one arrival per warp: 256 per stage cost more than the split
       ++n;
       return true;
     };
@@ -312,9 +328,10 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int stage = n & 1;
       const uint32_t phase = (n >> 1) & 1;
       // destination row of this lane's tile row (lane j <-> row warp*32 + j), fetched early
-      const int64_t my_gr = tile_row0 + warp * 32 + lane;
+      const int my_rr = tile_row0 + warp * 32 + lane;
+      const int64_t my_gr = row_base + my_rr;
       int64_t my_cr = my_gr;
-      if (c_idx && my_gr >= p0 && my_gr < p1) my_cr = __ldg(c_idx + my_gr);
+      if (c_idx && my_rr >= p0 && my_rr < p1) my_cr = __ldg(c_idx + my_gr);
       mbar_wait(tfull_bar(stage), phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(stage * NN);
@@ -326,7 +343,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         tmem_ld_wait();
         if (half == 1) {
           tc_fence_before();
-          mbar_arrive(tempty_bar(stage));  // TMEM stage free: the next MMA may start
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(stage));  // TMEM stage free: the next MMA may start
         }
 #pragma unroll
         for (int c8 = 0; c8 < 8; ++c8) {
@@ -341,9 +359,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int lr = i * 2 + (lane >> 4);  // row within this warp's 32
-        const int64_t gr = tile_row0 + warp * 32 + lr;
+        const int rr = tile_row0 + warp * 32 + lr;
         const int64_t cr = __shfl_sync(0xffffffffu, my_cr, lr);
-        if (gr >= p0 && gr < p1 && !(probe & 4)) {
+        if (rr >= p0 && rr < p1 && !(probe & 4)) {
           const int pc = (c & 8) | ((c & 7) ^ (lr & 7));
           const float4 val = *reinterpret_cast<const float4 *>(stg + lr * 256 + pc * 16);
           float *dst = Y + cr * NN + c * 4;
