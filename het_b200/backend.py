@@ -415,39 +415,32 @@ class HGTFusedAttentionAggregationCSRCompact(th.autograd.Function):
     """hetb200 fusion of rgnn_inner_product_right_node (kind 2) + the edge softmax + the message
     aggregation: one in-CSR pass computes the score, exponentiates it and accumulates the weighted
     compact messages, so the score never leaves registers on its way to the aggregation. The
-    backward runs the existing kernels (aggregation, softmax, inner product) on the saved score
-    and exp(mu*score)."""
+    backward is one out-CSR pass as well (aggregation-, softmax- and inner-product-backward fused)."""
 
     @staticmethod
-    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, outcsr_col_indices,
-                outcsr_eids, outcsr_reltypes, coo_rel_ptrs, coo_eids, coo_row_indices, coo_col_indices,
-                left_idx, msg_idx, left_compact, k, message_compact, mu, attn, t, ssum, new_h):
+    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, outcsr_row_ptrs,
+                outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx, msg_idx, left_compact, k,
+                message_compact, mu, attn, t, ssum, new_h):
         ctx.mark_dirty(new_h)
         K.hetb200_hgt_fused_attention_aggregation_csr(
             incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, left_idx, msg_idx, left_compact, k,
             message_compact, mu, attn, t, ssum, new_h)
-        ctx.save_for_backward(outcsr_col_indices, outcsr_eids, outcsr_reltypes, coo_rel_ptrs, coo_eids,
-                              coo_row_indices, coo_col_indices, left_idx, msg_idx, left_compact, k,
-                              message_compact, mu, attn, t, ssum, new_h)
+        ctx.save_for_backward(outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx,
+                              msg_idx, left_compact, k, message_compact, mu, attn, t, ssum, new_h)
         return new_h
 
     @staticmethod
     def backward(ctx, gradout):
-        (outcsr_col_indices, outcsr_eids, outcsr_reltypes, coo_rel_ptrs, coo_eids, coo_row_indices,
-         coo_col_indices, left_idx, msg_idx, left, k, msg, mu, attn, t, ssum, new_h) = ctx.saved_tensors
-        gradout = gradout.contiguous()
+        (outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx, msg_idx, left, k, msg,
+         mu, attn, t, ssum, new_h) = ctx.saved_tensors
         grad_msg = th.zeros_like(msg, memory_format=th.contiguous_format)
-        grad_attn = th.empty_like(attn, memory_format=th.contiguous_format)
-        grad_mu = th.zeros_like(mu, memory_format=th.contiguous_format)
-        K.hetb200_backward_hgt_fused_softmax_aggregation_csr(
-            outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx, msg, attn, t, ssum, new_h, gradout, mu,
-            grad_msg, grad_attn, grad_mu)
         grad_left = th.zeros_like(left, memory_format=th.contiguous_format)
         grad_k = th.zeros_like(k, memory_format=th.contiguous_format)
-        K.backward_inner_product_right_node_separatecoo(
-            {"edata_idx_to_inverse_idx": left_idx}, 2, coo_rel_ptrs, coo_eids, coo_row_indices, coo_col_indices,
-            left, k, grad_attn, grad_left, grad_k)
-        return (None,) * 13 + (grad_left, grad_k, grad_msg, grad_mu, None, None, None, None)
+        grad_mu = th.zeros_like(mu, memory_format=th.contiguous_format)
+        K.hetb200_backward_hgt_fused_attention_aggregation_csr(
+            outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx, msg_idx, left, k, msg,
+            mu, attn, t, ssum, new_h, gradout.contiguous(), grad_left, grad_k, grad_msg, grad_mu)
+        return (None,) * 10 + (grad_left, grad_k, grad_msg, grad_mu, None, None, None, None)
 
 
 def hgt_fused_attention_and_aggregation_csr_compact(graph, left_compact, k, message_compact, mu):
@@ -459,9 +452,9 @@ def hgt_fused_attention_and_aggregation_csr_compact(graph, left_compact, k, mess
     attn = message_compact.new_empty(e, h)
     t = message_compact.new_empty(e, h)
     return HGTFusedAttentionAggregationCSRCompact.apply(
-        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["col_indices"],
-        outcsr["eids"], outcsr["rel_types"], coo["rel_ptrs"], coo["eids"], coo["row_indices"],
-        coo["col_indices"], uniq["inverse_idx_col"], uniq["inverse_idx_row"], left_compact.contiguous(),
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["row_ptrs"],
+        outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"], uniq["inverse_idx_col"],
+        uniq["inverse_idx_row"], left_compact.contiguous(),
         k.contiguous(), message_compact.contiguous(), mu.contiguous(), attn, t, ssum, new_h)
 
 

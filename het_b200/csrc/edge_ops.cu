@@ -308,6 +308,138 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // ---------------------------------------------------------------------------
+// Backward of hgt_fused_fwd_kernel in ONE pass over the OUT-CSR (rows = sources), replacing the
+// aggregation-, softmax- and inner-product-backward kernels (HGTBackwardKernels.cu.h:343-440,
+// 499-627; InnerProductEdgeParallel.cu.h:119-202). For position p of source s with d = dst[p],
+// e = eids[p], r = rel[p]:
+//   norm = t[e,h] / sum[d,h]
+//   sg   = Σ_f gout[d,h,f]·(msg[M(e),h,f] − out[d,h,f]) · norm       (softmax Jacobian)
+//   ga   = sg · mu[r,h]                       (gradient of the score),   grad_mu[r,h] += sg · attn[e,h]
+//   grad_msg[M(e),h,:]  += norm · gout[d,h,:]
+//   grad_left[L(e),h,:] += ga · kv[s,h,:]
+//   grad_kv[s,h,:]      += ga · left[L(e),h,:]
+// Walking by source makes kv[s] a row constant (loaded once per row) and grad_kv[s] a register
+// accumulator stored once per row, gout[d] is read once instead of twice, and the per-edge score
+// gradient never exists in memory. grad_msg / grad_left / grad_kv must arrive zero-filled.
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kThreads)
+    hgt_fused_bwd_kernel(const int64_t *__restrict__ row_ptr, const int64_t *__restrict__ dst,
+                         const int64_t *__restrict__ eids, const int64_t *__restrict__ rel, int64_t num_rows,
+                         int64_t E, int num_rels, const float *__restrict__ left,
+                         const int64_t *__restrict__ left_idx, const float *__restrict__ kv,
+                         const float *__restrict__ msg, const int64_t *__restrict__ msg_idx,
+                         const float *__restrict__ mu, const float *__restrict__ attn,
+                         const float *__restrict__ t, const float *__restrict__ sum,
+                         const float *__restrict__ out, const float *__restrict__ gout,
+                         float *__restrict__ grad_left, float *__restrict__ grad_kv, float *__restrict__ grad_msg,
+                         float *__restrict__ grad_mu, int H, int hw, int use_smem) {
+  constexpr int GROUPS = kThreads / LPR;
+  constexpr int D = LPR * 4;
+  extern __shared__ float mu_acc[];
+  const int RH = num_rels * H;
+  if (use_smem) {
+    for (int j = threadIdx.x; j < RH; j += kThreads) mu_acc[j] = 0.f;
+    __syncthreads();
+  }
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int h = l / hw;
+  const bool leader = (l % hw) == 0;
+  const int64_t p0 = ((int64_t)blockIdx.x * GROUPS + g) * kChunk;
+  const bool live = p0 < E;  // dead lane groups still run the loop: the shuffles need every lane
+  const int64_t p1 = live ? ((p0 + kChunk < E) ? p0 + kChunk : E) : p0;
+
+  int64_t srow = 0, row_start = 0, row_end = 0;
+  float4 right = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (live) {
+    int64_t lo = 0, hi = num_rows;
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(row_ptr + mid) <= p0) lo = mid; else hi = mid;
+    }
+    srow = lo;
+    row_start = __ldg(row_ptr + srow);
+    row_end = __ldg(row_ptr + srow + 1);
+    right = ldg4(kv + srow * D + 4 * l);
+  }
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  auto flush = [&]() {
+    if (row_start >= p0 && row_end <= p1) st4(grad_kv + srow * D + 4 * l, acc);
+    else red_add4(grad_kv + srow * D + 4 * l, acc);
+  };
+
+  for (int64_t q = 0; q < kChunk; q += 2) {
+    int64_t e[2], dn[2], li[2], mi[2];
+    float tt[2], aa[2], sd[2], mm[2];
+    float4 go[2], ov[2], mv[2], lv[2];
+    bool ok[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int64_t p = p0 + q + j;
+      ok[j] = p < p1;
+      e[j] = ok[j] ? __ldg(eids + p) : 0;
+      dn[j] = ok[j] ? __ldg(dst + p) : 0;
+      mm[j] = ok[j] ? __ldg(mu + __ldg(rel + p) * H + h) : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      li[j] = left_idx ? __ldg(left_idx + e[j]) : e[j];
+      mi[j] = msg_idx ? __ldg(msg_idx + e[j]) : e[j];
+      tt[j] = __ldg(t + e[j] * H + h);
+      aa[j] = __ldg(attn + e[j] * H + h);
+      sd[j] = __ldg(sum + dn[j] * H + h);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      go[j] = ldg4(gout + dn[j] * D + 4 * l);
+      ov[j] = ldg4(out + dn[j] * D + 4 * l);
+      mv[j] = ldg4(msg + mi[j] * D + 4 * l);
+      lv[j] = ldg4(left + li[j] * D + 4 * l);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int64_t p = p0 + q + j;
+      if (ok[j] && p == row_end) {  // uniform inside the lane group
+        flush();
+        ++srow;
+        while (__ldg(row_ptr + srow + 1) == p) ++srow;  // sources without out-edges
+        row_start = p;
+        row_end = __ldg(row_ptr + srow + 1);
+        right = ldg4(kv + srow * D + 4 * l);
+        acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      const float dotv = go[j].x * (mv[j].x - ov[j].x) + go[j].y * (mv[j].y - ov[j].y) +
+                         go[j].z * (mv[j].z - ov[j].z) + go[j].w * (mv[j].w - ov[j].w);
+      const float sdot = group_sum(dotv, hw);
+      if (ok[j]) {
+        const float nrm = sd[j] != 0.f ? tt[j] / sd[j] : 0.f;
+        const float sg = sdot * nrm;
+        const float ga = sg * mm[j];
+        if (leader) {
+          const int64_t r = __ldg(rel + p);
+          if (use_smem) atomicAdd(&mu_acc[r * H + h], sg * aa[j]);
+          else atomicAdd(grad_mu + r * H + h, sg * aa[j]);
+        }
+        red_add4(grad_msg + mi[j] * D + 4 * l,
+                 make_float4(nrm * go[j].x, nrm * go[j].y, nrm * go[j].z, nrm * go[j].w));
+        red_add4(grad_left + li[j] * D + 4 * l,
+                 make_float4(ga * right.x, ga * right.y, ga * right.z, ga * right.w));
+        fma4(acc, ga, lv[j]);
+      }
+    }
+  }
+  if (live) flush();
+  if (use_smem) {
+    __syncthreads();
+    for (int j = threadIdx.x; j < RH; j += kThreads) {
+      const float v = mu_acc[j];
+      if (v != 0.f) atomicAdd(grad_mu + j, v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // HGT edge softmax over an in-CSR, edge-balanced: one lane per CSR position
 // (coalesced eids / rel loads), all H heads in that lane. The destination of a
 // position is found by binary search over row_ptr (the upper levels stay in
@@ -828,6 +960,32 @@ extern "C" int hetb_hgt_fused_fwd_csr(const int64_t *row_ptr, const int64_t *eid
   HETB_LAUNCH_OK();
   DISPATCH_LPR(lpr, (agg_normalize_kernel<L><<<(unsigned)row_grid, kThreads, 0, st>>>(
                         row_ptr, num_rows, sum, ret, H, F / 4)));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+extern "C" int hetb_hgt_fused_bwd_csr(const int64_t *row_ptr, const int64_t *dst, const int64_t *eids,
+                                      const int64_t *rel, int64_t num_rows, int64_t num_edges, int64_t num_rels,
+                                      const float *left, const int64_t *left_idx, const float *kv,
+                                      const float *msg, const int64_t *msg_idx, const float *mu,
+                                      const float *attn, const float *t, const float *sum, const float *out,
+                                      const float *gout, float *grad_left, float *grad_kv, float *grad_msg,
+                                      float *grad_mu, int H, int F, void *stream) {
+  HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0 && num_rels >= 0);
+  if (num_rows == 0 || num_edges == 0) return HETB_OK;
+  HETB_CHECK_ARG(row_ptr && dst && eids && rel && left && kv && msg && mu && attn && t && sum && out && gout &&
+                 grad_left && grad_kv && grad_msg && grad_mu);
+  const int lpr = lanes_per_row(H, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int groups = kThreads / lpr;
+  const int use_smem = (num_rels * H <= kMaxSmemMu) ? 1 : 0;
+  const size_t smem = use_smem ? (size_t)num_rels * H * sizeof(float) : 0;
+  const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
+  DISPATCH_LPR(lpr, (hgt_fused_bwd_kernel<L><<<(unsigned)grid, kThreads, smem, st>>>(
+                        row_ptr, dst, eids, rel, num_rows, num_edges, (int)num_rels, left, left_idx, kv, msg,
+                        msg_idx, mu, attn, t, sum, out, gout, grad_left, grad_kv, grad_msg, grad_mu, H, F / 4,
+                        use_smem)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -610,6 +610,29 @@ void hetb200_backward_hgt_fused_softmax_aggregation_csr(
            op);
 }
 
+// hetb200 fusion: the whole backward of hetb200_hgt_fused_attention_aggregation_csr in one out-CSR pass.
+void hetb200_backward_hgt_fused_attention_aggregation_csr(
+    Tensor &outcsr_row_ptrs, Tensor &outcsr_col_indices, Tensor &outcsr_eids, Tensor &outcsr_reltypes,
+    Tensor &left_idx, Tensor &msg_idx, Tensor &left_compact, Tensor &k, Tensor &messages_compact, Tensor &mu,
+    Tensor &attn, Tensor &t, Tensor &sum, Tensor &out, Tensor &gradout, Tensor &grad_left, Tensor &grad_k,
+    Tensor &grad_message_compact, Tensor &grad_mu) {
+  const char *op = "hetb200_backward_hgt_fused_attention_aggregation_csr";
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(messages_compact) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_fused_bwd_csr(
+               i64(outcsr_row_ptrs, op, "outcsr_row_ptrs"), i64(outcsr_col_indices, op, "outcsr_col_indices"),
+               i64(outcsr_eids, op, "outcsr_eids"), i64(outcsr_reltypes, op, "outcsr_reltypes"),
+               outcsr_row_ptrs.numel() - 1, outcsr_eids.numel(), mu.size(0), f32(left_compact, op, "left_compact"),
+               i64(left_idx, op, "left_idx"), f32(k, op, "k"), f32(messages_compact, op, "messages_compact"),
+               i64(msg_idx, op, "msg_idx"), f32(mu, op, "mu"), f32(attn, op, "attn"), f32(t, op, "t"),
+               f32(sum, op, "sum"), f32(out, op, "out"), f32(gradout, op, "gradout"),
+               f32w(grad_left, op, "grad_left"), f32w(grad_k, op, "grad_k"),
+               f32w(grad_message_compact, op, "grad_message_compact"), f32w(grad_mu, op, "grad_mu"), H, F,
+               stream_of(gradout)),
+           op);
+}
+
 // ---------------------------------------------------------------- loss ---
 // hetb200 extension: fused log_softmax + nll_loss (sum / denom) of the training step.
 void hetb200_softmax_cross_entropy(Tensor &logits, Tensor &labels, double denom, Tensor &lse, Tensor &loss) {
@@ -834,6 +857,8 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   // HGT (OpExport/HGTOps.inc.h:656-674)
   m.def("hetb200_hgt_fused_attention_aggregation_csr", hetb200_hgt_fused_attention_aggregation_csr);
   m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
+  m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
+        hetb200_backward_hgt_fused_attention_aggregation_csr);
   m.def("hetb200_softmax_cross_entropy", hetb200_softmax_cross_entropy);
   m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);
