@@ -343,36 +343,58 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
         wq = torch.empty(Uc, H, F, device=dev)
         leg("segment_mm_fwd(unique (rel,dst) rows, q.W_att)", lambda: K.rgnn_relational_matmul(d_col, 1, Watt, q, wq, False),
             uniq_dst * D * 4 + Uc * D * 4 + R * H * F * F * 4 + Uc * 8, "Q_unique*D*s + U*D*s + W + U*i")
-        score = torch.empty(E, H, device=dev)
-        dinv = {"edata_idx_to_inverse_idx": icx}
-        leg("inner_product_fwd(compact left)", lambda: K.rgnn_inner_product_right_node_separatecoo(
-            dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, score),
-            Uc * D * 4 + uniq_src * D * 4 + 3 * E * 8 + E * H * 4, "left_c + right_unique + eid,row,inv ; score")
         mu = torch.ones(R, H, device=dev) / 4
-        ssum, t, norm = torch.empty(N, H, device=dev), torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
-        leg("hgt_edge_softmax_fwd(in-CSR)", lambda: K.hgt_full_graph_edge_softmax_ops_csr(
-            ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], score, mu, ssum, t, norm),
-            E * H * 4 + 2 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4, "a + eid,rel + row_ptr ; t + norm + sum")
         msg = torch.randn(Ur, H, F, device=dev)
         new_h = torch.empty(N, H, F, device=dev)
-        leg("hgt_aggregate_fwd(in-CSR, compact msg)", lambda: K.hetb200_hgt_message_aggregation_csr_compact(
-            ic["row_ptrs"], ic["eids"], ir, msg, t, ssum, new_h),
-            Ur * D * 4 + E * H * 4 + 2 * E * 8 + (N + 1) * 8 + N * H * 4 + N * D * 4, "msg_c + t + eid,inv + row_ptr + sum ; out")
         gout = torch.randn(N, H, F, device=dev)
-        gs = torch.randn(E, H, device=dev)
-        gl, gr = torch.zeros_like(wq), torch.zeros_like(k)
-        leg("inner_product_bwd(compact left)", lambda: K.backward_inner_product_right_node_separatecoo(
-            dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, gs, gl, gr),
-            2 * Uc * D * 4 + 2 * uniq_src * D * 4 + 3 * E * 8 + E * H * 4,
-            "left_c + right_unique + g + idx ; grad_left_c + grad_right_unique")
-        ga, gmu = torch.empty(E, H, device=dev), torch.zeros(R, H, device=dev)
-        leg("hgt_edge_softmax_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
-            oc["col_indices"], oc["eids"], oc["rel_types"], ir, msg, score, norm, new_h, gout, mu, ga, gmu),
-            Ur * D * 4 + 2 * E * H * 4 + 2 * N * D * 4 + 4 * E * 8 + E * H * 4, "msg_c + a,norm + out,gout + idx ; grad_a")
-        gm = torch.zeros_like(msg)
-        leg("hgt_aggregate_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_message_aggregation_csr_compact(
-            oc["col_indices"], oc["eids"], ir, norm, gout, gm),
-            E * H * 4 + N * D * 4 + 3 * E * 8 + Ur * D * 4, "norm + gout + idx ; grad_msg_c")
+        ssum = torch.empty(N, H, device=dev)
+        if getattr(layer, "fused_attention_aggregation_flag", False):
+            attn, t = torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
+            leg("hgt_fused_score_softmax_aggregate_fwd(in-CSR, compact)",
+                lambda: K.hetb200_hgt_fused_attention_aggregation_csr(
+                    ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], icx, ir, wq, k, msg, mu, attn, t,
+                    ssum, new_h),
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 5 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4 + N * D * 4,
+                "left_c + k_unique + msg_c + eid,rel,src,inv_col,inv_row + row_ptr ; score + exp + sum + out")
+            gl, gk, gm, gmu = torch.zeros_like(wq), torch.zeros_like(k), torch.zeros_like(msg), torch.zeros(R, H, device=dev)
+            leg("hgt_fused_edge_bwd(out-CSR, compact)",
+                lambda: K.hetb200_backward_hgt_fused_attention_aggregation_csr(
+                    oc["row_ptrs"], oc["col_indices"], oc["eids"], oc["rel_types"], icx, ir, wq, k, msg, mu, attn, t,
+                    ssum, new_h, gout, gl, gk, gm, gmu),
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 5 * E * 8 + (Ns + 1) * 8 + 2 * E * H * 4 + N * H * 4
+                + 2 * N * D * 4 + Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4,
+                "left_c,k,msg_c,idx,score,exp,sum,out,gout ; grad_left_c + grad_k + grad_msg_c")
+        else:
+            score = torch.empty(E, H, device=dev)
+            dinv = {"edata_idx_to_inverse_idx": icx}
+            leg("inner_product_fwd(compact left)", lambda: K.rgnn_inner_product_right_node_separatecoo(
+                dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, score),
+                Uc * D * 4 + uniq_src * D * 4 + 3 * E * 8 + E * H * 4, "left_c + right_unique + eid,row,inv ; score")
+            mu = torch.ones(R, H, device=dev) / 4
+            ssum, t, norm = torch.empty(N, H, device=dev), torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
+            leg("hgt_edge_softmax_fwd(in-CSR)", lambda: K.hgt_full_graph_edge_softmax_ops_csr(
+                ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], score, mu, ssum, t, norm),
+                E * H * 4 + 2 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4, "a + eid,rel + row_ptr ; t + norm + sum")
+            msg = torch.randn(Ur, H, F, device=dev)
+            new_h = torch.empty(N, H, F, device=dev)
+            leg("hgt_aggregate_fwd(in-CSR, compact msg)", lambda: K.hetb200_hgt_message_aggregation_csr_compact(
+                ic["row_ptrs"], ic["eids"], ir, msg, t, ssum, new_h),
+                Ur * D * 4 + E * H * 4 + 2 * E * 8 + (N + 1) * 8 + N * H * 4 + N * D * 4, "msg_c + t + eid,inv + row_ptr + sum ; out")
+            gout = torch.randn(N, H, F, device=dev)
+            gs = torch.randn(E, H, device=dev)
+            gl, gr = torch.zeros_like(wq), torch.zeros_like(k)
+            leg("inner_product_bwd(compact left)", lambda: K.backward_inner_product_right_node_separatecoo(
+                dinv, 2, coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"], wq, k, gs, gl, gr),
+                2 * Uc * D * 4 + 2 * uniq_src * D * 4 + 3 * E * 8 + E * H * 4,
+                "left_c + right_unique + g + idx ; grad_left_c + grad_right_unique")
+            ga, gmu = torch.empty(E, H, device=dev), torch.zeros(R, H, device=dev)
+            leg("hgt_edge_softmax_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
+                oc["col_indices"], oc["eids"], oc["rel_types"], ir, msg, score, norm, new_h, gout, mu, ga, gmu),
+                Ur * D * 4 + 2 * E * H * 4 + 2 * N * D * 4 + 4 * E * 8 + E * H * 4, "msg_c + a,norm + out,gout + idx ; grad_a")
+            gm = torch.zeros_like(msg)
+            leg("hgt_aggregate_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_message_aggregation_csr_compact(
+                oc["col_indices"], oc["eids"], ir, norm, gout, gm),
+                E * H * 4 + N * D * 4 + 3 * E * 8 + Ur * D * 4, "norm + gout + idx ; grad_msg_c")
     del flush
     return out
 

@@ -657,38 +657,54 @@ __global__ void __launch_bounds__(kThreads)
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
   const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  const int64_t iters = ceil_div64(E, stride);
-  int64_t i = (int64_t)blockIdx.x * GROUPS + g;
-  for (int64_t it = 0; it < iters; ++it, i += stride) {
-    const bool ok = i < E;
-    float t = 0.f;
-    int64_t e = 0;
-    float a = 0.f, slope_g = 0.f;
-    if (ok) {
-      e = __ldg(eids + i);
-      const int64_t d = __ldg(dst_idx + i);
-      const float sd = __ldg(sum + d * H + h);
-      a = sd != 0.f ? __ldg(exp_in + e * H + h) / sd : 0.f;
-      const int64_t ea = elidx ? __ldg(elidx + e) : e, eb = eridx ? __ldg(eridx + e) : e;
-      const float x = __ldg(el + ea * H + h) + __ldg(er + eb * H + h);
-      slope_g = x > 0.f ? 1.f : slope;
-      const float4 go = ldg4(gout + d * D + 4 * l);
-      const float4 rv = ldg4(ret + d * D + 4 * l);
-      const int64_t ef = fidx ? __ldg(fidx + e) : e;
-      const float4 fv = fidx ? ldg4(feat + ef * D + 4 * l) : ldcs4(feat + e * D + 4 * l);
-      const float4 gf = make_float4(a * go.x, a * go.y, a * go.z, a * go.w);
-      if (fidx) red_add4(grad_feat + ef * D + 4 * l, gf);  // compact row: summed over its edges
-      else stcs4(grad_feat + e * D + 4 * l, gf);
-      t = go.x * (fv.x - rv.x) + go.y * (fv.y - rv.y) + go.z * (fv.z - rv.z) +
-          go.w * (fv.w - rv.w);
+  constexpr int U = 1;  // edges in flight per lane group (4 was measured slower: the reductions into compact rows contend)
+  const int64_t iters = ceil_div64(E, stride * U);
+  int64_t i0 = (int64_t)blockIdx.x * GROUPS + g;
+  for (int64_t it = 0; it < iters; ++it, i0 += stride * U) {
+    bool ok[U];
+    int64_t e[U], d[U], ef[U], ea[U], eb[U];
+    float a[U], slope_g[U], t[U];
+    float4 go[U], rv[U], fv[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t i = i0 + j * stride;
+      ok[j] = i < E;
+      e[j] = ok[j] ? __ldg(eids + i) : 0;
+      d[j] = ok[j] ? __ldg(dst_idx + i) : 0;
     }
-    t = group_sum(t, hw);
-    if (ok && leader) {
-      const float v = t * a * slope_g;
-      if (elidx) atomicAdd(grad_el + __ldg(elidx + e) * H + h, v);
-      else grad_el[e * H + h] = v;
-      if (eridx) atomicAdd(grad_er + __ldg(eridx + e) * H + h, v);
-      else grad_er[e * H + h] = v;
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      ef[j] = fidx ? __ldg(fidx + e[j]) : e[j];
+      ea[j] = elidx ? __ldg(elidx + e[j]) : e[j];
+      eb[j] = eridx ? __ldg(eridx + e[j]) : e[j];
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      go[j] = ldg4(gout + d[j] * D + 4 * l);
+      rv[j] = ldg4(ret + d[j] * D + 4 * l);
+      fv[j] = fidx ? ldg4(feat + ef[j] * D + 4 * l) : ldcs4(feat + e[j] * D + 4 * l);
+      const float sd = __ldg(sum + d[j] * H + h);
+      a[j] = sd != 0.f ? __ldg(exp_in + e[j] * H + h) / sd : 0.f;
+      const float x = __ldg(el + ea[j] * H + h) + __ldg(er + eb[j] * H + h);
+      slope_g[j] = x > 0.f ? 1.f : slope;
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      if (ok[j]) {
+        const float4 gf = make_float4(a[j] * go[j].x, a[j] * go[j].y, a[j] * go[j].z, a[j] * go[j].w);
+        if (fidx) red_add4(grad_feat + ef[j] * D + 4 * l, gf);  // compact row: summed over its edges
+        else stcs4(grad_feat + e[j] * D + 4 * l, gf);
+      }
+      t[j] = go[j].x * (fv[j].x - rv[j].x) + go[j].y * (fv[j].y - rv[j].y) + go[j].z * (fv[j].z - rv[j].z) +
+             go[j].w * (fv[j].w - rv[j].w);
+      t[j] = group_sum(t[j], hw);
+      if (ok[j] && leader) {
+        const float v = t[j] * a[j] * slope_g[j];
+        if (elidx) atomicAdd(grad_el + ea[j] * H + h, v);
+        else grad_el[e[j] * H + h] = v;
+        if (eridx) atomicAdd(grad_er + eb[j] * H + h, v);
+        else grad_er[e[j] * H + h] = v;
+      }
     }
   }
 }

@@ -1,6 +1,6 @@
 """Multi-GPU parity: destination-range sharded training step (NCCL) vs the single-GPU step.
 Run:  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-          --master-port 29511 tools/check_sharded.py [rgat|hgt]
+          --master-port 29511 tools/check_sharded.py [rgat|hgt] [compact]
 Every rank also runs the unsharded step on its own GPU and compares its shard of the
 logits, the loss and every (all-reduced) weight gradient. rtol 1e-4 (fp32 summation order)."""
 import os
@@ -22,7 +22,11 @@ dist.init_process_group("nccl", device_id=dev)
 
 coo = graphs.bgs_shaped(scale=0.2) if kind == "rgat" else graphs.mag_shaped(scale=0.01)
 heads, layers = (1, 1) if kind == "rgat" else (4, 2)
-sh = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world, cuda_graph=False)
+# "compact": the sharded arm runs the bench defaults (compact-as-of-node + fused HGT edge pass); the
+# single-GPU arm stays on the per-edge path, so the comparison crosses both implementations
+compact = len(sys.argv) > 2 and sys.argv[2] == "compact"
+sh = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world, cuda_graph=False,
+                      compact_as_of_node=compact, fused=compact)
 full = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=0, world=1, cuda_graph=False)
 
 
