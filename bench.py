@@ -311,7 +311,9 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
     x = torch.rand(Ns, D, device=dev) * 2 - 1
     d_row = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"], "unique_srcs_and_dests_node_indices": u["node_indices_row"]}
     d_col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"], "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
-    ir, icx = u["inverse_idx_row"], u["inverse_idx_col"]
+    ir, icx = u["inverse_idx_row"], u["inverse_idx_col"]                      # by edge id (COO ops)
+    iir, iic = u["incsr_inverse_idx_row"], u["incsr_inverse_idx_col"]        # aligned with the in-CSR
+    oir, oic = u["outcsr_inverse_idx_row"], u["outcsr_inverse_idx_col"]      # aligned with the out-CSR
     if trainer.kind == "rgat":
         W = layer.conv_weights.detach().contiguous()
         WT = W.transpose(2, 3).contiguous()
@@ -321,14 +323,14 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
         el, er = torch.randn(Ur, H, 1, device=dev), torch.randn(Uc, H, 1, device=dev)
         ssum, ex, ret = torch.empty(N, H, device=dev), torch.empty(E, H, 1, device=dev), torch.empty(N, H, F, device=dev)
         leg("rgat_edge_softmax_aggregate_fwd(in-CSR, compact)",
-            lambda: K.hetb200_relational_fused_gat_csr_compact(ic["row_ptrs"], ic["eids"], ir, icx, feat, el, er, ssum, ex,
+            lambda: K.hetb200_relational_fused_gat_csr_compact(ic["row_ptrs"], ic["eids"], iir, iic, feat, el, er, ssum, ex,
                                                                ret, 0.2),
             Ur * D * 4 + (Ur + Uc) * H * 4 + 3 * E * 8 + (N + 1) * 8 + E * H * 4 + N * H * 4 + N * D * 4,
             "feat_c + el_c,er_c + eid,inv_row,inv_col + row_ptr ; exp + sum + ret")
         gout = torch.randn(N, H, F, device=dev)
         gf, gel, ger = torch.zeros_like(feat), torch.zeros_like(el), torch.zeros_like(er)
         leg("rgat_edge_bwd(out-CSR, compact)",
-            lambda: K.hetb200_backward_relational_fused_gat_csr_compact(oc["col_indices"], oc["eids"], ir, icx, feat, el, er,
+            lambda: K.hetb200_backward_relational_fused_gat_csr_compact(oc["col_indices"], oc["eids"], oir, oic, feat, el, er,
                                                                         ssum, ex, ret, gout, gf, gel, ger, 0.2),
             2 * Ur * D * 4 + 2 * (Ur + Uc) * H * 4 + E * H * 4 + N * H * 4 + 2 * N * D * 4 + 4 * E * 8,
             "feat_c,el_c,er_c,exp,sum,ret,gout,idx ; grad_feat_c,grad_el_c,grad_er_c")
@@ -352,14 +354,14 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
             attn, t = torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
             leg("hgt_fused_score_softmax_aggregate_fwd(in-CSR, compact)",
                 lambda: K.hetb200_hgt_fused_attention_aggregation_csr(
-                    ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], icx, ir, wq, k, msg, mu, attn, t,
+                    ic["row_ptrs"], ic["col_indices"], ic["eids"], ic["rel_types"], iic, iir, wq, k, msg, mu, attn, t,
                     ssum, new_h),
                 Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 5 * E * 8 + (N + 1) * 8 + 2 * E * H * 4 + N * H * 4 + N * D * 4,
                 "left_c + k_unique + msg_c + eid,rel,src,inv_col,inv_row + row_ptr ; score + exp + sum + out")
             gl, gk, gm, gmu = torch.zeros_like(wq), torch.zeros_like(k), torch.zeros_like(msg), torch.zeros(R, H, device=dev)
             leg("hgt_fused_edge_bwd(out-CSR, compact)",
                 lambda: K.hetb200_backward_hgt_fused_attention_aggregation_csr(
-                    oc["row_ptrs"], oc["col_indices"], oc["eids"], oc["rel_types"], icx, ir, wq, k, msg, mu, attn, t,
+                    oc["row_ptrs"], oc["col_indices"], oc["eids"], oc["rel_types"], oic, oir, wq, k, msg, mu, attn, t,
                     ssum, new_h, gout, gl, gk, gm, gmu),
                 Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 5 * E * 8 + (Ns + 1) * 8 + 2 * E * H * 4 + N * H * 4
                 + 2 * N * D * 4 + Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4,
@@ -378,7 +380,7 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
             msg = torch.randn(Ur, H, F, device=dev)
             new_h = torch.empty(N, H, F, device=dev)
             leg("hgt_aggregate_fwd(in-CSR, compact msg)", lambda: K.hetb200_hgt_message_aggregation_csr_compact(
-                ic["row_ptrs"], ic["eids"], ir, msg, t, ssum, new_h),
+                ic["row_ptrs"], ic["eids"], iir, msg, t, ssum, new_h),
                 Ur * D * 4 + E * H * 4 + 2 * E * 8 + (N + 1) * 8 + N * H * 4 + N * D * 4, "msg_c + t + eid,inv + row_ptr + sum ; out")
             gout = torch.randn(N, H, F, device=dev)
             gs = torch.randn(E, H, device=dev)
@@ -389,11 +391,11 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
                 "left_c + right_unique + g + idx ; grad_left_c + grad_right_unique")
             ga, gmu = torch.empty(E, H, device=dev), torch.zeros(R, H, device=dev)
             leg("hgt_edge_softmax_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
-                oc["col_indices"], oc["eids"], oc["rel_types"], ir, msg, score, norm, new_h, gout, mu, ga, gmu),
+                oc["col_indices"], oc["eids"], oc["rel_types"], oir, msg, score, norm, new_h, gout, mu, ga, gmu),
                 Ur * D * 4 + 2 * E * H * 4 + 2 * N * D * 4 + 4 * E * 8 + E * H * 4, "msg_c + a,norm + out,gout + idx ; grad_a")
             gm = torch.zeros_like(msg)
             leg("hgt_aggregate_bwd(out-CSR, compact msg)", lambda: K.hetb200_backward_hgt_message_aggregation_csr_compact(
-                oc["col_indices"], oc["eids"], ir, norm, gout, gm),
+                oc["col_indices"], oc["eids"], oir, norm, gout, gm),
                 E * H * 4 + N * D * 4 + 3 * E * 8 + Ur * D * 4, "norm + gout + idx ; grad_msg_c")
     del flush
     return out
@@ -550,9 +552,20 @@ def main():
     }
     if not args.no_roofline:
         legs = (kernel_rooflines_compact if args.compact else kernel_rooflines)(trainer, peak, peak_src)
+        # measured DRAM traffic per launch (one ncu --set full capture, profiles/ncu_traffic.json), only for
+        # the configuration it was captured on; "dram_frac" = that traffic / this run's kernel time / peak
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                traffic = json.load(f).get(args.workload, {}) if (scale == 1.0 and args.compact and args.fused) else {}
+        except (OSError, ValueError):
+            traffic = {}
+        for d in legs:
+            if d["kernel"] in traffic:
+                d["traffic"] = int(traffic[d["kernel"]])
+                d["dram_frac"] = round(d["traffic"] / (d["ms"] * 1e-3) / 1e9 / peak, 4)
         top = max(legs, key=lambda d: d["ms"])
-        line["roofline"] = {k: top[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "kernel",
-                                                 "ms", "algorithmic_bytes", "peak_source")}
+        line["roofline"] = {k: top.get(k) for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "dram_frac",
+                                                     "kernel", "ms", "algorithmic_bytes", "peak_source")}
         line["kernels"] = legs
     if world == 1 and not args.no_cpu_baseline:
         del trainer

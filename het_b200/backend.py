@@ -326,12 +326,13 @@ class RelationalFusedGatCSRCompact(th.autograd.Function):
     (rgat_layers_and_funcs.py:325-470, relational_fused_gat_compact_as_of_node_separate_coo_single_sided)."""
 
     @staticmethod
-    def forward(ctx, incsr_row_ptr, incsr_eids, outcsr_col_indices, outcsr_eids, inverse_row, inverse_col,
-                feat_compact, el_compact, er_compact, s, exp, ret, slope):
+    def forward(ctx, incsr_row_ptr, incsr_eids, outcsr_col_indices, outcsr_eids, in_inverse_row, in_inverse_col,
+                inverse_row, inverse_col, feat_compact, el_compact, er_compact, s, exp, ret, slope):
+        # in_inverse_* are aligned with incsr_eids, inverse_* with outcsr_eids
         ctx.mark_dirty(ret)
         K.hetb200_relational_fused_gat_csr_compact(
-            incsr_row_ptr, incsr_eids, inverse_row, inverse_col, feat_compact, el_compact, er_compact, s, exp,
-            ret, slope)
+            incsr_row_ptr, incsr_eids, in_inverse_row, in_inverse_col, feat_compact, el_compact, er_compact, s,
+            exp, ret, slope)
         ctx.save_for_backward(outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat_compact,
                               el_compact, er_compact, s, exp, ret)
         ctx.slope = slope
@@ -346,7 +347,7 @@ class RelationalFusedGatCSRCompact(th.autograd.Function):
         K.hetb200_backward_relational_fused_gat_csr_compact(
             outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat, el, er, s, exp, ret,
             gradout.contiguous(), grad_feat, grad_el, grad_er, ctx.slope)
-        return (None,) * 6 + (grad_feat, grad_el, grad_er, None, None, None, None)
+        return (None,) * 8 + (grad_feat, grad_el, grad_er, None, None, None, None)
 
 
 def relational_fused_gat_csr_compact(graph, feat_compact, el_compact, er_compact, slope):
@@ -357,9 +358,9 @@ def relational_fused_gat_csr_compact(graph, feat_compact, el_compact, er_compact
     s = el_compact.new_empty([graph.get_num_nodes(), h])
     ret = el_compact.new_empty([graph.get_num_nodes()] + list(feat_compact.size()[1:]))
     return RelationalFusedGatCSRCompact.apply(
-        incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["inverse_idx_row"],
-        uniq["inverse_idx_col"], feat_compact.contiguous(), el_compact.contiguous(), er_compact.contiguous(),
-        s, exp, ret, slope)
+        incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["incsr_inverse_idx_row"],
+        uniq["incsr_inverse_idx_col"], uniq["outcsr_inverse_idx_row"], uniq["outcsr_inverse_idx_col"],
+        feat_compact.contiguous(), el_compact.contiguous(), er_compact.contiguous(), s, exp, ret, slope)
 
 
 class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact(th.autograd.Function):
@@ -368,14 +369,15 @@ class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact(th.autograd.
 
     @staticmethod
     def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, outcsr_col_indices,
-                outcsr_eids, outcsr_reltypes, msg_idx, unnormalized_attn_score, mu, ssum, t, norm,
+                outcsr_eids, outcsr_reltypes, in_msg_idx, msg_idx, unnormalized_attn_score, mu, ssum, t, norm,
                 message_compact, new_h):
+        # in_msg_idx is aligned with incsr_eids, msg_idx with outcsr_eids
         ctx.mark_dirty(new_h)
         K.hgt_full_graph_edge_softmax_ops_csr(
             incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, unnormalized_attn_score, mu, ssum, t,
             norm)
         K.hetb200_hgt_message_aggregation_csr_compact(
-            incsr_row_ptrs, incsr_eids, msg_idx, message_compact, t, ssum, new_h)
+            incsr_row_ptrs, incsr_eids, in_msg_idx, message_compact, t, ssum, new_h)
         ctx.save_for_backward(outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx,
                               unnormalized_attn_score, mu, norm, message_compact, new_h)
         return new_h
@@ -393,7 +395,7 @@ class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact(th.autograd.
         K.hetb200_backward_hgt_edge_softmax_ops_csr_compact(
             outcsr_col_indices, outcsr_eids, outcsr_reltypes, msg_idx, message_compact, unnormalized_attn_score,
             norm, new_h, gradout, mu, grad_attn_score, grad_mu)
-        return (None,) * 8 + (grad_attn_score, grad_mu, None, None, None, grad_message, None)
+        return (None,) * 9 + (grad_attn_score, grad_mu, None, None, None, grad_message, None)
 
 
 def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(graph, message_compact,
@@ -407,8 +409,8 @@ def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(graph, 
     norm = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
     return HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact.apply(
         incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["col_indices"],
-        outcsr["eids"], outcsr["rel_types"], uniq["inverse_idx_row"], unnormalized_attn_score.contiguous(),
-        mu.contiguous(), ssum, t, norm, message_compact.contiguous(), new_h)
+        outcsr["eids"], outcsr["rel_types"], uniq["incsr_inverse_idx_row"], uniq["outcsr_inverse_idx_row"],
+        unnormalized_attn_score.contiguous(), mu.contiguous(), ssum, t, norm, message_compact.contiguous(), new_h)
 
 
 class HGTFusedAttentionAggregationCSRCompact(th.autograd.Function):
@@ -419,12 +421,13 @@ class HGTFusedAttentionAggregationCSRCompact(th.autograd.Function):
 
     @staticmethod
     def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, outcsr_row_ptrs,
-                outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx, msg_idx, left_compact, k,
-                message_compact, mu, attn, t, ssum, new_h):
+                outcsr_col_indices, outcsr_eids, outcsr_reltypes, in_left_idx, in_msg_idx, left_idx, msg_idx,
+                left_compact, k, message_compact, mu, attn, t, ssum, new_h):
+        # in_*_idx are aligned with incsr_eids, *_idx with outcsr_eids
         ctx.mark_dirty(new_h)
         K.hetb200_hgt_fused_attention_aggregation_csr(
-            incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, left_idx, msg_idx, left_compact, k,
-            message_compact, mu, attn, t, ssum, new_h)
+            incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, in_left_idx, in_msg_idx, left_compact,
+            k, message_compact, mu, attn, t, ssum, new_h)
         ctx.save_for_backward(outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx,
                               msg_idx, left_compact, k, message_compact, mu, attn, t, ssum, new_h)
         return new_h
@@ -440,7 +443,7 @@ class HGTFusedAttentionAggregationCSRCompact(th.autograd.Function):
         K.hetb200_backward_hgt_fused_attention_aggregation_csr(
             outcsr_row_ptrs, outcsr_col_indices, outcsr_eids, outcsr_reltypes, left_idx, msg_idx, left, k, msg,
             mu, attn, t, ssum, new_h, gradout.contiguous(), grad_left, grad_k, grad_msg, grad_mu)
-        return (None,) * 10 + (grad_left, grad_k, grad_msg, grad_mu, None, None, None, None)
+        return (None,) * 12 + (grad_left, grad_k, grad_msg, grad_mu, None, None, None, None)
 
 
 def hgt_fused_attention_and_aggregation_csr_compact(graph, left_compact, k, message_compact, mu):
@@ -453,8 +456,9 @@ def hgt_fused_attention_and_aggregation_csr_compact(graph, left_compact, k, mess
     t = message_compact.new_empty(e, h)
     return HGTFusedAttentionAggregationCSRCompact.apply(
         incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], outcsr["row_ptrs"],
-        outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"], uniq["inverse_idx_col"],
-        uniq["inverse_idx_row"], left_compact.contiguous(),
+        outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"], uniq["incsr_inverse_idx_col"],
+        uniq["incsr_inverse_idx_row"], uniq["outcsr_inverse_idx_col"], uniq["outcsr_inverse_idx_row"],
+        left_compact.contiguous(),
         k.contiguous(), message_compact.contiguous(), mu.contiguous(), attn, t, ssum, new_h)
 
 

@@ -91,8 +91,10 @@ __global__ void __launch_bounds__(kThreads)
                            float *__restrict__ sum, float *__restrict__ exp_out,
                            float *__restrict__ ret, int H, int hw, float slope,
                            int divide,
-                           // compact-as-of-node with direct indexing (all indexed by edge id,
-                           // NULL = the tensor is per-edge): row of feat / wa / wb to read
+                           // compact-as-of-node with direct indexing (NULL = the tensor is per-edge):
+                           // row of feat / wa / wb to read, ALIGNED WITH eids (one entry per CSR
+                           // position, = inverse_idx[eids[p]] gathered once at plan time, so the edge
+                           // pass has one dependent load level less and no random 8-byte gathers)
                            const int64_t *__restrict__ fidx,
                            const int64_t *__restrict__ waidx,
                            const int64_t *__restrict__ wbidx) {
@@ -162,14 +164,14 @@ __global__ void __launch_bounds__(kThreads)
       for (int j = 0; j < 4; ++j) e[j] = __ldg(eids + p + j);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int64_t ea = waidx ? __ldg(waidx + e[j]) : e[j];
+        const int64_t ea = waidx ? __ldg(waidx + p + j) : e[j];
         if (MODE == 0) {
-          const int64_t eb = wbidx ? __ldg(wbidx + e[j]) : e[j];
+          const int64_t eb = wbidx ? __ldg(wbidx + p + j) : e[j];
           w[j] = __ldg(wa + ea * H + h) + __ldg(wb + eb * H + h);
         } else {
           w[j] = __ldg(wa + ea * H + h) * inv_d;
         }
-        v[j] = fidx ? ldg4(feat + __ldg(fidx + e[j]) * D + 4 * l) : ldcs4(feat + e[j] * D + 4 * l);
+        v[j] = fidx ? ldg4(feat + __ldg(fidx + p + j) * D + 4 * l) : ldcs4(feat + e[j] * D + 4 * l);
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -183,16 +185,16 @@ __global__ void __launch_bounds__(kThreads)
     }
     for (; p < stop; ++p) {
       const int64_t e = __ldg(eids + p);
-      const int64_t ea = waidx ? __ldg(waidx + e) : e;
+      const int64_t ea = waidx ? __ldg(waidx + p) : e;
       float w;
       if (MODE == 0) {
-        const int64_t eb = wbidx ? __ldg(wbidx + e) : e;
+        const int64_t eb = wbidx ? __ldg(wbidx + p) : e;
         w = leaky_exp(__ldg(wa + ea * H + h) + __ldg(wb + eb * H + h), slope);
         if (leader) exp_out[e * H + h] = w;
       } else {
         w = __ldg(wa + ea * H + h) * inv_d;
       }
-      fma4(acc, w, fidx ? ldg4(feat + __ldg(fidx + e) * D + 4 * l) : ldcs4(feat + e * D + 4 * l));
+      fma4(acc, w, fidx ? ldg4(feat + __ldg(fidx + p) * D + 4 * l) : ldcs4(feat + e * D + 4 * l));
       s += w;
     }
   }
@@ -271,8 +273,8 @@ __global__ void __launch_bounds__(kThreads)
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      li[j] = left_idx ? __ldg(left_idx + e[j]) : e[j];
-      mi[j] = msg_idx ? __ldg(msg_idx + e[j]) : e[j];
+      li[j] = left_idx ? __ldg(left_idx + (ok[j] ? p0 + q + j : 0)) : e[j];
+      mi[j] = msg_idx ? __ldg(msg_idx + (ok[j] ? p0 + q + j : 0)) : e[j];
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -384,8 +386,8 @@ __global__ void __launch_bounds__(kThreads)
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      li[j] = left_idx ? __ldg(left_idx + e[j]) : e[j];
-      mi[j] = msg_idx ? __ldg(msg_idx + e[j]) : e[j];
+      li[j] = left_idx ? __ldg(left_idx + (ok[j] ? p0 + q + j : 0)) : e[j];
+      mi[j] = msg_idx ? __ldg(msg_idx + (ok[j] ? p0 + q + j : 0)) : e[j];
       tt[j] = __ldg(t + e[j] * H + h);
       aa[j] = __ldg(attn + e[j] * H + h);
       sd[j] = __ldg(sum + dn[j] * H + h);
@@ -674,9 +676,9 @@ __global__ void __launch_bounds__(kThreads)
     }
 #pragma unroll
     for (int j = 0; j < U; ++j) {
-      ef[j] = fidx ? __ldg(fidx + e[j]) : e[j];
-      ea[j] = elidx ? __ldg(elidx + e[j]) : e[j];
-      eb[j] = eridx ? __ldg(eridx + e[j]) : e[j];
+      ef[j] = fidx ? __ldg(fidx + (ok[j] ? i0 + j * stride : 0)) : e[j];
+      ea[j] = elidx ? __ldg(elidx + (ok[j] ? i0 + j * stride : 0)) : e[j];
+      eb[j] = eridx ? __ldg(eridx + (ok[j] ? i0 + j * stride : 0)) : e[j];
     }
 #pragma unroll
     for (int j = 0; j < U; ++j) {
@@ -733,7 +735,7 @@ __global__ void __launch_bounds__(kThreads)
     }
     const float4 go = ldg4(gout + d * D + 4 * l);
     const float4 gm = make_float4(a * go.x, a * go.y, a * go.z, a * go.w);
-    if (midx) red_add4(grad_msg + __ldg(midx + e) * D + 4 * l, gm);  // compact row: summed
+    if (midx) red_add4(grad_msg + __ldg(midx + i) * D + 4 * l, gm);  // compact row: summed
     else stcs4(grad_msg + e * D + 4 * l, gm);
   }
 }
@@ -781,7 +783,7 @@ __global__ void __launch_bounds__(kThreads)
       d = __ldg(dst_idx + i);
       const float4 go = ldg4(gout + d * D + 4 * l);
       const float4 ov = ldg4(out + d * D + 4 * l);
-      const float4 mv = midx ? ldg4(msg + __ldg(midx + e) * D + 4 * l) : ldcs4(msg + e * D + 4 * l);
+      const float4 mv = midx ? ldg4(msg + __ldg(midx + i) * D + 4 * l) : ldcs4(msg + e * D + 4 * l);
       s = go.x * (mv.x - ov.x) + go.y * (mv.y - ov.y) + go.z * (mv.z - ov.z) +
           go.w * (mv.w - ov.w);
     }

@@ -102,6 +102,7 @@ class HetGraph:
         ``node_indices_<side>``  [U]    node id of every unique (relation, node) pair
         ``inverse_idx_<side>``   [E]    compact row of edge id e ("edata_idx_to_inverse_idx";
                                          edge ids are separate-COO positions after canonicalisation)
+        ``incsr_inverse_idx_<side>``, ``outcsr_inverse_idx_<side>``  [E]  the same per CSR position
         with side ``row`` = sources, ``col`` = destinations."""
         if getattr(self, "_unique_single_sided", None) is None:
             coo = self.separate_coo
@@ -118,6 +119,11 @@ class HetGraph:
                 out["node_indices_" + side] = (uniq % n).contiguous()
                 # eids are 0..E-1 in separate-COO order, so position == edge id
                 out["inverse_idx_" + side] = inverse.contiguous()
+                # the same map gathered into in-CSR / out-CSR position order (aligned with the
+                # eids array of that format): what the in-CSR / out-CSR edge kernels read, one
+                # dependent load level less than inverse_idx[eids[p]]
+                out["incsr_inverse_idx_" + side] = inverse[self.in_csr["eids"]].contiguous()
+                out["outcsr_inverse_idx_" + side] = inverse[self.out_csr["eids"]].contiguous()
             self._unique_single_sided = out
         return self._unique_single_sided
 

@@ -122,8 +122,10 @@ int hetb_inner_product_bwd(const int64_t *eids, const int64_t *row_idx,
 /* Compact-as-of-node with direct indexing (CompactAsOfNodeKind 2 / 4,
  * hrt/include/kernel_enums.h:6-48; "edata_idx_to_inverse_idx[_row|_col]"): when a
  * pointer is non-NULL the corresponding tensor holds one row per unique
- * (relation, node) pair instead of one per edge, and row X_idx[e] is the one edge id e
- * uses. Gradients of a compact tensor are SUMMED into it (it must arrive zero-filled). */
+ * (relation, node) pair instead of one per edge. The index arrays of the CSR / edge-list
+ * ops are ALIGNED WITH THE eids ARGUMENT: X_idx[p] = edata_idx_to_inverse_idx[eids[p]],
+ * gathered once when the graph is built, so the edge pass has one dependent load level
+ * less. Gradients of a compact tensor are SUMMED into it (it must arrive zero-filled). */
 typedef struct hetb_compact_idx {
   const int64_t *feat_idx; /* feat / grad_feat rows  (by source:      ..._row) */
   const int64_t *el_idx;   /* el / grad_el rows      (by source:      ..._row) */
@@ -198,7 +200,7 @@ int hetb_hgt_aggregate_fwd_csr(const int64_t *row_ptr, const int64_t *eids,
                                const float *msg, const float *score,
                                const float *sum, float *ret, int H, int F,
                                int divide_by_sum,
-                               const int64_t *msg_idx /* NULL, or compact msg row per edge id */,
+                               const int64_t *msg_idx /* NULL, or compact msg row per position (aligned with eids) */,
                                void *stream);
 
 /* grad_msg[e,h,:] = norm[e,h] · gout[dst_idx[p],h,:]
@@ -225,7 +227,7 @@ int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
                               const float *out, const float *gout,
                               const float *mu, float *grad_attn,
                               float *grad_mu, int H, int F,
-                              const int64_t *msg_idx /* NULL, or compact msg row per edge id */,
+                              const int64_t *msg_idx /* NULL, or compact msg row per position (aligned with eids) */,
                               const float *sum_div /* non-NULL: norm holds exp(mu·score), divide by sum[d,h] */,
                               void *stream);
 
@@ -234,7 +236,7 @@ int hetb_hgt_edge_softmax_bwd(const int64_t *dst_idx, const int64_t *eids,
  * hgt_full_graph_message_mean_aggregation_csr; same maths, reference files as those three):
  *   attn[e,h] = Σ_f left[L(e),h,f]·kv[src[p],h,f];  t[e,h] = exp(attn·mu[rel[p],h]);
  *   sum[d,h] = Σ_p t;  ret[d,h,:] = Σ_p t[e,h]·msg[M(e),h,:] / sum[d,h]
- * with L(e) = left_idx ? left_idx[e] : e and M(e) = msg_idx ? msg_idx[e] : e. */
+ * with L(e) = left_idx ? left_idx[p] : e and M(e) = msg_idx ? msg_idx[p] : e (aligned with eids). */
 int hetb_hgt_fused_fwd_csr(const int64_t *row_ptr, const int64_t *eids, const int64_t *rel,
                            const int64_t *src, int64_t num_rows, int64_t num_edges,
                            const float *left, const int64_t *left_idx, const float *kv,
