@@ -143,6 +143,68 @@ class FullGraphTrainer:
             dist.all_reduce(loss, group=self.group)
         return float(loss.item())
 
+    def run_from_host(self, batches) -> list:
+        """Pipelined epochs over an iterable of (x_host, labels_host) pinned-memory pairs: while step
+        i computes, a copy stream already moves step i+1's inputs into the other of two device
+        staging buffers, and step i's loss comes back through a pinned slot that is read one step
+        later. Every step still pays its own H2D copy and its own D2H loss read; they just overlap
+        the previous / next step's kernels instead of serialising with them. Returns the losses."""
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_pipe", None) is None:
+            self._pipe = {
+                "copy": torch.cuda.Stream(dev),
+                "x": [torch.empty_like(self.x_in, requires_grad=False) for _ in range(2)],
+                "y": [torch.empty_like(self.labels_in) for _ in range(2)],
+                "loss": [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)],
+                "ready": [torch.cuda.Event() for _ in range(2)],   # H2D into slot done
+                "free": [torch.cuda.Event() for _ in range(2)],    # slot consumed by the step
+                "done": [torch.cuda.Event() for _ in range(2)],    # loss of the step in the pinned slot
+            }
+        P = self._pipe
+        copy = P["copy"]
+        copy.wait_stream(main)
+
+        def prefetch(i, batch):
+            j = i & 1
+            with torch.cuda.stream(copy), torch.no_grad():
+                if i >= 2:
+                    copy.wait_event(P["free"][j])
+                P["x"][j].copy_(batch[0], non_blocking=True)
+                P["y"][j].copy_(batch[1], non_blocking=True)
+                P["ready"][j].record(copy)
+
+        losses = []
+        it = iter(batches)
+        nxt = next(it, None)
+        if nxt is not None:
+            prefetch(0, nxt)
+        i = 0
+        while nxt is not None:
+            cur, j = nxt, i & 1
+            nxt = next(it, None)
+            if nxt is not None:
+                prefetch(i + 1, nxt)
+            main.wait_event(P["ready"][j])
+            with torch.no_grad():
+                self.x_in.copy_(P["x"][j])
+                self.labels_in.copy_(P["y"][j])
+            P["free"][j].record(main)
+            if i >= 2:  # the pinned loss slot j is about to be reused: collect step i-2 first
+                P["done"][j].synchronize()
+                losses.append(float(P["loss"][j].item()))
+            loss = self._run("feat")
+            if self.world > 1:
+                loss = loss.clone()
+                dist.all_reduce(loss, group=self.group)
+            P["loss"][j].copy_(loss.reshape(1), non_blocking=True)
+            P["done"][j].record(main)
+            i += 1
+        for k in range(max(0, i - 2), i):
+            P["done"][k & 1].synchronize()
+            losses.append(float(P["loss"][k & 1].item()))
+        return losses
+
     def h2d_bytes_per_step(self) -> int:
         return self.n_local * self.x_in.shape[1] * 4 + self.n_local * 8
 
