@@ -30,9 +30,13 @@ class HET_RelGraphEmbed(nn.Module):
 class HET_RGATLayer(nn.Module):
     def __init__(self, in_feat, out_feat, num_rels, num_heads, *, bias=True, activation=None,
                  self_loop=False, gat_edge_parallel_flag=False, dropout=0.0, leaky_relu_slope=0.2,
-                 compact_as_of_node_flag=False):
+                 compact_as_of_node_flag=False, linear_reorder_flag=False):
         super().__init__()
         self.compact_as_of_node_flag = compact_as_of_node_flag
+        # Hector's linear operator reordering on the destination side (compact path only):
+        # er = (X.W_r).a_r = X.(W_r.a_r), so the (relation, destination) rows need one
+        # row-dot with a per-relation vector instead of a 64-wide typed linear layer.
+        self.linear_reorder_flag = linear_reorder_flag
         assert out_feat % num_heads == 0, "out_feat must be a multiple of num_heads"
         self.in_feat, self.out_feat = in_feat, out_feat
         self.num_rels, self.num_heads = num_rels, num_heads
@@ -97,11 +101,16 @@ class HET_RGATLayer(nn.Module):
         col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
                "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
         feat_compact = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
-        feat_compact_dst = B.rgnn_relational_matmul(col, self.conv_weights, inputs_dst, True, 1)
         el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
             u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
-        er_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
-            u["rel_ptrs_col"], self.attn_r.unsqueeze(-1), feat_compact_dst.view(feat_compact_dst.size(0), -1))
+        if self.linear_reorder_flag:
+            w_r = th.einsum("rhkf,rhf->rhk", self.conv_weights, self.attn_r)  # [R, H, in]
+            er_compact = B.rgnn_relational_matmul(col, w_r.unsqueeze(-1), inputs_dst, True, 1)
+        else:
+            feat_compact_dst = B.rgnn_relational_matmul(col, self.conv_weights, inputs_dst, True, 1)
+            er_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
+                u["rel_ptrs_col"], self.attn_r.unsqueeze(-1),
+                feat_compact_dst.view(feat_compact_dst.size(0), -1))
         return B.relational_fused_gat_csr_compact(
             g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
             self.leaky_relu_slope)

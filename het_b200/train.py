@@ -53,7 +53,8 @@ class FullGraphTrainer:
         torch.manual_seed(seed)  # identical replicated weights on every rank
         if kind == "rgat":
             self.model = HET_RGATModel(coo.num_rels, hidden, hidden, out_dim, heads, layers,
-                                       compact_as_of_node_flag=compact_as_of_node).to(self.device)
+                                       compact_as_of_node_flag=compact_as_of_node,
+                                       linear_reorder_flag=bool(fused and compact_as_of_node)).to(self.device)
         else:
             self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
                                            compact_as_of_node_flag=compact_as_of_node,

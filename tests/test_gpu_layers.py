@@ -27,13 +27,16 @@ def _coo_t(coo):
     ("aifb", 0.5, 1, True, False),
     # compact_as_of_node_flag: X.W_r once per unique (relation, node) pair, direct indexing
     ("aifb", 1.0, 1, False, True), ("bgs", 0.1, 1, False, True), ("bgs", 0.05, 4, False, True),
+    # + linear operator reordering of the destination logits: er = X.(W_r.a_r)
+    ("aifb", 1.0, 1, False, "reorder"), ("bgs", 0.1, 1, False, "reorder"), ("bgs", 0.05, 4, False, "reorder"),
 ])
 def test_rgat_layer_fwd_bwd(cuda, shape, scale, heads, edge_parallel, compact):
     from het_b200.models import HET_RGATLayer
     coo, g = _graph(cuda, shape, scale)
     torch.manual_seed(0)
     layer = HET_RGATLayer(64, 64, coo.num_rels, heads, gat_edge_parallel_flag=edge_parallel,
-                          compact_as_of_node_flag=compact).to(cuda)
+                          compact_as_of_node_flag=bool(compact),
+                          linear_reorder_flag=(compact == "reorder")).to(cuda)
     with torch.no_grad():
         layer.h_bias.uniform_(-0.1, 0.1)
     x = (torch.rand(coo.num_nodes, 64, device=cuda) * 2 - 1).requires_grad_(True)
