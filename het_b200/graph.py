@@ -84,6 +84,13 @@ class HetGraph:
     def get_original_node_type_offsets(self):
         return self.node_type_offsets
 
+    def get_relation_node_types(self):
+        """(source node type, destination node type) of every relation, or None when the graph
+        was built from bare arrays (canonical edge types, as DGL's heterograph keeps them)."""
+        if getattr(self, "rel_src_type", None) is None:
+            return None
+        return self.rel_src_type, self.rel_dst_type
+
     def get_separate_unique_node_indices(self):
         # the double-sided lists (binary-search compact kinds) are not built; the
         # non-compact ops ignore these tensors.

@@ -147,8 +147,12 @@ class HET_RGATModel(nn.Module):
 class HET_HGTLayerHetero(nn.Module):
     def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
                  compact_as_of_node_flag=False, compact_direct_indexing_flag=True,
-                 fused_attention_aggregation_flag=False):
+                 fused_attention_aggregation_flag=False, linear_reorder_flag=False):
         super().__init__()
+        # Hector's linear operator reordering (compact path): (h.W_q[type]).W_att[r] = h.(W_q[type].W_att[r])
+        # and the same for W_v / W_msg, so Q and V are never materialised; the composed [R, in, out]
+        # weights cost R small products per step. Needs one (src type, dst type) pair per relation.
+        self.linear_reorder_flag = linear_reorder_flag
         # compact_as_of_node_flag (hrt/python/HGT/models.py:177-208): W_att·Q is computed once per
         # unique (relation, destination) pair; here the same is also done for W_msg·V per unique
         # (relation, source) pair (a hetb200 extension, same maths). Only direct indexing is built.
@@ -181,9 +185,25 @@ class HET_HGTLayerHetero(nn.Module):
         """``gather`` (multi-GPU): all-gathers K and V rows of the owned destinations into
         the source-indexed matrices; Q stays local (it is gathered by destination)."""
         offs = G.get_original_node_type_offsets()
+        reorder = (self.linear_reorder_flag and self.compact_as_of_node_flag
+                   and G.get_relation_node_types() is not None)
         k = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
-        q = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.q_linears, h).view(-1, self.num_heads, self.d_k)
-        v = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.v_linears, h).view(-1, self.num_heads, self.d_k)
+        if reorder:
+            rel_src_type, rel_dst_type = G.get_relation_node_types()
+            H, dk = self.num_heads, self.d_k
+
+            def compose(lin, rel_w, types):  # [R, 1, in, out]: lin[type(r)] . blockdiag_h(rel_w[r, h])
+                w = th.einsum("rihd,rhde->rihe", lin[types, 0].view(-1, self.in_dim, H, dk), rel_w)
+                return w.reshape(-1, 1, self.in_dim, self.out_dim)
+
+            q = h  # stands for Q below: the composed weight carries W_q
+            v = h
+            w_att = compose(self.q_linears, self.relation_att, rel_dst_type)
+            w_msg = compose(self.v_linears, self.relation_msg, rel_src_type)
+        else:
+            q = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.q_linears, h).view(-1, self.num_heads, self.d_k)
+            v = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.v_linears, h).view(-1, self.num_heads, self.d_k)
+            w_att, w_msg = self.relation_att, self.relation_msg
         if gather is not None:
             k, v = gather(k), gather(v)
         coo = G.get_separate_coo_original()
@@ -199,10 +219,13 @@ class HET_HGTLayerHetero(nn.Module):
             u = G.get_separate_unique_node_indices_single_sided()
             attn_weight_dst_product_compact = B.rgnn_relational_matmul(
                 {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
-                 "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, self.relation_att, q, False, 1)
+                 "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, w_att, q, reorder, 1)
             message_compact = B.rgnn_relational_matmul(
                 {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
-                 "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, self.relation_msg, v, False, 1)
+                 "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, w_msg, v, reorder, 1)
+            if reorder:
+                attn_weight_dst_product_compact = attn_weight_dst_product_compact.view(-1, self.num_heads, self.d_k)
+                message_compact = message_compact.view(-1, self.num_heads, self.d_k)
             if self.fused_attention_aggregation_flag:
                 new_h = B.hgt_fused_attention_and_aggregation_csr_compact(
                     G, attn_weight_dst_product_compact, k, message_compact, self.relation_pri / self.sqrt_dk)

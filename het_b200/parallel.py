@@ -77,10 +77,13 @@ def make_shard(coo: HeteroCOO, rank: int, world: int) -> ShardPlan:
 
 def shard_graph(plan: ShardPlan, coo: HeteroCOO, device):
     from .graph import HetGraph
-    return HetGraph.from_arrays(
+    g = HetGraph.from_arrays(
         f"{coo.name}[{plan.rank}/{plan.world}]", torch.from_numpy(plan.src), torch.from_numpy(plan.dst),
         torch.from_numpy(plan.etype), plan.num_gathered_rows, plan.num_local_nodes, coo.num_rels,
         torch.from_numpy(plan.node_type_offsets), device)
+    g.rel_src_type = torch.from_numpy(coo.rel_src_type).to(device)
+    g.rel_dst_type = torch.from_numpy(coo.rel_dst_type).to(device)
+    return g
 
 
 class _AllGatherRows(torch.autograd.Function):

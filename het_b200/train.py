@@ -58,7 +58,8 @@ class FullGraphTrainer:
         else:
             self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
                                            compact_as_of_node_flag=compact_as_of_node,
-                                           fused_attention_aggregation_flag=bool(fused and compact_as_of_node)
+                                           fused_attention_aggregation_flag=bool(fused and compact_as_of_node),
+                                           linear_reorder_flag=bool(fused and compact_as_of_node)
                                            ).to(self.device)
         gen = torch.Generator().manual_seed(seed + 1)
         embed_full = torch.rand(coo.num_nodes, hidden, generator=gen) * 2 - 1

@@ -59,6 +59,7 @@ def test_rgat_layer_fwd_bwd(cuda, shape, scale, heads, edge_parallel, compact):
     (0.002, 4, 1, False), (0.005, 1, 1, False), (0.002, 4, 2, False),
     (0.002, 4, 1, True), (0.005, 1, 1, True), (0.002, 4, 2, True),   # compact_as_of_node_flag
     (0.002, 4, 1, 2), (0.005, 1, 1, 2), (0.002, 4, 2, 2),            # + fused score/softmax/aggregation pass
+    (0.002, 4, 1, 3), (0.005, 1, 1, 3), (0.002, 4, 2, 3),            # + linear operator reordering (W_q.W_att, W_v.W_msg)
 ])
 def test_hgt_layer_fwd_bwd(cuda, scale, heads, layers, compact):
     from het_b200.models import HET_HGT_DGLHetero
@@ -66,7 +67,8 @@ def test_hgt_layer_fwd_bwd(cuda, scale, heads, layers, compact):
     torch.manual_seed(1)
     model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, 64, 64, heads, num_layers=layers,
                               compact_as_of_node_flag=bool(compact),
-                              fused_attention_aggregation_flag=(compact == 2)).to(cuda)
+                              fused_attention_aggregation_flag=(compact in (2, 3)),
+                              linear_reorder_flag=(compact == 3)).to(cuda)
     with torch.no_grad():
         for layer in model.layers:
             layer.relation_pri.uniform_(0.5, 1.5)
