@@ -443,6 +443,26 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def _teardown(trainer, world):
+    """Multi-GPU exit. The captured step graphs hold NCCL work, so they go before the communicator;
+    a communicator teardown that still blocks (seen with graph-captured collectives) must not turn a
+    finished measurement into a hang, so a watchdog ends the process once the line is out."""
+    if world <= 1:
+        return
+    import threading
+    sys.stdout.flush()
+    dog = threading.Timer(20.0, lambda: os._exit(0))
+    dog.daemon = True
+    dog.start()
+    trainer._graphs.clear()
+    trainer._loss.clear()
+    torch.cuda.synchronize()
+    dist.destroy_process_group()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -468,7 +488,7 @@ def main():
     kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
     coo, scale = _make_graph(args)
     # whole-step CUDA-graph capture; with NCCL collectives inside only when asked for (HETB_GRAPH_MULTI=1)
-    use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "0") == "1")
+    use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "1") == "1")
     trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
                                cuda_graph=use_graph, compact_as_of_node=args.compact, fused=args.fused)
 
@@ -544,8 +564,7 @@ def main():
     e2e_value = coo.num_edges * layers / (e2e_ms_step * 1e-3)
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _teardown(trainer, world)
         return
 
     peak, peak_src = _peaks()
@@ -596,8 +615,7 @@ def main():
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                                 "ms_per_step": ms}
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    _teardown(trainer, world)
 
 
 if __name__ == "__main__":

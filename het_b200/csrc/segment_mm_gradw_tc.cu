@@ -12,8 +12,8 @@
 //
 // Layout trick: a row-major [rows][32 floats] panel whose 32-byte chunks are XOR-swizzled with
 // the row is exactly the canonical MN-major tf32 UMMA operand (SWIZZLE_128B_BASE32B) with
-// MN = feature and K = row (tc_ptx.cuh). So rows are copied as they lie in global memory (one
-// 16-byte cp.async per chunk, swizzled destination) and the tensor core contracts over the row
+// MN = feature and K = row (tc_ptx.cuh). So rows are stored as they lie in global memory (one
+// 16-byte chunk per lane, swizzled destination) and the tensor core contracts over the row
 // index — no transpose anywhere.
 //
 // Precision: split-tf32 (the tensor core has no fp32 MMA). x = hi + lo with hi = x truncated to
@@ -25,20 +25,23 @@
 //   D[64:128, 0:64] = X_lo^T G_hi   D[64:128, 64:128] = X_lo^T G_lo
 // which the flush adds into the same dW block (error vs the fp64 oracle ~1e-6 relative).
 //
-// Structure (persistent, one CTA per SM, 512 threads, warp specialised, mbarrier pipeline):
+// Structure (persistent, one CTA per SM, 416 threads, warp specialised, mbarrier pipeline):
 //   warps 0-3   flush    : at the end of a segment run, tcgen05.ld the 128 x 128 accumulator and
-//                          red.add.v4 it into dW[s] (only the live blocks for per-head weights)
+//                          red.add.v4 it into dW[s] (only the live blocks for per-head weights);
+//                          they wait with a back-off so their polling does not steal issue slots
 //   warp  4     MMA      : one lane issues tcgen05.mma.kind::tf32 (M128 N128 K8, A and B MN-major),
 //                          one per 8 rows; the accumulator stays in TMEM across the CTA's whole run
 //                          of a segment (two accumulators, so a flush overlaps the next segment).
 //                          MN-major tf32 MMAs run at about half rate and the issue queue is
 //                          shallow, so this warp does nothing else: what to issue comes from a
-//                          one-word stage descriptor the split warps leave in shared memory.
-//   warps 5-7   loaders  : each takes every 3rd stage: SR rows x (X row + G row) as 16-byte
-//                          cp.async (zero fill past the end of a piece), completion signalled
-//                          through cp.async.mbarrier.arrive; gather indices are fetched one own
-//                          stage (= 3 stages) ahead. Nothing waits on a global load.
-//   warps 8-15  split    : LDS the raw rows, write lo beside them, proxy fence, one arrival per warp
+//                          one-word stage descriptor the producers leave in shared memory.
+//   warps 5-12  producers: each warp owns SR/8 rows of every stage. Predicated 128-bit loads of the
+//                          X and G rows (gather indices loaded straight into the address register,
+//                          two register sets so the next stage's rows are in flight while this
+//                          one is stored), then raw row + exact lo remainder into the swizzled
+//                          stage, proxy fence, ONE mbarrier arrival per warp. (An earlier version
+//                          used cp.async loaders + separate split warps: LDGSTS issue cost ~64 clk
+//                          per 512 B made it slower than the register path)
 // A CTA owns a contiguous row range; its stages are cut at segment boundaries, so an accumulator
 // only ever holds rows of one segment.
 #include "common.cuh"
