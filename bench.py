@@ -331,11 +331,12 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
             "feat_c + el_c,er_c + eid,inv_row,inv_col + row_ptr ; exp + sum + ret")
         gout = torch.randn(N, H, F, device=dev)
         gf, gel, ger = torch.zeros_like(feat), torch.zeros_like(el), torch.zeros_like(er)
-        leg("rgat_edge_bwd(out-CSR, compact)",
-            lambda: K.hetb200_backward_relational_fused_gat_csr_compact(oc["col_indices"], oc["eids"], oir, oic, feat, el, er,
-                                                                        ssum, ex, ret, gout, gf, gel, ger, 0.2),
-            2 * Ur * D * 4 + 2 * (Ur + Uc) * H * 4 + E * H * 4 + N * H * 4 + 2 * N * D * 4 + 4 * E * 8,
-            "feat_c,el_c,er_c,exp,sum,ret,gout,idx ; grad_feat_c,grad_el_c,grad_er_c")
+        leg("rgat_edge_bwd(compact-row walker)",
+            lambda: K.hetb200_backward_relational_fused_gat_compact_rows(
+                u["urow_ptrs"], u["urow_dst"], u["urow_eids"], u["urow_inverse_idx_col"], feat, el, er, ssum, ex, ret,
+                gout, gf, gel, ger, 0.2),
+            2 * Ur * D * 4 + 2 * (Ur + Uc) * H * 4 + E * H * 4 + 3 * N * H * 4 + 2 * N * D * 4 + 3 * E * 8 + (Ur + 1) * 8,
+            "feat_c,el_c,er_c,exp,sum,ret,gout,gdotr,dst,eid,er_idx,urow_ptr ; grad_feat_c,grad_el_c,grad_er_c,gdotr")
         gx, gw = torch.zeros_like(x), torch.zeros_like(W)
         leg("segment_mm_bwd(unique rows: dX scatter + dW)",
             lambda: K.backward_rgnn_relational_matmul(d_row, 1, WT, x, gf, gx, gw, True),

@@ -327,8 +327,11 @@ class RelationalFusedGatCSRCompact(th.autograd.Function):
 
     @staticmethod
     def forward(ctx, incsr_row_ptr, incsr_eids, outcsr_col_indices, outcsr_eids, in_inverse_row, in_inverse_col,
-                inverse_row, inverse_col, feat_compact, el_compact, er_compact, s, exp, ret, slope):
-        # in_inverse_* are aligned with incsr_eids, inverse_* with outcsr_eids
+                inverse_row, inverse_col, feat_compact, el_compact, er_compact, s, exp, ret, slope, by_rows=False):
+        # in_inverse_* are aligned with incsr_eids, inverse_* with outcsr_eids. by_rows: the backward
+        # walks the edges grouped by compact source row instead of the out-CSR, and the four
+        # backward arguments are (urow_dst, urow_eids, urow_ptrs, urow_inverse_idx_col)
+        ctx.by_rows = by_rows
         ctx.mark_dirty(ret)
         K.hetb200_relational_fused_gat_csr_compact(
             incsr_row_ptr, incsr_eids, in_inverse_row, in_inverse_col, feat_compact, el_compact, er_compact, s,
@@ -344,10 +347,18 @@ class RelationalFusedGatCSRCompact(th.autograd.Function):
         grad_el = th.zeros_like(el, memory_format=th.contiguous_format)
         grad_er = th.zeros_like(er, memory_format=th.contiguous_format)
         grad_feat = th.zeros_like(feat, memory_format=th.contiguous_format)
-        K.hetb200_backward_relational_fused_gat_csr_compact(
-            outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat, el, er, s, exp, ret,
-            gradout.contiguous(), grad_feat, grad_el, grad_er, ctx.slope)
-        return (None,) * 8 + (grad_feat, grad_el, grad_er, None, None, None, None)
+        if ctx.by_rows:
+            K.hetb200_backward_relational_fused_gat_compact_rows(
+                inverse_row, outcsr_col_indices, outcsr_eids, inverse_col, feat, el, er, s, exp, ret,
+                gradout.contiguous(), grad_feat, grad_el, grad_er, ctx.slope)
+        else:
+            K.hetb200_backward_relational_fused_gat_csr_compact(
+                outcsr_col_indices, outcsr_eids, inverse_row, inverse_col, feat, el, er, s, exp, ret,
+                gradout.contiguous(), grad_feat, grad_el, grad_er, ctx.slope)
+        return (None,) * 8 + (grad_feat, grad_el, grad_er, None, None, None, None, None)
+
+
+RGAT_COMPACT_BACKWARD_BY_ROWS = True  # False: edge-parallel out-CSR backward with one reduction per edge
 
 
 def relational_fused_gat_csr_compact(graph, feat_compact, el_compact, er_compact, slope):
@@ -357,10 +368,15 @@ def relational_fused_gat_csr_compact(graph, feat_compact, el_compact, er_compact
     exp = el_compact.new_empty([graph.get_num_edges(), h, 1])
     s = el_compact.new_empty([graph.get_num_nodes(), h])
     ret = el_compact.new_empty([graph.get_num_nodes()] + list(feat_compact.size()[1:]))
+    if RGAT_COMPACT_BACKWARD_BY_ROWS:
+        bwd = (uniq["urow_dst"], uniq["urow_eids"], uniq["urow_ptrs"], uniq["urow_inverse_idx_col"])
+    else:
+        bwd = (outcsr["col_indices"], outcsr["eids"], uniq["outcsr_inverse_idx_row"], uniq["outcsr_inverse_idx_col"])
     return RelationalFusedGatCSRCompact.apply(
-        incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["incsr_inverse_idx_row"],
-        uniq["incsr_inverse_idx_col"], uniq["outcsr_inverse_idx_row"], uniq["outcsr_inverse_idx_col"],
-        feat_compact.contiguous(), el_compact.contiguous(), er_compact.contiguous(), s, exp, ret, slope)
+        incsr["row_ptrs"], incsr["eids"], bwd[0], bwd[1], uniq["incsr_inverse_idx_row"],
+        uniq["incsr_inverse_idx_col"], bwd[2], bwd[3],
+        feat_compact.contiguous(), el_compact.contiguous(), er_compact.contiguous(), s, exp, ret, slope,
+        RGAT_COMPACT_BACKWARD_BY_ROWS)
 
 
 class HGTFullGraphEdgeSoftmaxAndMessageMeanAggregationOpsCSRCompact(th.autograd.Function):

@@ -343,6 +343,27 @@ void hetb200_backward_relational_fused_gat_csr_compact(
            op);
 }
 
+// The same backward walking the edges grouped by compact (relation, source) row
+// (HetGraph: urow_ptrs / urow_dst / urow_eids / urow_inverse_idx_col).
+void hetb200_backward_relational_fused_gat_compact_rows(
+    Tensor &urow_ptrs, Tensor &urow_dst, Tensor &urow_eids, Tensor &urow_inverse_col,
+    Tensor &feat_src, Tensor &el, Tensor &er, Tensor &sum, Tensor &exp, Tensor &ret, Tensor &gradout,
+    Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope) {
+  const char *op = "hetb200_backward_relational_fused_gat_compact_rows";
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(feat_src) / H);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  Tensor scratch = at::empty({sum.numel()}, sum.options());
+  check_rc(hetb_rgat_bwd_compact_rows(
+               i64(urow_ptrs, op, "urow_ptrs"), i64(urow_dst, op, "urow_dst"), i64(urow_eids, op, "urow_eids"),
+               i64(urow_inverse_col, op, "urow_inverse_col"), urow_ptrs.numel() - 1, urow_eids.numel(),
+               sum.numel() / H, f32(feat_src, op, "feat_src"), f32(el, op, "el"), f32(er, op, "er"),
+               f32(sum, op, "sum"), f32(exp, op, "exp"), f32(ret, op, "ret"), f32(gradout, op, "gradout"),
+               f32w(scratch, op, "scratch"), f32w(grad_feat_src, op, "grad_feat_src"), f32w(grad_el, op, "grad_el"),
+               f32w(grad_er, op, "grad_er"), H, F, (float)slope, stream_of(gradout)),
+           op);
+}
+
 // OpExport/RGATOps.inc.h:430-461
 void backward_relational_fused_gat_csr(
     Tensor &outcsr_row_ptr, Tensor &outcsr_col_indices, Tensor &outcsr_eids,
@@ -863,6 +884,7 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);
   m.def("hetb200_backward_relational_fused_gat_csr_compact", hetb200_backward_relational_fused_gat_csr_compact);
+  m.def("hetb200_backward_relational_fused_gat_compact_rows", hetb200_backward_relational_fused_gat_compact_rows);
   m.def("hetb200_hgt_message_aggregation_csr_compact", hetb200_hgt_message_aggregation_csr_compact);
   m.def("hetb200_backward_hgt_message_aggregation_csr_compact",
         hetb200_backward_hgt_message_aggregation_csr_compact);

@@ -131,6 +131,17 @@ class HetGraph:
                 # dependent load level less than inverse_idx[eids[p]]
                 out["incsr_inverse_idx_" + side] = inverse[self.in_csr["eids"]].contiguous()
                 out["outcsr_inverse_idx_" + side] = inverse[self.out_csr["eids"]].contiguous()
+            # the edges grouped by compact source row (a CSR over the (relation, source) rows): the
+            # RGAT compact backward walks this order so a compact row's gradient is a register sum
+            inv_row = out["inverse_idx_row"]
+            order = torch.argsort(inv_row, stable=True)
+            counts = torch.bincount(inv_row, minlength=int(out["node_indices_row"].numel()))
+            ptrs = torch.zeros(counts.numel() + 1, dtype=torch.int64, device=inv_row.device)
+            torch.cumsum(counts, 0, out=ptrs[1:])
+            out["urow_ptrs"] = ptrs
+            out["urow_eids"] = coo["eids"][order].contiguous()
+            out["urow_dst"] = coo["col_indices"][order].contiguous()
+            out["urow_inverse_idx_col"] = out["inverse_idx_col"][order].contiguous()
             self._unique_single_sided = out
         return self._unique_single_sided
 

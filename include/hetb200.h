@@ -175,6 +175,22 @@ int hetb_rgat_bwd(const int64_t *dst_idx, const int64_t *eids,
                   const hetb_compact_idx *cidx /* NULL: per-edge tensors */,
                   void *stream);
 
+/* The same backward for compact feat / el (one row per unique (relation, source) pair) and compact
+ * er (one per unique (relation, destination) pair), walking the edges GROUPED BY COMPACT SOURCE
+ * ROW: urow_ptr[num_urows+1] is a CSR over the compact source rows, and per position p of row u:
+ * u_dst[p] the destination, u_eids[p] the edge id, u_eridx[p] the compact er row. grad_feat[u]
+ * and grad_el[u] are accumulated in registers and stored once per row (the reference's compact
+ * backward, RGATBackwardKernels.cu.h:14-250, adds every edge's product atomically).
+ * gdotr_scratch: num_dst*H floats of workspace. grad_* must arrive zero-filled. */
+int hetb_rgat_bwd_compact_rows(const int64_t *urow_ptr, const int64_t *u_dst,
+                               const int64_t *u_eids, const int64_t *u_eridx,
+                               int64_t num_urows, int64_t num_edges, int64_t num_dst,
+                               const float *feat, const float *el, const float *er,
+                               const float *sum, const float *exp_in, const float *ret,
+                               const float *gout, float *gdotr_scratch, float *grad_feat,
+                               float *grad_el, float *grad_er, int H, int F, float slope,
+                               void *stream);
+
 /* ------------------------------------------------------------------------
  * HGT edge attention pipeline
  * ---------------------------------------------------------------------- */
