@@ -336,7 +336,9 @@ __global__ void __launch_bounds__(kThreads)
 //   grad_kv[s,h,:]      += ga · left[L(e),h,:]
 // Walking by source makes kv[s] a row constant (loaded once per row) and grad_kv[s] a register
 // accumulator stored once per row, gout[d] is read once instead of twice, and the per-edge score
-// gradient never exists in memory. grad_msg / grad_left / grad_kv must arrive zero-filled.
+// gradient never exists in memory. The out[d] row is not gathered per edge either:
+// Σ_f gout·(msg − out) = gout·msg − <gout[d,h,:], out[d,h,:]>, the second term from a
+// per-destination pre-pass (rowdot_heads_kernel), one scalar per (destination, head). grad_msg / grad_left / grad_kv must arrive zero-filled.
 // ---------------------------------------------------------------------------
 template <int LPR>
 __global__ void __launch_bounds__(kThreads)
@@ -347,7 +349,8 @@ __global__ void __launch_bounds__(kThreads)
                          const float *__restrict__ msg, const int64_t *__restrict__ msg_idx,
                          const float *__restrict__ mu, const float *__restrict__ attn,
                          const float *__restrict__ t, const float *__restrict__ sum,
-                         const float *__restrict__ out, const float *__restrict__ gout,
+                         const float *__restrict__ gdoto,  // [num_dst, H] = <gout[d,h,:], out[d,h,:]> (pre-pass)
+                         const float *__restrict__ gout,
                          float *__restrict__ grad_left, float *__restrict__ grad_kv, float *__restrict__ grad_msg,
                          float *__restrict__ grad_mu, int H, int hw, int use_smem) {
   constexpr int GROUPS = kThreads / LPR;
@@ -383,8 +386,8 @@ __global__ void __launch_bounds__(kThreads)
 
   for (int64_t q = 0; q < kChunk; q += 2) {
     int64_t e[2], dn[2], li[2], mi[2];
-    float tt[2], aa[2], sd[2], mm[2];
-    float4 go[2], ov[2], mv[2], lv[2];
+    float tt[2], aa[2], sd[2], mm[2], cc[2];
+    float4 go[2], mv[2], lv[2];
     bool ok[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -401,11 +404,11 @@ __global__ void __launch_bounds__(kThreads)
       tt[j] = __ldg(t + e[j] * H + h);
       aa[j] = __ldg(attn + e[j] * H + h);
       sd[j] = __ldg(sum + dn[j] * H + h);
+      cc[j] = __ldg(gdoto + dn[j] * H + h);
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       go[j] = ldg4(gout + dn[j] * D + 4 * l);
-      ov[j] = ldg4(out + dn[j] * D + 4 * l);
       mv[j] = ldg4(msg + mi[j] * D + 4 * l);
       lv[j] = ldg4(left + li[j] * D + 4 * l);
     }
@@ -421,9 +424,8 @@ __global__ void __launch_bounds__(kThreads)
         right = ldg4(kv + srow * D + 4 * l);
         acc = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      const float dotv = go[j].x * (mv[j].x - ov[j].x) + go[j].y * (mv[j].y - ov[j].y) +
-                         go[j].z * (mv[j].z - ov[j].z) + go[j].w * (mv[j].w - ov[j].w);
-      const float sdot = group_sum(dotv, hw);
+      const float dotv = go[j].x * mv[j].x + go[j].y * mv[j].y + go[j].z * mv[j].z + go[j].w * mv[j].w;
+      const float sdot = group_sum(dotv, hw) - cc[j];
       if (ok[j]) {
         const float nrm = sd[j] != 0.f ? tt[j] / sd[j] : 0.f;
         const float sg = sdot * nrm;
@@ -1127,23 +1129,27 @@ extern "C" int hetb_hgt_fused_bwd_csr(const int64_t *row_ptr, const int64_t *dst
                                       const float *left, const int64_t *left_idx, const float *kv,
                                       const float *msg, const int64_t *msg_idx, const float *mu,
                                       const float *attn, const float *t, const float *sum, const float *out,
-                                      const float *gout, float *grad_left, float *grad_kv, float *grad_msg,
+                                      const float *gout, int64_t num_dst, float *gdoto_scratch,
+                                      float *grad_left, float *grad_kv, float *grad_msg,
                                       float *grad_mu, int H, int F, void *stream) {
-  HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0 && num_rels >= 0);
+  HETB_CHECK_ARG(num_rows >= 0 && num_edges >= 0 && num_rels >= 0 && num_dst >= 0);
   if (num_rows == 0 || num_edges == 0) return HETB_OK;
   HETB_CHECK_ARG(row_ptr && dst && eids && rel && left && kv && msg && mu && attn && t && sum && out && gout &&
-                 grad_left && grad_kv && grad_msg && grad_mu);
+                 gdoto_scratch && num_dst > 0 && grad_left && grad_kv && grad_msg && grad_mu);
   const int lpr = lanes_per_row(H, F);
   if (!lpr) return HETB_EUNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   const int groups = kThreads / lpr;
   const int use_smem = (num_rels * H <= kMaxSmemMu) ? 1 : 0;
   const size_t smem = use_smem ? (size_t)num_rels * H * sizeof(float) : 0;
+  DISPATCH_LPR(lpr, (rowdot_heads_kernel<L><<<(unsigned)ceil_div64(num_dst, groups), kThreads, 0, st>>>(
+                        gout, out, num_dst, gdoto_scratch, H, F / 4)));
+  HETB_LAUNCH_OK();
   const int64_t grid = ceil_div64(ceil_div64(num_edges, kChunk), groups);
   DISPATCH_LPR(lpr, (hgt_fused_bwd_kernel<L><<<(unsigned)grid, kThreads, smem, st>>>(
                         row_ptr, dst, eids, rel, num_rows, num_edges, (int)num_rels, left, left_idx, kv, msg,
-                        msg_idx, mu, attn, t, sum, out, gout, grad_left, grad_kv, grad_msg, grad_mu, H, F / 4,
-                        use_smem)));
+                        msg_idx, mu, attn, t, sum, gdoto_scratch, gout, grad_left, grad_kv, grad_msg, grad_mu, H,
+                        F / 4, use_smem)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -641,14 +641,15 @@ void hetb200_backward_hgt_fused_attention_aggregation_csr(
   const int H = (int)mu.size(1);
   const int F = (int)(xlen(messages_compact) / H);
   c10::cuda::CUDAGuard guard(gradout.device());
+  Tensor scratch = at::empty({sum.numel()}, sum.options());
   check_rc(hetb_hgt_fused_bwd_csr(
                i64(outcsr_row_ptrs, op, "outcsr_row_ptrs"), i64(outcsr_col_indices, op, "outcsr_col_indices"),
                i64(outcsr_eids, op, "outcsr_eids"), i64(outcsr_reltypes, op, "outcsr_reltypes"),
                outcsr_row_ptrs.numel() - 1, outcsr_eids.numel(), mu.size(0), f32(left_compact, op, "left_compact"),
                i64(left_idx, op, "left_idx"), f32(k, op, "k"), f32(messages_compact, op, "messages_compact"),
                i64(msg_idx, op, "msg_idx"), f32(mu, op, "mu"), f32(attn, op, "attn"), f32(t, op, "t"),
-               f32(sum, op, "sum"), f32(out, op, "out"), f32(gradout, op, "gradout"),
-               f32w(grad_left, op, "grad_left"), f32w(grad_k, op, "grad_k"),
+               f32(sum, op, "sum"), f32(out, op, "out"), f32(gradout, op, "gradout"), sum.numel() / H,
+               f32w(scratch, op, "scratch"), f32w(grad_left, op, "grad_left"), f32w(grad_k, op, "grad_k"),
                f32w(grad_message_compact, op, "grad_message_compact"), f32w(grad_mu, op, "grad_mu"), H, F,
                stream_of(gradout)),
            op);

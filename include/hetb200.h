@@ -263,13 +263,16 @@ int hetb_hgt_fused_fwd_csr(const int64_t *row_ptr, const int64_t *eids, const in
  * hetb_hgt_aggregate_bwd + hetb_hgt_edge_softmax_bwd + hetb_inner_product_bwd: with
  * norm = t[e,h]/sum[d,h], sg = Σ_f gout[d,h,f]·(msg[M(e),h,f] − out[d,h,f])·norm, ga = sg·mu[r,h]:
  *   grad_msg[M(e)] += norm·gout[d];  grad_left[L(e)] += ga·kv[s];  grad_kv[s] += ga·left[L(e)];
- *   grad_mu[r,h] += sg·attn[e,h].   grad_* must arrive zero-filled. */
+ *   grad_mu[r,h] += sg·attn[e,h].   grad_* must arrive zero-filled.
+ * gdoto_scratch: num_dst*H floats of workspace (<gout[d,h,:], out[d,h,:]> per destination, so the
+ * edge pass gathers one destination row instead of two). */
 int hetb_hgt_fused_bwd_csr(const int64_t *row_ptr, const int64_t *dst, const int64_t *eids,
                            const int64_t *rel, int64_t num_rows, int64_t num_edges, int64_t num_rels,
                            const float *left, const int64_t *left_idx, const float *kv,
                            const float *msg, const int64_t *msg_idx, const float *mu,
                            const float *attn, const float *t, const float *sum, const float *out,
-                           const float *gout, float *grad_left, float *grad_kv, float *grad_msg,
+                           const float *gout, int64_t num_dst, float *gdoto_scratch,
+                           float *grad_left, float *grad_kv, float *grad_msg,
                            float *grad_mu, int H, int F, void *stream);
 
 /* ------------------------------------------------------------------------
