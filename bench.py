@@ -37,6 +37,7 @@ if ROOT not in sys.path:
 
 WORKLOADS = {
     # name: (model, graph shape, heads, layers, BASELINE.json config it corresponds to)
+    "rgcn_aifb": ("rgcn", "aifb", 1, 2, "configs[0], with backward + Adam"),
     "rgat_aifb": ("rgat", "aifb", 1, 1, "configs[0] graph, RGAT"),
     "rgat_bgs": ("rgat", "bgs", 1, 1, "configs[1]"),
     "hgt_mag": ("hgt", "mag", 4, 2, "configs[2]"),
@@ -135,7 +136,18 @@ def cpu_dgl_baseline(wl, coo, steps, warmup, budget_s):
     def P(*shape):
         return torch.nn.Parameter(torch.randn(*shape, generator=g) * 0.1)
 
-    if kind == "rgat":
+    if kind == "rgcn":
+        ps = [dict(w=P(R, D, D), b=P(D)) for _ in range(layers)]
+        norm = 1.0 / torch.bincount(dst, minlength=n).clamp(min=1).to(torch.float32)[dst]
+
+        def fwd():
+            h = x
+            for i, p in enumerate(ps):
+                h = M.dgl_rgcn_layer(src, dst, et, h, p["w"], norm) + p["b"]
+                if i + 1 < len(ps):
+                    h = torch.relu(h)
+            return h
+    elif kind == "rgat":
         ps = [dict(fc=P(R, D, D), al=P(R, heads, F), ar=P(R, heads, F)) for _ in range(layers)]
 
         def fwd():
@@ -296,7 +308,7 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
     u = g.get_separate_unique_node_indices_single_sided()
     Ur, Uc = int(u["node_indices_row"].numel()), int(u["node_indices_col"].numel())
     layer = trainer.model.layers[0]
-    H, D = layer.num_heads, 64
+    H, D = getattr(layer, "num_heads", 1), 64
     F = D // H
     flush = torch.zeros(64 * 1024 * 1024, device=dev)
     uniq_src = int(torch.unique(coo["row_indices"]).numel())
@@ -316,6 +328,27 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
     ir, icx = u["inverse_idx_row"], u["inverse_idx_col"]                      # by edge id (COO ops)
     iir, iic = u["incsr_inverse_idx_row"], u["incsr_inverse_idx_col"]        # aligned with the in-CSR
     oir, oic = u["outcsr_inverse_idx_row"], u["outcsr_inverse_idx_col"]      # aligned with the out-CSR
+    if trainer.kind == "rgcn":
+        W = layer.weight.detach().unsqueeze(1).contiguous()
+        WT = W.transpose(2, 3).contiguous()
+        feat = torch.empty(Ur, 1, D, device=dev)
+        leg("segment_mm_fwd(unique (rel,src) rows, X.W_r)", lambda: K.rgnn_relational_matmul(d_row, 1, W, x, feat, True),
+            uniq_src * D * 4 + Ur * D * 4 + R * D * D * 4 + Ur * 8, "X_unique*D*s + U*D*s + R*D*D*s + U*i")
+        ret = torch.empty(N, D, device=dev)
+        norm = trainer.edge_norm
+        leg("rgcn_aggregate_fwd(in-CSR, compact)",
+            lambda: K.hetb200_rgcn_node_aggregation_csr_compact(ic["row_ptrs"], ic["eids"], iir, feat, norm, ret),
+            Ur * D * 4 + E * 4 + 2 * E * 8 + (N + 1) * 8 + N * D * 4, "feat_c + norm + eid,inv_row + row_ptr ; ret")
+        gout = torch.randn(N, D, device=dev)
+        gf = torch.zeros_like(feat)
+        leg("rgcn_aggregate_bwd(out-CSR, compact)",
+            lambda: K.hetb200_backward_hgt_message_aggregation_csr_compact(oc["col_indices"], oc["eids"], oir, norm, gout, gf),
+            N * D * 4 + E * 4 + 3 * E * 8 + Ur * D * 4, "gout + norm + dst,eid,inv_row ; grad_feat_c")
+        gx, gw = torch.zeros_like(x), torch.zeros_like(W)
+        leg("segment_mm_bwd(unique rows: dX scatter + dW)",
+            lambda: K.backward_rgnn_relational_matmul(d_row, 1, WT, x, gf, gx, gw, True),
+            Ur * D * 4 + 2 * uniq_src * D * 4 + 2 * R * D * D * 4 + Ur * 8, "dY_c + X_unique + W ; dX_unique + dW ; list")
+        return out
     if trainer.kind == "rgat":
         W = layer.conv_weights.detach().contiguous()
         WT = W.transpose(2, 3).contiguous()
@@ -593,7 +626,7 @@ def main():
         "clocks": clocks, "loss": final_loss, "eager_first_loss": eager_loss,
     }
     if not args.no_roofline:
-        legs = (kernel_rooflines_compact if args.compact else kernel_rooflines)(trainer, peak, peak_src)
+        legs = (kernel_rooflines_compact if (args.compact or kind == "rgcn") else kernel_rooflines)(trainer, peak, peak_src)
         # measured DRAM traffic per launch (one ncu --set full capture, profiles/ncu_traffic.json), only for
         # the configuration it was captured on; "dram_frac" = that traffic / this run's kernel time / peak
         try:
@@ -610,7 +643,7 @@ def main():
                                                      "kernel", "ms", "algorithmic_bytes", "peak_source")}
         line["kernels"] = legs
     if world == 1 and not args.no_cpu_baseline:
-        del trainer
+        trainer = None
         torch.cuda.empty_cache()
         v, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, 3, 1, budget_s=25.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,

@@ -502,3 +502,104 @@ class SoftmaxCrossEntropy(th.autograd.Function):
 
 def softmax_cross_entropy(logits, labels, denom):
     return SoftmaxCrossEntropy.apply(logits, labels, denom)
+
+
+# ----- rgcn_layers_and_funcs.py:481-601 (RGCN) --------------------------------
+class RgcnLayer1SeparateCoo(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, separate_coo_rel_ptrs, separate_coo_eids, separate_coo_row_indices,
+                separate_coo_col_indices, x, weight, norm, ret):
+        ctx.save_for_backward(separate_coo_rel_ptrs, separate_coo_eids, separate_coo_row_indices,
+                              separate_coo_col_indices, weight, norm, x)
+        ctx.mark_dirty(ret)
+        K.rgcn_layer1_separate_coo(separate_coo_rel_ptrs, separate_coo_eids, separate_coo_row_indices,
+                                   separate_coo_col_indices, x, weight, norm, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        rel_ptrs, eids, row_indices, col_indices, weight, norm, x = ctx.saved_tensors
+        grad_x = th.zeros_like(x, memory_format=th.contiguous_format)
+        grad_weight = th.zeros_like(weight, memory_format=th.contiguous_format)
+        grad_norm = th.zeros_like(norm, memory_format=th.contiguous_format)
+        K.backward_rgcn_layer1_separate_coo(
+            rel_ptrs, eids, row_indices, col_indices, x, th.transpose(weight, 1, 2).contiguous(), norm,
+            grad_norm, grad_x, gradout.contiguous(), grad_weight)
+        return None, None, None, None, grad_x, grad_weight, grad_norm, None
+
+
+def rgcn_layer1_separate_coo(graph, x, weight, norm):
+    """rgcn_layers_and_funcs.py:570-601: out[dst] = sum_e norm[e] * x[src] @ weight[rel(e)]."""
+    coo = graph.get_separate_coo_original()
+    ret = th.empty((graph.get_num_nodes(), weight.size(2)), dtype=weight.dtype, device=weight.device)
+    return RgcnLayer1SeparateCoo.apply(coo["rel_ptrs"], coo["eids"], coo["row_indices"], coo["col_indices"],
+                                       x.contiguous(), weight.contiguous(), norm.contiguous(), ret)
+
+
+# ----- rgcn_layers_and_funcs.py:684-755 (compact sources, direct indexing) -------------------
+class RGCNNodeMeanAggregationCompactAsOfNodeDirectIndexingSeparateCOO(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, separate_coo_eids, separate_coo_rel_ptrs, separate_coo_row_indices,
+                separate_coo_col_indices, inverse_indices_row, feat_src, enorm, ret):
+        ctx.save_for_backward(separate_coo_eids, separate_coo_rel_ptrs, separate_coo_row_indices,
+                              separate_coo_col_indices, inverse_indices_row, feat_src, enorm, ret)
+        ctx.mark_dirty(ret)
+        K.rgcn_node_mean_aggregation_compact_as_of_node_separate_coo(
+            separate_coo_eids, separate_coo_rel_ptrs, separate_coo_row_indices, separate_coo_col_indices,
+            {"inverse_indices_row": inverse_indices_row}, feat_src, enorm, ret, True)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        eids, rel_ptrs, row_indices, col_indices, inverse_indices_row, feat_src, enorm, ret = ctx.saved_tensors
+        grad_feat_src = th.zeros_like(feat_src, memory_format=th.contiguous_format)
+        K.backward_rgcn_node_mean_aggregation_compact_as_of_node_separate_coo(
+            eids, rel_ptrs, row_indices, col_indices, {"inverse_indices_row": inverse_indices_row}, feat_src,
+            enorm, ret, gradout.contiguous(), grad_feat_src, True)
+        return None, None, None, None, None, grad_feat_src, None, None
+
+
+def rgcn_node_mean_aggregation_compact_as_of_node_separate_coo_single_sided(
+        g, feat_compact_src, enorm, compact_direct_indexing_flag):
+    """rgcn_layers_and_funcs.py:782-830. Only direct indexing is built (the binary-search kind
+    raises, like the other compact ops)."""
+    if not compact_direct_indexing_flag:
+        raise NotImplementedError("compact_as_of_node without direct indexing (binary search)")
+    coo = g.get_separate_coo_original()
+    uniq = g.get_separate_unique_node_indices_single_sided()
+    ret = th.empty([g.get_num_nodes()] + list(feat_compact_src.size()[1:]), dtype=feat_compact_src.dtype,
+                   device=feat_compact_src.device)
+    return RGCNNodeMeanAggregationCompactAsOfNodeDirectIndexingSeparateCOO.apply(
+        coo["eids"], coo["rel_ptrs"], coo["row_indices"], coo["col_indices"], uniq["inverse_idx_row"],
+        feat_compact_src.contiguous(), enorm.contiguous(), ret)
+
+
+class RgcnNodeAggregationCSRCompact(th.autograd.Function):
+    """hetb200 extension: the same aggregation over the in-CSR with the edge-balanced walker (no
+    atomics in the forward); backward over the out-CSR into the compact rows."""
+
+    @staticmethod
+    def forward(ctx, incsr_row_ptrs, incsr_eids, outcsr_col_indices, outcsr_eids, in_msg_idx, msg_idx,
+                feat_compact, enorm, ret):
+        ctx.mark_dirty(ret)
+        K.hetb200_rgcn_node_aggregation_csr_compact(incsr_row_ptrs, incsr_eids, in_msg_idx, feat_compact, enorm, ret)
+        ctx.save_for_backward(outcsr_col_indices, outcsr_eids, msg_idx, feat_compact, enorm)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        outcsr_col_indices, outcsr_eids, msg_idx, feat_compact, enorm = ctx.saved_tensors
+        grad_feat = th.zeros_like(feat_compact, memory_format=th.contiguous_format)
+        K.hetb200_backward_hgt_message_aggregation_csr_compact(
+            outcsr_col_indices, outcsr_eids, msg_idx, enorm, gradout.contiguous(), grad_feat)
+        return (None,) * 6 + (grad_feat, None, None)
+
+
+def rgcn_node_aggregation_csr_compact(g, feat_compact_src, enorm):
+    incsr, outcsr = g.get_in_csr(), g.get_out_csr()
+    uniq = g.get_separate_unique_node_indices_single_sided()
+    ret = th.empty([g.get_num_nodes()] + list(feat_compact_src.size()[1:]), dtype=feat_compact_src.dtype,
+                   device=feat_compact_src.device)
+    return RgcnNodeAggregationCSRCompact.apply(
+        incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["incsr_inverse_idx_row"],
+        uniq["outcsr_inverse_idx_row"], feat_compact_src.contiguous(), enorm.contiguous(), ret)

@@ -853,6 +853,32 @@ __global__ void __launch_bounds__(kThreads)
   if (live) flush();
 }
 
+// ---------------------------------------------------------------------------
+// RGCN edge-parallel aggregation over the separate COO (the layout the reference's RGCN ops take):
+//   ret[dst[i], :] += norm[e] · feat[F(e), :],  e = eids[i],  F(e) = feat_idx ? feat_idx[e] : e
+// (per-edge X[src]·W_r rows, or compact rows by direct indexing). ret arrives zero-filled by the
+// host entry. The in-CSR walker (hetb_hgt_aggregate_fwd_csr without the divide) is the fast path
+// when the CSR is at hand; this one serves the COO op signatures.
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kThreads)
+    rgcn_scatter_kernel(const int64_t *__restrict__ eids, const int64_t *__restrict__ dst,
+                        const int64_t *__restrict__ feat_idx, int64_t E, const float *__restrict__ feat,
+                        const float *__restrict__ norm, float *__restrict__ ret) {
+  constexpr int GROUPS = kThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int64_t stride = (int64_t)gridDim.x * GROUPS;
+  for (int64_t i = (int64_t)blockIdx.x * GROUPS + g; i < E; i += stride) {
+    const int64_t e = __ldg(eids + i);
+    const int64_t d = __ldg(dst + i);
+    const int64_t fr = feat_idx ? __ldg(feat_idx + e) : e;
+    const float w = __ldg(norm + e);
+    const float4 v = feat_idx ? ldg4(feat + fr * D + 4 * l) : ldcs4(feat + fr * D + 4 * l);
+    red_add4(ret + d * D + 4 * l, make_float4(w * v.x, w * v.y, w * v.z, w * v.w));
+  }
+}
+
 template <int LPR>
 __global__ void __launch_bounds__(kThreads)
     hgt_aggregate_bwd_kernel(const int64_t *__restrict__ dst_idx,
@@ -1281,6 +1307,32 @@ extern "C" int hetb_rgat_bwd_compact_rows(const int64_t *urow_ptr, const int64_t
   DISPATCH_LPR(lpr, (rgat_bwd_urow_kernel<L><<<(unsigned)grid, kThreads, 0, st>>>(
                         urow_ptr, u_dst, u_eids, u_eridx, num_urows, num_edges, feat, el, er, sum,
                         exp_in, gdotr_scratch, gout, grad_feat, grad_el, grad_er, H, F / 4, slope)));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+extern "C" int hetb_rgcn_aggregate_coo(const int64_t *eids, const int64_t *dst_idx,
+                                       const int64_t *feat_idx, int64_t num_edges, int64_t num_dst,
+                                       const float *feat, const float *norm, float *ret, int F,
+                                       void *stream) {
+  HETB_CHECK_ARG(num_edges >= 0 && num_dst >= 0);
+  if (num_dst == 0) return HETB_OK;
+  HETB_CHECK_ARG(ret != nullptr);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int lpr = lanes_per_row(1, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  {
+    const int64_t n = num_dst * F;
+    const int64_t need = ceil_div64(n, kThreads);
+    const int zg = (int)(need < kNumSMs * 16 ? need : kNumSMs * 16);
+    zero_f32_kernel<<<zg, kThreads, 0, st>>>(ret, n);
+    HETB_LAUNCH_OK();
+  }
+  if (num_edges == 0) return HETB_OK;
+  HETB_CHECK_ARG(eids && dst_idx && feat && norm);
+  const int grid = edge_grid(num_edges, kThreads / lpr);
+  DISPATCH_LPR(lpr, (rgcn_scatter_kernel<L><<<grid, kThreads, 0, st>>>(eids, dst_idx, feat_idx, num_edges,
+                                                                       feat, norm, ret)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -505,6 +505,127 @@ void hetb200_hgt_message_aggregation_csr_compact(
            op);
 }
 
+// ---------------------------------------------------------------------------
+// RGCN. OpExport/RGCNOps.inc.h:84-138: one fused SGEMM with an atomic, norm-scaled
+// scatter in the reference; here the typed linear (tcgen05 segment MM, per-edge rows) followed by
+// the edge-parallel aggregation. weights [R, in, out], edge_norm [E, 1], node_feat_output [N, out].
+// ---------------------------------------------------------------------------
+void rgcn_layer1_separate_coo(Tensor &separate_coo_relptrs, Tensor &separate_coo_eids,
+                              Tensor &separate_coo_row_indices, Tensor &separate_coo_col_indices,
+                              Tensor &node_feat_input, Tensor &weights, Tensor &edge_norm,
+                              Tensor &node_feat_output) {
+  const char *op = "rgcn_layer1_separate_coo";
+  TORCH_CHECK(weights.dim() == 3, op, ": weights must be [R,in,out]");
+  const int K = (int)weights.size(1), N = (int)weights.size(2);
+  const int64_t E = separate_coo_eids.numel();
+  c10::cuda::CUDAGuard guard(node_feat_output.device());
+  void *st = stream_of(node_feat_output);
+  Tensor per_edge = at::empty({E, N}, node_feat_output.options());
+  const int64_t *eids = i64(separate_coo_eids, op, "separate_coo_eids");
+  const int64_t *rel_ptrs = i64(separate_coo_relptrs, op, "separate_coo_relptrs");
+  check_rc(hetb_segment_mm(f32(node_feat_input, op, "node_feat_input"),
+                           i64(separate_coo_row_indices, op, "separate_coo_row_indices"), 1,
+                           f32(weights, op, "weights"), f32w(per_edge, op, "per_edge"), eids, 1, rel_ptrs,
+                           separate_coo_relptrs.numel() - 1, E, 1, K, N, 0, st),
+           op);
+  check_rc(hetb_rgcn_aggregate_coo(eids, i64(separate_coo_col_indices, op, "separate_coo_col_indices"), nullptr,
+                                   E, node_feat_output.size(0), f32(per_edge, op, "per_edge"),
+                                   f32(edge_norm, op, "edge_norm"), f32w(node_feat_output, op, "node_feat_output"),
+                                   N, st),
+           op);
+}
+
+// OpExport/RGCNOps.inc.h:368-470. weights_transposed [R, out, in]; grad_* arrive zero-filled.
+//   G[e] = norm[e] * gout[dst];  grad_x[src] += G[e] W_r^T;  grad_W[r] += x[src]^T G[e];
+//   grad_norm[e] = <x[src], gout[dst] W_r^T>
+void backward_rgcn_layer1_separate_coo(Tensor &separate_coo_relptrs, Tensor &separate_coo_eids,
+                                       Tensor &separate_coo_row_indices, Tensor &separate_coo_col_indices,
+                                       Tensor &node_feat_input, Tensor &weights_transposed, Tensor &edge_norm,
+                                       Tensor &grad_edge_norm, Tensor &delta_node_feat_input,
+                                       Tensor &delta_node_feat_output, Tensor &delta_weights) {
+  const char *op = "backward_rgcn_layer1_separate_coo";
+  TORCH_CHECK(weights_transposed.dim() == 3, op, ": weights_transposed must be [R,out,in]");
+  const int N = (int)weights_transposed.size(1), K = (int)weights_transposed.size(2);  // forward: K in, N out
+  const int64_t E = separate_coo_eids.numel();
+  const int64_t R = separate_coo_relptrs.numel() - 1;
+  c10::cuda::CUDAGuard guard(delta_node_feat_output.device());
+  void *st = stream_of(delta_node_feat_output);
+  const int64_t *eids = i64(separate_coo_eids, op, "separate_coo_eids");
+  const int64_t *rel_ptrs = i64(separate_coo_relptrs, op, "separate_coo_relptrs");
+  const int64_t *row = i64(separate_coo_row_indices, op, "separate_coo_row_indices");
+  const int64_t *col = i64(separate_coo_col_indices, op, "separate_coo_col_indices");
+  const float *x = f32(node_feat_input, op, "node_feat_input");
+  const float *wt = f32(weights_transposed, op, "weights_transposed");
+  const float *gout = f32(delta_node_feat_output, op, "delta_node_feat_output");
+  Tensor scaled = at::empty({E, N}, delta_node_feat_output.options());  // G
+  check_rc(hetb_hgt_aggregate_bwd(col, eids, E, f32(edge_norm, op, "edge_norm"), gout, f32w(scaled, op, "scaled"), 1,
+                                  N, nullptr, nullptr, st),
+           op);
+  check_rc(hetb_segment_mm(f32(scaled, op, "scaled"), eids, 1, wt, f32w(delta_node_feat_input, op, "grad_x"), row, 1,
+                           rel_ptrs, R, E, 1, N, K, 1, st),
+           op);
+  check_rc(hetb_segment_mm_grad_w(x, row, 1, f32(scaled, op, "scaled"), eids, 1, f32w(delta_weights, op, "grad_w"),
+                                  rel_ptrs, R, E, 1, K, N, st),
+           op);
+  // grad_norm: P[e] = gout[dst] W_r^T (per-edge, [E, in]), then <P[e], x[src]>
+  Tensor proj = at::empty({E, K}, delta_node_feat_output.options());
+  check_rc(hetb_segment_mm(gout, col, 1, wt, f32w(proj, op, "proj"), eids, 1, rel_ptrs, R, E, 1, N, K, 0, st), op);
+  check_rc(hetb_inner_product_fwd(eids, row, nullptr, E, f32(proj, op, "proj"), x,
+                                  f32w(grad_edge_norm, op, "grad_edge_norm"), 1, K, st),
+           op);
+}
+
+// OpExport/RGCNOps.inc.h:23-82: ret[dst] = sum_e enorm[e] * feat_src[inverse_indices_row[e]] (direct indexing).
+void rgcn_node_mean_aggregation_compact_as_of_node_separate_coo(
+    Tensor &separate_coo_eids, Tensor &separate_coo_rel_ptrs, Tensor &separate_coo_row_indices,
+    Tensor &separate_coo_col_indices, TensorDict args_tensor_dict, Tensor &feat_src, Tensor &enorm, Tensor &ret,
+    bool direct_index_flag) {
+  const char *op = "rgcn_node_mean_aggregation_compact_as_of_node_separate_coo";
+  (void)separate_coo_rel_ptrs; (void)separate_coo_row_indices;
+  if (!direct_index_flag) check_rc(HETB_EUNSUPPORTED, op);  // binary-search kind: not built
+  Tensor inverse = args_tensor_dict.at("inverse_indices_row");
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_rgcn_aggregate_coo(i64(separate_coo_eids, op, "separate_coo_eids"),
+                                   i64(separate_coo_col_indices, op, "separate_coo_col_indices"),
+                                   i64(inverse, op, "inverse_indices_row"), separate_coo_eids.numel(), ret.size(0),
+                                   f32(feat_src, op, "feat_src"), f32(enorm, op, "enorm"), f32w(ret, op, "ret"),
+                                   (int)xlen(feat_src), stream_of(ret)),
+           op);
+}
+
+// OpExport/RGCNOps.inc.h:303-366: grad_feat_src[inverse_indices_row[e]] += enorm[e] * gradout[dst].
+// Separate-COO edge ids are canonical (position == edge id), which the index map relies on.
+void backward_rgcn_node_mean_aggregation_compact_as_of_node_separate_coo(
+    Tensor &separate_coo_eids, Tensor &separate_coo_rel_ptrs, Tensor &separate_coo_row_indices,
+    Tensor &separate_coo_col_indices, TensorDict args_tensor_dict, Tensor &feat_src, Tensor &enorm, Tensor &ret,
+    Tensor &gradout, Tensor &grad_feat_src, bool direct_index_flag) {
+  const char *op = "backward_rgcn_node_mean_aggregation_compact_as_of_node_separate_coo";
+  (void)separate_coo_rel_ptrs; (void)separate_coo_row_indices; (void)feat_src; (void)ret;
+  if (!direct_index_flag) check_rc(HETB_EUNSUPPORTED, op);
+  Tensor inverse = args_tensor_dict.at("inverse_indices_row");
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_aggregate_bwd(i64(separate_coo_col_indices, op, "separate_coo_col_indices"),
+                                  i64(separate_coo_eids, op, "separate_coo_eids"), separate_coo_eids.numel(),
+                                  f32(enorm, op, "enorm"), f32(gradout, op, "gradout"),
+                                  f32w(grad_feat_src, op, "grad_feat_src"), 1, (int)xlen(grad_feat_src),
+                                  i64(inverse, op, "inverse_indices_row"), nullptr, stream_of(gradout)),
+           op);
+}
+
+// hetb200 extension: the same aggregation over the in-CSR (edge-balanced walker, no atomics);
+// msg_idx is aligned with incsr_eids. Backward: hetb200_backward_hgt_message_aggregation_csr_compact.
+void hetb200_rgcn_node_aggregation_csr_compact(Tensor &incsr_row_ptrs, Tensor &incsr_eids, Tensor &msg_idx,
+                                               Tensor &feat_compact, Tensor &enorm, Tensor &ret) {
+  const char *op = "hetb200_rgcn_node_aggregation_csr_compact";
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_hgt_aggregate_fwd_csr(i64(incsr_row_ptrs, op, "incsr_row_ptrs"), i64(incsr_eids, op, "incsr_eids"),
+                                      incsr_row_ptrs.numel() - 1, incsr_eids.numel(),
+                                      f32(feat_compact, op, "feat_compact"), f32(enorm, op, "enorm"), nullptr,
+                                      f32w(ret, op, "ret"), 1, (int)xlen(feat_compact), 0,
+                                      i64(msg_idx, op, "msg_idx"), stream_of(ret)),
+           op);
+}
+
 // OpExport/HGTOps.inc.h:477-487
 void backward_hgt_full_graph_message_mean_aggregation_csr(
     Tensor &outcsr_row_ptrs, Tensor &outcsr_col_indices,
@@ -887,6 +1008,14 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_relational_fused_gat_csr_compact", hetb200_backward_relational_fused_gat_csr_compact);
   m.def("hetb200_backward_relational_fused_gat_compact_rows", hetb200_backward_relational_fused_gat_compact_rows);
   m.def("hetb200_hgt_message_aggregation_csr_compact", hetb200_hgt_message_aggregation_csr_compact);
+  // RGCN (OpExport/RGCNOps.inc.h:666-678)
+  m.def("rgcn_layer1_separate_coo", rgcn_layer1_separate_coo);
+  m.def("backward_rgcn_layer1_separate_coo", backward_rgcn_layer1_separate_coo);
+  m.def("rgcn_node_mean_aggregation_compact_as_of_node_separate_coo",
+        rgcn_node_mean_aggregation_compact_as_of_node_separate_coo);
+  m.def("backward_rgcn_node_mean_aggregation_compact_as_of_node_separate_coo",
+        backward_rgcn_node_mean_aggregation_compact_as_of_node_separate_coo);
+  m.def("hetb200_rgcn_node_aggregation_csr_compact", hetb200_rgcn_node_aggregation_csr_compact);
   m.def("hetb200_backward_hgt_message_aggregation_csr_compact",
         hetb200_backward_hgt_message_aggregation_csr_compact);
   m.def("hetb200_backward_hgt_edge_softmax_ops_csr_compact", hetb200_backward_hgt_edge_softmax_ops_csr_compact);

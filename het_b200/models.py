@@ -144,6 +144,103 @@ class HET_RGATModel(nn.Module):
         return h
 
 
+class HET_EglRelGraphConv_EdgeParallel(nn.Module):
+    """RGCN layer (hrt/python/RGCN/RGCN.py:194-350): out[dst] = sum_e norm[e] * x[src] @ W[rel(e)]
+    (+ bias, activation, dropout). ``compact_as_of_node_flag``: x @ W_r once per unique (relation,
+    source) pair, then the aggregation reads the compact rows by direct indexing;
+    ``csr_aggregation_flag`` (hetb200): that aggregation as the in-CSR walker instead of the
+    reference's edge-parallel COO kernel. Basis regularizer as in the reference."""
+
+    def __init__(self, in_feat, out_feat, num_rels, num_edges=None, regularizer="basis", num_bases=None,
+                 bias=True, activation=None, self_loop=False, compact_as_of_node_flag=False,
+                 compact_direct_indexing_flag=False, dropout=0.0, layer_type=1, csr_aggregation_flag=False):
+        super().__init__()
+        if self_loop:
+            raise NotImplementedError
+        if regularizer != "basis":
+            raise ValueError("Regularizer must be either 'basis' or 'bdd'")
+        self.in_feat, self.out_feat, self.num_rels = in_feat, out_feat, num_rels
+        self.compact_as_of_node_flag = compact_as_of_node_flag
+        self.compact_direct_indexing_flag = compact_direct_indexing_flag
+        self.csr_aggregation_flag = csr_aggregation_flag
+        self.num_bases = num_bases if (num_bases is not None and 0 < num_bases <= num_rels) else num_rels
+        self.bias, self.activation, self.layer_type = bias, activation, layer_type
+        self.weight = nn.Parameter(th.empty(self.num_bases, in_feat, out_feat))
+        nn.init.xavier_uniform_(self.weight, gain=nn.init.calculate_gain("relu"))
+        if self.num_bases < num_rels:
+            self.w_comp = nn.Parameter(th.empty(num_rels, self.num_bases))
+            nn.init.xavier_uniform_(self.w_comp, gain=nn.init.calculate_gain("relu"))
+        if bias:
+            self.h_bias = nn.Parameter(th.zeros(out_feat))
+        self.dropout = nn.Dropout(dropout)
+
+    def forward(self, g, x, norm=None):
+        if self.layer_type == 0:
+            raise NotImplementedError
+        if self.num_bases < self.num_rels:
+            weight = th.matmul(self.w_comp, self.weight.view(self.num_bases, -1)).view(
+                self.num_rels, self.in_feat, self.out_feat)
+        else:
+            weight = self.weight
+        if norm is None:
+            norm = th.ones(g.get_num_edges(), 1, dtype=x.dtype, device=x.device)
+        if self.compact_as_of_node_flag:
+            u = g.get_separate_unique_node_indices_single_sided()
+            feat_compact_src = B.rgnn_relational_matmul(
+                {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
+                 "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, weight.unsqueeze(1), x, True, 1)
+            feat_compact_src = feat_compact_src.squeeze(1)
+            if self.csr_aggregation_flag:
+                node_repr = B.rgcn_node_aggregation_csr_compact(g, feat_compact_src, norm)
+            else:
+                node_repr = B.rgcn_node_mean_aggregation_compact_as_of_node_separate_coo_single_sided(
+                    g, feat_compact_src, norm, self.compact_direct_indexing_flag)
+        else:
+            node_repr = B.rgcn_layer1_separate_coo(g, x, weight, norm)
+        if self.bias:
+            node_repr = node_repr + self.h_bias
+        if self.activation:
+            node_repr = self.activation(node_repr)
+        return self.dropout(node_repr)
+
+
+class HET_EGLRGCNSingleLayerModel(nn.Module):
+    """hrt/python/RGCN/RGCN.py:353-405 (separate_coo sparse format only)."""
+
+    def __init__(self, n_infeat, out_dim, num_rels, num_nodes=None, num_edges=None, sparse_format="separate_coo",
+                 num_bases=None, dropout=0.0, activation=None, compact_as_of_node_flag=False,
+                 compact_direct_indexing_flag=False, **kw):
+        super().__init__()
+        if sparse_format != "separate_coo":
+            raise NotImplementedError("seastar CSR/COO RGCN kernels are out of scope (DESIGN.md section 7)")
+        self.num_nodes = num_nodes
+        self.layer2 = HET_EglRelGraphConv_EdgeParallel(
+            n_infeat, out_dim, num_rels, num_edges, num_bases=num_bases, dropout=dropout, activation=activation,
+            layer_type=1, compact_as_of_node_flag=compact_as_of_node_flag,
+            compact_direct_indexing_flag=compact_direct_indexing_flag, **kw)
+
+    def forward(self, mydglgraph, feats, edge_norm):
+        return self.layer2(mydglgraph, feats, edge_norm)
+
+
+class HET_RGCNModel(nn.Module):
+    """Stack of RGCN layers, ReLU between them (the BASELINE "RGCN 2-layer" config; the reference
+    wires its HET RGCN as a single layer, RGCN.py:353-405, and its DGL baseline as two)."""
+
+    def __init__(self, num_rels, in_dim, h_dim, out_dim, num_layers=2, **kw):
+        super().__init__()
+        dims = [in_dim] + [h_dim] * (num_layers - 1) + [out_dim]
+        self.layers = nn.ModuleList(
+            HET_EglRelGraphConv_EdgeParallel(dims[i], dims[i + 1], num_rels,
+                                             activation=th.relu if i + 1 < num_layers else None, **kw)
+            for i in range(num_layers))
+
+    def forward(self, g, h, norm, gather=None):
+        for layer in self.layers:
+            h = layer(g, h if gather is None else gather(h), norm)
+        return h
+
+
 class HET_HGTLayerHetero(nn.Module):
     def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
                  compact_as_of_node_flag=False, compact_direct_indexing_flag=True,

@@ -26,14 +26,14 @@ from . import backend as B
 from . import parallel
 from .graph import HetGraph
 from .graphs import HeteroCOO
-from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel
+from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel, HET_RGCNModel
 
 
 class FullGraphTrainer:
     def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
                  layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0,
                  compact_as_of_node=False, fused=False):
-        assert kind in ("rgat", "hgt")
+        assert kind in ("rgat", "hgt", "rgcn")
         self.kind, self.device, self.rank, self.world, self.group = kind, torch.device(device), rank, world, group
         self.num_nodes_total = coo.num_nodes
         self.num_edges_total = coo.num_edges
@@ -55,6 +55,14 @@ class FullGraphTrainer:
             self.model = HET_RGATModel(coo.num_rels, hidden, hidden, out_dim, heads, layers,
                                        compact_as_of_node_flag=compact_as_of_node,
                                        linear_reorder_flag=bool(fused and compact_as_of_node)).to(self.device)
+        elif kind == "rgcn":
+            self.model = HET_RGCNModel(coo.num_rels, hidden, hidden, out_dim, layers,
+                                       compact_as_of_node_flag=compact_as_of_node, compact_direct_indexing_flag=True,
+                                       csr_aggregation_flag=bool(fused and compact_as_of_node)).to(self.device)
+            # edge norm 1 / in-degree(dst), indexed by canonical edge id (= separate-COO position)
+            col = self.g.get_separate_coo_original()["col_indices"]
+            deg = torch.bincount(col, minlength=self.g.get_num_nodes()).clamp(min=1).to(torch.float32)
+            self.edge_norm = (1.0 / deg[col]).view(-1, 1).contiguous()
         else:
             self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
                                            compact_as_of_node_flag=compact_as_of_node,
@@ -84,6 +92,8 @@ class FullGraphTrainer:
         return parallel.all_gather_rows(x, self.plan.max_rows, self.group)
 
     def forward(self, h0):
+        if self.kind == "rgcn":
+            return self.model(self.g, h0, self.edge_norm, None if self.world == 1 else self._gather)
         if self.world == 1:
             return self.model(self.g, h0)
         return self.model(self.g, h0, self._gather)

@@ -276,6 +276,22 @@ int hetb_hgt_fused_bwd_csr(const int64_t *row_ptr, const int64_t *dst, const int
                            float *grad_mu, int H, int F, void *stream);
 
 /* ------------------------------------------------------------------------
+ * RGCN
+ * ---------------------------------------------------------------------- */
+
+/* ret[dst_idx[i], :] = Σ_i norm[e] · feat[F(e), :],  e = eids[i],  F(e) = feat_idx ? feat_idx[e] : e.
+ * Edge-parallel aggregation over the separate COO: the second half of rgcn_layer1_separate_coo
+ * (OpExport/RGCNOps.inc.h:84-138; feat = per-edge X[src]·W_r rows from hetb_segment_mm) and
+ * rgcn_node_mean_aggregation_compact_as_of_node_separate_coo with direct indexing
+ * (RGCNOps.inc.h:23-82; feat compact, feat_idx = inverse_indices_row). ret is zero-filled here
+ * (the reference accumulates into a th.empty tensor). With a CSR at hand,
+ * hetb_hgt_aggregate_fwd_csr(divide_by_sum = 0) computes the same sum without atomics; the
+ * backward is hetb_hgt_aggregate_bwd (grad_feat) and hetb_inner_product_fwd (grad_norm). */
+int hetb_rgcn_aggregate_coo(const int64_t *eids, const int64_t *dst_idx, const int64_t *feat_idx,
+                            int64_t num_edges, int64_t num_dst, const float *feat,
+                            const float *norm, float *ret, int F, void *stream);
+
+/* ------------------------------------------------------------------------
  * Loss of the full-graph training step
  * ---------------------------------------------------------------------- */
 
