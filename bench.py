@@ -483,7 +483,8 @@ def _teardown(trainer, world):
     finished measurement into a hang, so a watchdog ends the process once the line is out."""
     if world <= 1:
         return
-    import threading
+    import torch
+    import torch.distributed as dist
     sys.stdout.flush()
     dog = threading.Timer(20.0, lambda: os._exit(0))
     dog.daemon = True
