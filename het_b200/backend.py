@@ -603,3 +603,91 @@ def rgcn_node_aggregation_csr_compact(g, feat_compact_src, enorm):
     return RgcnNodeAggregationCSRCompact.apply(
         incsr["row_ptrs"], incsr["eids"], outcsr["col_indices"], outcsr["eids"], uniq["incsr_inverse_idx_row"],
         uniq["outcsr_inverse_idx_row"], feat_compact_src.contiguous(), enorm.contiguous(), ret)
+
+
+class HGTReorderedProjections(th.autograd.Function):
+    """The three typed linears of one HGT layer input under linear operator reordering, as ONE
+    autograd node:  k = h.W_k[type];  left_c = h[dst].(W_q.W_att)[r] per unique (relation, dst);
+    msg_c = h[src].(W_v.W_msg)[r] per unique (relation, src). Same ops as calling
+    rgnn_relational_matmul_no_scatter_gather_list + rgnn_relational_matmul (kind 1) twice; the
+    point is the backward: the three input gradients land in ONE buffer (the node-typed linear
+    stores every row, the two compact ones scatter-add into it), which saves two zero-fills and
+    two [N, D] additions per layer that autograd would otherwise do to sum them."""
+
+    @staticmethod
+    def forward(ctx, offs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, k_linears, w_att, w_msg):
+        n, d_out = h.size(0), k_linears.size(1) * k_linears.size(3)
+        k = th.empty((n, d_out), dtype=h.dtype, device=h.device)
+        K.rgnn_relational_matmul_no_scatter_gather_list(offs, k_linears, h, k)
+        left = th.empty((nodes_col.numel(), w_att.size(1), w_att.size(3)), dtype=h.dtype, device=h.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col,
+                                  "unique_srcs_and_dests_node_indices": nodes_col}, 1, w_att, h, left, True)
+        msg = th.empty((nodes_row.numel(), w_msg.size(1), w_msg.size(3)), dtype=h.dtype, device=h.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row,
+                                  "unique_srcs_and_dests_node_indices": nodes_row}, 1, w_msg, h, msg, True)
+        ctx.save_for_backward(offs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, k_linears, w_att, w_msg)
+        return k, left, msg
+
+    @staticmethod
+    def backward(ctx, grad_k, grad_left, grad_msg):
+        offs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, k_linears, w_att, w_msg = ctx.saved_tensors
+        # the node-type offsets cover every row, so the first op writes all of grad_h
+        grad_h = th.empty_like(h, memory_format=th.contiguous_format)
+        grad_wk = th.zeros_like(k_linears, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(
+            offs, th.transpose(k_linears, 2, 3).contiguous(), h, grad_k.contiguous(), grad_h, grad_wk)
+        grad_watt = th.zeros_like(w_att, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col, "unique_srcs_and_dests_node_indices": nodes_col}, 1,
+            th.transpose(w_att, 2, 3).contiguous(), h, grad_left.contiguous(), grad_h, grad_watt, True)
+        grad_wmsg = th.zeros_like(w_msg, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row, "unique_srcs_and_dests_node_indices": nodes_row}, 1,
+            th.transpose(w_msg, 2, 3).contiguous(), h, grad_msg.contiguous(), grad_h, grad_wmsg, True)
+        return None, None, None, None, None, grad_h, grad_wk, grad_watt, grad_wmsg
+
+
+def hgt_reordered_projections(g, h, k_linears, w_att, w_msg):
+    u = g.get_separate_unique_node_indices_single_sided()
+    return HGTReorderedProjections.apply(
+        g.get_original_node_type_offsets(), u["rel_ptrs_col"], u["node_indices_col"], u["rel_ptrs_row"],
+        u["node_indices_row"], h.contiguous(), k_linears.contiguous(), w_att.contiguous(), w_msg.contiguous())
+
+
+class RelationalMatmulCompactPair(th.autograd.Function):
+    """Two compact typed linears of the SAME input as one autograd node (RGAT under linear operator
+    reordering: X.W_r per unique (relation, source) and X.(W_r.a_r) per unique (relation,
+    destination)): both input gradients scatter-add into one zero-filled buffer instead of two that
+    autograd then has to sum."""
+
+    @staticmethod
+    def forward(ctx, rel_ptrs_a, nodes_a, rel_ptrs_b, nodes_b, x, w_a, w_b):
+        out_a = th.empty((nodes_a.numel(), w_a.size(1), w_a.size(3)), dtype=x.dtype, device=x.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_a,
+                                  "unique_srcs_and_dests_node_indices": nodes_a}, 1, w_a, x, out_a, True)
+        out_b = th.empty((nodes_b.numel(), w_b.size(1), w_b.size(3)), dtype=x.dtype, device=x.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_b,
+                                  "unique_srcs_and_dests_node_indices": nodes_b}, 1, w_b, x, out_b, True)
+        ctx.save_for_backward(rel_ptrs_a, nodes_a, rel_ptrs_b, nodes_b, x, w_a, w_b)
+        return out_a, out_b
+
+    @staticmethod
+    def backward(ctx, grad_a, grad_b):
+        rel_ptrs_a, nodes_a, rel_ptrs_b, nodes_b, x, w_a, w_b = ctx.saved_tensors
+        grad_x = th.zeros_like(x, memory_format=th.contiguous_format)
+        grad_wa = th.zeros_like(w_a, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_a, "unique_srcs_and_dests_node_indices": nodes_a}, 1,
+            th.transpose(w_a, 2, 3).contiguous(), x, grad_a.contiguous(), grad_x, grad_wa, True)
+        grad_wb = th.zeros_like(w_b, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_b, "unique_srcs_and_dests_node_indices": nodes_b}, 1,
+            th.transpose(w_b, 2, 3).contiguous(), x, grad_b.contiguous(), grad_x, grad_wb, True)
+        return None, None, None, None, grad_x, grad_wa, grad_wb
+
+
+def relational_matmul_compact_pair(g, x, w_row, w_col):
+    u = g.get_separate_unique_node_indices_single_sided()
+    return RelationalMatmulCompactPair.apply(u["rel_ptrs_row"], u["node_indices_row"], u["rel_ptrs_col"],
+                                             u["node_indices_col"], x.contiguous(), w_row.contiguous(),
+                                             w_col.contiguous())

@@ -100,17 +100,23 @@ class HET_RGATLayer(nn.Module):
                "unique_srcs_and_dests_node_indices": u["node_indices_row"]}
         col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
                "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
-        feat_compact = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
-        el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
-            u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
+        er_compact = None
         if self.linear_reorder_flag:
-            w_r = th.einsum("rhkf,rhf->rhk", self.conv_weights, self.attn_r)  # [R, H, in]
-            er_compact = B.rgnn_relational_matmul(col, w_r.unsqueeze(-1), inputs_dst, True, 1)
+            w_r = th.einsum("rhkf,rhf->rhk", self.conv_weights, self.attn_r).unsqueeze(-1)  # [R, H, in, 1]
+            if inputs_dst is inputs:
+                # both compact products read the same X: one autograd node, one grad_X buffer
+                feat_compact, er_compact = B.relational_matmul_compact_pair(g, inputs, self.conv_weights, w_r)
+            else:
+                feat_compact = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
+                er_compact = B.rgnn_relational_matmul(col, w_r, inputs_dst, True, 1)
         else:
+            feat_compact = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
             feat_compact_dst = B.rgnn_relational_matmul(col, self.conv_weights, inputs_dst, True, 1)
             er_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
                 u["rel_ptrs_col"], self.attn_r.unsqueeze(-1),
                 feat_compact_dst.view(feat_compact_dst.size(0), -1))
+        el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
+            u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
         return B.relational_fused_gat_csr_compact(
             g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
             self.leaky_relu_slope)
@@ -284,7 +290,9 @@ class HET_HGTLayerHetero(nn.Module):
         offs = G.get_original_node_type_offsets()
         reorder = (self.linear_reorder_flag and self.compact_as_of_node_flag
                    and G.get_relation_node_types() is not None)
-        k = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
+        combined = reorder and gather is None  # k comes out of hgt_reordered_projections below
+        k = None if combined else B.rgnn_relational_matmul_no_scatter_gather_list(
+            offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
         if reorder:
             rel_src_type, rel_dst_type = G.get_relation_node_types()
             H, dk = self.num_heads, self.d_k
@@ -314,12 +322,18 @@ class HET_HGTLayerHetero(nn.Module):
             if not self.compact_direct_indexing_flag:
                 raise NotImplementedError("compact_as_of_node without direct indexing (binary search)")
             u = G.get_separate_unique_node_indices_single_sided()
-            attn_weight_dst_product_compact = B.rgnn_relational_matmul(
-                {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
-                 "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, w_att, q, reorder, 1)
-            message_compact = B.rgnn_relational_matmul(
-                {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
-                 "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, w_msg, v, reorder, 1)
+            if reorder and gather is None:
+                # k and the two compact products read the same h: one autograd node, one grad_h buffer
+                k, attn_weight_dst_product_compact, message_compact = B.hgt_reordered_projections(
+                    G, h, self.k_linears, w_att, w_msg)
+                k = k.view(-1, self.num_heads, self.d_k)
+            else:
+                attn_weight_dst_product_compact = B.rgnn_relational_matmul(
+                    {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"],
+                     "unique_srcs_and_dests_node_indices": u["node_indices_col"]}, w_att, q, reorder, 1)
+                message_compact = B.rgnn_relational_matmul(
+                    {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"],
+                     "unique_srcs_and_dests_node_indices": u["node_indices_row"]}, w_msg, v, reorder, 1)
             if reorder:
                 attn_weight_dst_product_compact = attn_weight_dst_product_compact.view(-1, self.num_heads, self.d_k)
                 message_compact = message_compact.view(-1, self.num_heads, self.d_k)
