@@ -691,3 +691,25 @@ def relational_matmul_compact_pair(g, x, w_row, w_col):
     return RelationalMatmulCompactPair.apply(u["rel_ptrs_row"], u["node_indices_row"], u["rel_ptrs_col"],
                                              u["node_indices_col"], x.contiguous(), w_row.contiguous(),
                                              w_col.contiguous())
+
+
+class AddBias(th.autograd.Function):
+    """h + bias (the layer epilogue, RGAT/models.py:264-278); the bias gradient is one column-sum
+    kernel over the incoming gradient and the input gradient is the incoming gradient itself."""
+
+    @staticmethod
+    def forward(ctx, h, bias):
+        return h + bias
+
+    @staticmethod
+    def backward(ctx, gradout):
+        gradout = gradout.contiguous()
+        grad_bias = th.empty(gradout.size(-1), dtype=gradout.dtype, device=gradout.device)
+        K.hetb200_column_sum(gradout.view(-1, gradout.size(-1)), grad_bias)
+        return gradout, grad_bias
+
+
+def add_bias(h, bias):
+    if h.is_cuda and h.dim() == 2 and h.size(1) % 4 == 0 and 256 % (h.size(1) // 4) == 0 and h.dtype == th.float32:
+        return AddBias.apply(h, bias)
+    return h + bias

@@ -78,6 +78,43 @@ __global__ void __launch_bounds__(kLossThreads)
   }
 }
 
+// Column sum of a row-major [rows, cols] matrix (cols a multiple of 4, <= 256): the gradient of the
+// layer bias, d/db (h + b) = sum over rows of the incoming gradient (HET_RGATLayer._epilogue,
+// hrt/python/RGAT/models.py:264-278). One lane per 4 columns, CTAs stride the rows, partial sums
+// meet in shared memory, one vector reduction per CTA into the zeroed output.
+__global__ void __launch_bounds__(kLossThreads)
+    column_sum_kernel(const float *__restrict__ x, int64_t rows, int cols, float *__restrict__ out) {
+  __shared__ float4 part[kLossThreads];
+  const int lpr = cols / 4;                       // lanes per row
+  const int groups = kLossThreads / lpr;          // rows per CTA step
+  const int g = threadIdx.x / lpr, l = threadIdx.x % lpr;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (g < groups) {
+    const int64_t stride = (int64_t)gridDim.x * groups;
+    int64_t r = (int64_t)blockIdx.x * groups + g;
+    for (; r + 3 * stride < rows; r += 4 * stride) {  // 4 rows in flight per lane
+      const float4 a = ldg4(x + r * cols + 4 * l), b = ldg4(x + (r + stride) * cols + 4 * l);
+      const float4 c = ldg4(x + (r + 2 * stride) * cols + 4 * l), d = ldg4(x + (r + 3 * stride) * cols + 4 * l);
+      acc.x += (a.x + b.x) + (c.x + d.x); acc.y += (a.y + b.y) + (c.y + d.y);
+      acc.z += (a.z + b.z) + (c.z + d.z); acc.w += (a.w + b.w) + (c.w + d.w);
+    }
+    for (; r < rows; r += stride) {
+      const float4 a = ldg4(x + r * cols + 4 * l);
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+  }
+  part[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x < lpr) {
+    float4 s = part[threadIdx.x];
+    for (int k = 1; k < groups; ++k) {
+      const float4 v = part[k * lpr + threadIdx.x];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    red_add4(out + 4 * threadIdx.x, s);
+  }
+}
+
 }  // namespace hetb
 
 using namespace hetb;
@@ -109,6 +146,22 @@ extern "C" int hetb_softmax_xent_bwd(const float *logits, const int64_t *labels,
   const int grid = (int)(need < kNumSMs * 16 ? need : kNumSMs * 16);
   xent_bwd_kernel<<<grid, kLossThreads, 0, (cudaStream_t)stream>>>(logits, labels, lse, grad_loss, num_rows,
                                                                    num_classes, 1.f / denom, grad_logits);
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+extern "C" int hetb_column_sum(const float *x, int64_t num_rows, int num_cols, float *out, void *stream) {
+  HETB_CHECK_ARG(num_rows >= 0 && num_cols > 0 && out);
+  if (num_cols % 4 || num_cols > 4 * kLossThreads || (kLossThreads % (num_cols / 4)) != 0) return HETB_EUNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t ce = cudaMemsetAsync(out, 0, sizeof(float) * (size_t)num_cols, st);
+  if (ce != cudaSuccess) return (int)ce;
+  if (num_rows == 0) return HETB_OK;
+  HETB_CHECK_ARG(x != nullptr);
+  const int groups = kLossThreads / (num_cols / 4);
+  const int64_t need = ceil_div64(num_rows, (int64_t)groups * 8);
+  const int grid = (int)(need < kNumSMs * 4 ? (need < 1 ? 1 : need) : kNumSMs * 4);
+  column_sum_kernel<<<grid, kLossThreads, 0, st>>>(x, num_rows, num_cols, out);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -626,6 +626,14 @@ void hetb200_rgcn_node_aggregation_csr_compact(Tensor &incsr_row_ptrs, Tensor &i
            op);
 }
 
+// hetb200 extension: grad of a layer bias = column sum of the incoming gradient.
+void hetb200_column_sum(Tensor &x, Tensor &out) {
+  const char *op = "hetb200_column_sum";
+  TORCH_CHECK(x.dim() == 2 && out.numel() == x.size(1), op, ": x must be [rows, cols] and out [cols]");
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(hetb_column_sum(f32(x, op, "x"), x.size(0), (int)x.size(1), f32w(out, op, "out"), stream_of(x)), op);
+}
+
 // OpExport/HGTOps.inc.h:477-487
 void backward_hgt_full_graph_message_mean_aggregation_csr(
     Tensor &outcsr_row_ptrs, Tensor &outcsr_col_indices,
@@ -1002,6 +1010,7 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
   m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
         hetb200_backward_hgt_fused_attention_aggregation_csr);
+  m.def("hetb200_column_sum", hetb200_column_sum);
   m.def("hetb200_softmax_cross_entropy", hetb200_softmax_cross_entropy);
   m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);

@@ -126,7 +126,7 @@ class HET_RGATLayer(nn.Module):
         if self.self_loop:
             h = h + th.matmul(inputs_dst, self.loop_weight)
         if self.bias:
-            h = h + self.h_bias
+            h = B.add_bias(h, self.h_bias)
         if self.activation:
             h = self.activation(h)
         return self.dropout(h)
@@ -204,7 +204,7 @@ class HET_EglRelGraphConv_EdgeParallel(nn.Module):
         else:
             node_repr = B.rgcn_layer1_separate_coo(g, x, weight, norm)
         if self.bias:
-            node_repr = node_repr + self.h_bias
+            node_repr = B.add_bias(node_repr, self.h_bias)
         if self.activation:
             node_repr = self.activation(node_repr)
         return self.dropout(node_repr)

@@ -335,6 +335,10 @@ int hetb_stable_sort_by_key(const int64_t *key, int64_t num_edges,
 int hetb_expand_row_ptr(const int64_t *row_ptr, int64_t num_rows,
                         int64_t num_edges, int64_t *row_idx, void *stream);
 
+/* out[c] = sum_i x[i, c] for a row-major [num_rows, num_cols] matrix: the gradient of the layer
+ * bias (h + b; hrt/python/RGAT/models.py:264-278, RGCN/RGCN.py:343-344). num_cols % 4 == 0. */
+int hetb_column_sum(const float *x, int64_t num_rows, int num_cols, float *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

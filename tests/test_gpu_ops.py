@@ -170,3 +170,15 @@ def test_softmax_cross_entropy(cuda, n, c):
     ref.backward()
     close(loss, ref, "loss")
     close(x.grad, x64.grad, "grad logits", rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rows,cols", [(0, 64), (1, 64), (7300, 64), (94_001, 64), (1000, 16), (513, 128)])
+def test_column_sum(cuda, rows, cols):
+    """hetb200_column_sum (the bias gradient) against torch in fp64."""
+    from het_b200.kernels import K
+    torch.manual_seed(0)
+    x = torch.randn(rows, cols, device=cuda)
+    out = torch.full((cols,), 7.0, device=cuda)  # must be overwritten, not accumulated into
+    K.hetb200_column_sum(x, out)
+    close(out, x.double().sum(0).cpu(), "column sum", rtol=1e-4, atol=1e-5)
