@@ -713,3 +713,64 @@ def add_bias(h, bias):
     if h.is_cuda and h.dim() == 2 and h.size(1) % 4 == 0 and 256 % (h.size(1) // 4) == 0 and h.dtype == th.float32:
         return AddBias.apply(h, bias)
     return h + bias
+
+
+class RelationalFusedGatCSRCompactWithLogits(th.autograd.Function):
+    """el = <feat_compact, attn_l[r]> followed by relational_fused_gat_csr_compact as ONE autograd node:
+    the same two ops (rgnn_relational_matmul_no_scatter_gather_list + the compact in-CSR RGAT op),
+    but in the backward the el path adds its part of grad_feat straight into the buffer the edge
+    backward produced, instead of a second [U, D] tensor that autograd then sums with it."""
+
+    @staticmethod
+    def forward(ctx, rel_ptrs_row, incsr_row_ptr, incsr_eids, in_inverse_row, in_inverse_col, bwd0, bwd1, bwd2, bwd3,
+                feat_compact, er_compact, attn_l, s, exp, ret, slope, by_rows):
+        u, h = feat_compact.size(0), attn_l.size(1)
+        el = th.empty((u, h), dtype=feat_compact.dtype, device=feat_compact.device)
+        w_l = attn_l.unsqueeze(-1).contiguous()
+        K.rgnn_relational_matmul_no_scatter_gather_list(rel_ptrs_row, w_l, feat_compact.view(u, -1), el)
+        el = el.view(u, h, 1)
+        ctx.mark_dirty(ret)
+        K.hetb200_relational_fused_gat_csr_compact(
+            incsr_row_ptr, incsr_eids, in_inverse_row, in_inverse_col, feat_compact, el, er_compact, s, exp, ret,
+            slope)
+        ctx.save_for_backward(rel_ptrs_row, bwd0, bwd1, bwd2, bwd3, feat_compact, el, er_compact, w_l, s, exp, ret)
+        ctx.slope, ctx.by_rows = slope, by_rows
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        rel_ptrs_row, bwd0, bwd1, bwd2, bwd3, feat, el, er, w_l, s, exp, ret = ctx.saved_tensors
+        grad_el = th.zeros_like(el, memory_format=th.contiguous_format)
+        grad_er = th.zeros_like(er, memory_format=th.contiguous_format)
+        grad_feat = th.zeros_like(feat, memory_format=th.contiguous_format)
+        if ctx.by_rows:  # (urow_dst, urow_eids, urow_ptrs, urow_inverse_idx_col)
+            K.hetb200_backward_relational_fused_gat_compact_rows(
+                bwd2, bwd0, bwd1, bwd3, feat, el, er, s, exp, ret, gradout.contiguous(), grad_feat, grad_el,
+                grad_er, ctx.slope)
+        else:            # (outcsr_col_indices, outcsr_eids, outcsr_inverse_idx_row, outcsr_inverse_idx_col)
+            K.hetb200_backward_relational_fused_gat_csr_compact(
+                bwd0, bwd1, bwd2, bwd3, feat, el, er, s, exp, ret, gradout.contiguous(), grad_feat, grad_el,
+                grad_er, ctx.slope)
+        grad_wl = th.zeros_like(w_l, memory_format=th.contiguous_format)
+        u = feat.size(0)
+        K.hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate(
+            rel_ptrs_row, th.transpose(w_l, 2, 3).contiguous(), feat.view(u, -1), grad_el.view(u, -1),
+            grad_feat.view(u, -1), grad_wl)
+        return (None,) * 9 + (grad_feat, grad_er, grad_wl.squeeze(-1), None, None, None, None, None)
+
+
+def relational_fused_gat_csr_compact_with_logits(graph, feat_compact, er_compact, attn_l, slope):
+    incsr, outcsr = graph.get_in_csr(), graph.get_out_csr()
+    uniq = graph.get_separate_unique_node_indices_single_sided()
+    h = attn_l.size(1)
+    exp = feat_compact.new_empty([graph.get_num_edges(), h, 1])
+    s = feat_compact.new_empty([graph.get_num_nodes(), h])
+    ret = feat_compact.new_empty([graph.get_num_nodes()] + list(feat_compact.size()[1:]))
+    if RGAT_COMPACT_BACKWARD_BY_ROWS:
+        bwd = (uniq["urow_dst"], uniq["urow_eids"], uniq["urow_ptrs"], uniq["urow_inverse_idx_col"])
+    else:
+        bwd = (outcsr["col_indices"], outcsr["eids"], uniq["outcsr_inverse_idx_row"], uniq["outcsr_inverse_idx_col"])
+    return RelationalFusedGatCSRCompactWithLogits.apply(
+        uniq["rel_ptrs_row"], incsr["row_ptrs"], incsr["eids"], uniq["incsr_inverse_idx_row"],
+        uniq["incsr_inverse_idx_col"], bwd[0], bwd[1], bwd[2], bwd[3], feat_compact.contiguous(),
+        er_compact.contiguous(), attn_l.contiguous(), s, exp, ret, slope, RGAT_COMPACT_BACKWARD_BY_ROWS)

@@ -192,11 +192,11 @@ void rgnn_relational_matmul_no_scatter_gather_list(Tensor &ntype_offset_ptrs,
 }
 
 // OpExport/RGNNOps.inc.h:744-753
-void backward_rgnn_relational_matmul_no_scatter_gather_list(
+static void backward_no_scatter_gather_impl(const char *op, bool force_accumulate,
+    
     Tensor &ntype_offset_ptrs, Tensor &weights_transposed,
     Tensor &node_feat_input, Tensor &grad_node_feat_output,
     Tensor &grad_node_feat_input, Tensor &grad_weights) {
-  const char *op = "backward_rgnn_relational_matmul_no_scatter_gather_list";
   TORCH_CHECK(weights_transposed.dim() == 4, op, ": weights must be 4-D");
   const int H = (int)weights_transposed.size(1),
             N = (int)weights_transposed.size(2),
@@ -207,7 +207,7 @@ void backward_rgnn_relational_matmul_no_scatter_gather_list(
   void *st = stream_of(grad_node_feat_output);
   const int64_t *ptrs = i64(ntype_offset_ptrs, op, "ntype_offset_ptrs");
   const int64_t T = ntype_offset_ptrs.numel() - 1;
-  const int accumulate = (a_heads == 1 && H > 1) ? 1 : 0;
+  const int accumulate = (force_accumulate || (a_heads == 1 && H > 1)) ? 1 : 0;
   check_rc(hetb_segment_mm(f32(grad_node_feat_output, op, "grad_node_feat_output"),
                            nullptr, H,
                            f32(weights_transposed, op, "weights_transposed"),
@@ -219,6 +219,24 @@ void backward_rgnn_relational_matmul_no_scatter_gather_list(
                f32(grad_node_feat_output, op, "grad_node_feat_output"), nullptr,
                H, f32w(grad_weights, op, "grad_weights"), ptrs, T, M, H, K, N, st),
            op);
+}
+
+void backward_rgnn_relational_matmul_no_scatter_gather_list(
+    Tensor &ntype_offset_ptrs, Tensor &weights_transposed, Tensor &node_feat_input,
+    Tensor &grad_node_feat_output, Tensor &grad_node_feat_input, Tensor &grad_weights) {
+  backward_no_scatter_gather_impl("backward_rgnn_relational_matmul_no_scatter_gather_list", false, ntype_offset_ptrs,
+                                  weights_transposed, node_feat_input, grad_node_feat_output, grad_node_feat_input,
+                                  grad_weights);
+}
+
+// hetb200 extension: the same backward, but the input gradient is ADDED to grad_node_feat_input
+// (which already holds the gradient that reached the same tensor through another consumer).
+void hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate(
+    Tensor &ntype_offset_ptrs, Tensor &weights_transposed, Tensor &node_feat_input,
+    Tensor &grad_node_feat_output, Tensor &grad_node_feat_input, Tensor &grad_weights) {
+  backward_no_scatter_gather_impl("hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate", true,
+                                  ntype_offset_ptrs, weights_transposed, node_feat_input, grad_node_feat_output,
+                                  grad_node_feat_input, grad_weights);
 }
 
 // OpExport/RGNNOps.inc.h:609-658
@@ -1011,6 +1029,8 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
         hetb200_backward_hgt_fused_attention_aggregation_csr);
   m.def("hetb200_column_sum", hetb200_column_sum);
+  m.def("hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate",
+        hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate);
   m.def("hetb200_softmax_cross_entropy", hetb200_softmax_cross_entropy);
   m.def("hetb200_backward_softmax_cross_entropy", hetb200_backward_softmax_cross_entropy);
   m.def("hetb200_relational_fused_gat_csr_compact", hetb200_relational_fused_gat_csr_compact);

@@ -115,6 +115,10 @@ class HET_RGATLayer(nn.Module):
             er_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
                 u["rel_ptrs_col"], self.attn_r.unsqueeze(-1),
                 feat_compact_dst.view(feat_compact_dst.size(0), -1))
+        if self.linear_reorder_flag:
+            # el row-dot + edge pass as one autograd node (one grad_feat buffer)
+            return B.relational_fused_gat_csr_compact_with_logits(
+                g, feat_compact, er_compact.view(-1, self.num_heads, 1), self.attn_l, self.leaky_relu_slope)
         el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
             u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
         return B.relational_fused_gat_csr_compact(
