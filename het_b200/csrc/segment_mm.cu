@@ -163,41 +163,27 @@ __global__ void __launch_bounds__(kMMThreads)
                         int64_t M, int H, int hw, int accumulate) {
   constexpr int GROUPS = kMMThreads / LPR;
   constexpr int D = LPR * 4;
-  constexpr int U = 4;  // rows in flight per lane group: one 16 B load per lane does not cover the HBM latency
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
   const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  const int64_t iters = ceil_div64(M, stride * U);
-  int64_t i0 = (int64_t)blockIdx.x * GROUPS + g;
-  for (int64_t it = 0; it < iters; ++it, i0 += stride * U) {
-    bool ok[U];
-    int s[U];
-    int64_t ar[U];
-    float4 x[U], w[U];
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      const int64_t i = i0 + j * stride;
-      ok[j] = i < M;
-      s[j] = ok[j] ? segment_of(seg_ptrs, num_segs, i) : 0;
-      ar[j] = (ok[j] && a_idx) ? __ldg(a_idx + i) : i;
+  const int64_t iters = ceil_div64(M, stride);
+  int64_t i = (int64_t)blockIdx.x * GROUPS + g;
+  for (int64_t it = 0; it < iters; ++it, i += stride) {
+    const bool ok = i < M;
+    float v = 0.f;
+    if (ok) {
+      const int s = segment_of(seg_ptrs, num_segs, i);
+      const int64_t ar = a_idx ? __ldg(a_idx + i) : i;
+      v = dot4(ldcs4(A + ar * D + 4 * l), ldg4(W + (int64_t)s * D + 4 * l));
     }
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      x[j] = ok[j] ? ldcs4(A + ar[j] * D + 4 * l) : make_float4(0.f, 0.f, 0.f, 0.f);
-      w[j] = ldg4(W + (int64_t)s[j] * D + 4 * l);
-    }
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      const int64_t i = i0 + j * stride;
-      const float v = group_sum(dot4(x[j], w[j]), hw);
-      if (ok[j] && leader) {
-        const int64_t cr = c_idx ? __ldg(c_idx + i) : i;
-        if (accumulate)
-          atomicAdd(Y + cr * H + h, v);
-        else
-          Y[cr * H + h] = v;
-      }
+    v = group_sum(v, hw);
+    if (ok && leader) {
+      const int64_t cr = c_idx ? __ldg(c_idx + i) : i;
+      if (accumulate)
+        atomicAdd(Y + cr * H + h, v);
+      else
+        Y[cr * H + h] = v;
     }
   }
 }
@@ -213,38 +199,20 @@ __global__ void __launch_bounds__(kMMThreads)
                         int64_t M, int H, int hw, int accumulate) {
   constexpr int GROUPS = kMMThreads / LPR;
   constexpr int D = LPR * 4;
-  constexpr int U = 4;  // rows in flight per lane group (segment search, index and scalar loads overlap)
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int h = l / hw;
   const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  for (int64_t i0 = (int64_t)blockIdx.x * GROUPS + g; i0 < M; i0 += stride * U) {
-    bool ok[U];
-    int s[U];
-    int64_t ar[U], cr[U];
-    float a[U];
-    float4 w[U];
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      const int64_t i = i0 + j * stride;
-      ok[j] = i < M;
-      s[j] = ok[j] ? segment_of(seg_ptrs, num_segs, i) : 0;
-      ar[j] = (ok[j] && a_idx) ? __ldg(a_idx + i) : i;
-      cr[j] = (ok[j] && c_idx) ? __ldg(c_idx + i) : i;
-    }
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      a[j] = ok[j] ? __ldg(A + ar[j] * H + h) : 0.f;
-      w[j] = ldg4(W + (int64_t)s[j] * D + 4 * l);
-    }
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      if (!ok[j]) continue;
-      const float4 y = make_float4(a[j] * w[j].x, a[j] * w[j].y, a[j] * w[j].z, a[j] * w[j].w);
-      if (accumulate)
-        red_add4(Y + cr[j] * D + 4 * l, y);
-      else
-        stcs4(Y + cr[j] * D + 4 * l, y);
-    }
+  for (int64_t i = (int64_t)blockIdx.x * GROUPS + g; i < M; i += stride) {
+    const int s = segment_of(seg_ptrs, num_segs, i);
+    const int64_t ar = a_idx ? __ldg(a_idx + i) : i;
+    const int64_t cr = c_idx ? __ldg(c_idx + i) : i;
+    const float a = __ldg(A + ar * H + h);
+    const float4 w = ldg4(W + (int64_t)s * D + 4 * l);
+    const float4 y = make_float4(a * w.x, a * w.y, a * w.z, a * w.w);
+    if (accumulate)
+      red_add4(Y + cr * D + 4 * l, y);
+    else
+      stcs4(Y + cr * D + 4 * l, y);
   }
 }
 
