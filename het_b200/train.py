@@ -89,7 +89,7 @@ class FullGraphTrainer:
 
     # ------------------------------------------------------------------
     def _gather(self, x):
-        return parallel.all_gather_rows(x, self.plan.max_rows, self.group)
+        return parallel.gather_rows(x, self.plan, self.group)
 
     def forward(self, h0):
         if self.kind == "rgcn":

@@ -184,7 +184,7 @@ def test_hgt_fused_on_padded_shard_sources(cuda):
     from het_b200 import graphs, parallel
     from het_b200.models import HET_HGT_DGLHetero
     coo = graphs.SHAPES["mag"](scale=0.005)
-    plan = parallel.make_shard(coo, 3, 4)
+    plan = parallel.make_shard(coo, 3, 4, layout="padded")
     g = parallel.shard_graph(plan, coo, cuda)
     n = plan.num_local_nodes
     assert plan.num_gathered_rows > 2 * n  # the padding is there

@@ -29,7 +29,12 @@ def test_shards_cover_every_edge_once_and_remap_sources():
     world = 3
     seen = 0
     for r in range(world):
-        p = parallel.make_shard(coo, r, world)
+        g = parallel.make_shard(coo, r, world)  # default layout: global ids, nothing padded
+        mine = (coo.dst >= g.lo) & (coo.dst < g.hi)
+        assert g.layout == "global" and np.array_equal(g.src, coo.src[mine])
+        assert g.num_gathered_rows == coo.num_nodes and sum(g.sizes) == coo.num_nodes
+        assert g.gathered_offset == g.lo
+        p = parallel.make_shard(coo, r, world, layout="padded")
         seen += p.src.size
         assert p.dst.min() >= 0 and p.dst.max() < p.num_local_nodes
         # padded source id -> (owner, local row) -> global id round-trips
@@ -49,19 +54,19 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, layout="global"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from het_b200 import graphs, parallel
         coo = graphs.aifb_shaped(scale=0.2)
-        plan = parallel.make_shard(coo, rank, world)
+        plan = parallel.make_shard(coo, rank, world, layout=layout)
         torch.manual_seed(0)
         x_full = torch.randn(coo.num_nodes, 8, dtype=torch.float64)
         w = torch.randn(8, 4, dtype=torch.float64, requires_grad=True)
         x_loc = x_full[plan.lo:plan.hi].clone().requires_grad_(True)
-        xg = parallel.all_gather_rows(x_loc, plan.max_rows)
-        assert xg.shape[0] == world * plan.max_rows
+        xg = parallel.gather_rows(x_loc, plan)
+        assert xg.shape[0] == plan.num_gathered_rows
         # a toy "layer": out[dst] += (x[src] @ w), loss = sum(out * c)
         src, dst = torch.from_numpy(plan.src), torch.from_numpy(plan.dst)
         out = torch.zeros(plan.num_local_nodes, 4, dtype=torch.float64).index_add(0, dst, xg[src] @ w)
@@ -82,11 +87,12 @@ def _worker(rank, world, port, q):
 
 
 @pytest.mark.timeout(180)
-def test_all_gather_rows_autograd_gloo_world2():
+@pytest.mark.parametrize("layout", ["global", "padded"])
+def test_all_gather_rows_autograd_gloo_world2(layout):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, layout)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:

@@ -33,7 +33,7 @@ def run(rank, profile=False):
 
     def gather(t):  # stand-in for the all-gather: own rows at their place in the padded layout, zeros elsewhere
         out = t.new_zeros((plan.num_gathered_rows,) + tuple(t.shape[1:]))
-        out[plan.rank * plan.max_rows: plan.rank * plan.max_rows + n] = t
+        out[plan.gathered_offset: plan.gathered_offset + n] = t
         return out
 
     def step():
