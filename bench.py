@@ -53,8 +53,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="hetb200", choices=["hetb200", "reference"])
-    ap.add_argument("--workload", default="rgat_bgs", choices=sorted(WORKLOADS))
-    ap.add_argument("--scale", type=float, default=None, help="graph scale (default 1.0 x gpus)")
+    ap.add_argument("--workload", default="hgt_mag", choices=sorted(WORKLOADS),
+                    help="default hgt_mag = BASELINE.json configs[2] on one GPU and configs[4] (the same graph, "
+                         "sharded by destination range: strong scaling) on N > 1")
+    ap.add_argument("--scale", type=float, default=None,
+                    help="graph scale; default 1.0 (the named config, strong scaling over --gpus); "
+                         "--scale N with --gpus N grows the graph with the GPU count (weak scaling)")
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
@@ -451,8 +455,13 @@ def _peaks():
 def _make_graph(args):
     from het_b200 import graphs
     kind, shape, heads, layers, cfg = WORKLOADS[args.workload]
-    scale = args.scale if args.scale is not None else float(max(1, args.gpus))
+    scale = args.scale if args.scale is not None else 1.0
     return graphs.SHAPES[shape](scale=scale), scale
+
+
+def _scaling_label(args, scale):
+    """"weak" when the graph grows with the GPU count (--scale == --gpus > 1), else "strong" (total work fixed)."""
+    return "weak" if (args.gpus > 1 and abs(scale - args.gpus) < 1e-9) else "strong"
 
 
 def run_reference(args, rank):
@@ -465,7 +474,8 @@ def run_reference(args, rank):
     val, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, args.steps, args.warmup, budget_s=150.0)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": _scaling_label(args, scale),
+        "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s), hidden 64, {heads} head(s), "
                                f"{coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
@@ -486,7 +496,12 @@ def _teardown(trainer, world):
     import torch
     import torch.distributed as dist
     sys.stdout.flush()
-    dog = threading.Timer(20.0, lambda: os._exit(0))
+    def _stuck():
+        sys.stderr.write("bench.py: NCCL communicator teardown did not return within 60 s; exiting with code 3\n")
+        sys.stderr.flush()
+        os._exit(3)
+
+    dog = threading.Timer(60.0, _stuck)
     dog.daemon = True
     dog.start()
     trainer._graphs.clear()
@@ -605,7 +620,8 @@ def main():
     peak, peak_src = _peaks()
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": _scaling_label(args, scale), "vs_baseline": None,
+        "dtype": "f32",
         "data": "synthetic",
         "config": {
             "workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s) fwd+loss+bwd+Adam, hidden 64, "
@@ -646,7 +662,8 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         trainer = None
         torch.cuda.empty_cache()
-        v, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, 3, 1, budget_s=25.0)
+        big = coo.num_edges > 5_000_000  # one full-graph CPU step at mag / wikikg2 size is ~20 s: no warm-up step
+        v, ms, cores, sample, done = cpu_dgl_baseline(args.workload, coo, 1 if big else 3, 0 if big else 1, budget_s=25.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                                 "ms_per_step": ms}
     print(json.dumps(line), flush=True)

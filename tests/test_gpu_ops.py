@@ -11,14 +11,7 @@ pytestmark = pytest.mark.gpu
 RTOL, ATOL = 1e-4, 1e-5
 
 
-def close(got, want, what, rtol=RTOL, atol=ATOL):
-    g = got.detach().double().cpu().reshape(-1)
-    w = want.detach().double().cpu().reshape(-1)
-    assert g.shape == w.shape, f"{what}: shape {got.shape} vs {want.shape}"
-    scale = w.abs().max().clamp(min=1.0)
-    err = (g - w).abs()
-    bad = err > (atol * scale + rtol * w.abs())
-    assert not bool(bad.any()), f"{what}: max err {err.max():.3e} (scale {scale:.3e}), {int(bad.sum())} bad"
+from oracle.testing import close  # noqa: E402,F401  (re-exported: other test modules import it from here)
 
 
 def make_graph(n, e, r, seed, hub=False):

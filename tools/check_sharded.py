@@ -28,14 +28,19 @@ compact = len(sys.argv) > 2 and sys.argv[2] == "compact"
 sh = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world, cuda_graph=False,
                       compact_as_of_node=compact, fused=compact)
 full = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=0, world=1, cuda_graph=False)
+# magnitude-preserving weights (same on both arms and on every rank): logits and every gradient O(0.1-1)
+from oracle.testing import unit_gain_init  # noqa: E402
+unit_gain_init(sh.model, seed=11)
+unit_gain_init(full.model, seed=11)
 
 
-def close(a, b, what, rtol=1e-4, atol=1e-5):
+def close(a, b, what, rtol=1e-4, atol=2e-5):
+    """relative to max|reference| (no absolute floor); prints the reference magnitude beside the error"""
     a, b = a.double(), b.double()
-    scale = b.abs().max().clamp(min=1.0)
+    scale = b.abs().max()
     err = (a - b).abs()
-    ok = bool((err <= atol * scale + rtol * b.abs()).all())
-    print(f"[rank {rank}] {what}: max err {err.max():.3e} {'ok' if ok else 'FAIL'}", flush=True)
+    ok = bool((err <= atol * scale + rtol * b.abs()).all()) and bool(torch.isfinite(a).all())
+    print(f"[rank {rank}] {what}: max err {err.max():.3e} vs max|ref| {scale:.3e} {'ok' if ok else 'FAIL'}", flush=True)
     return ok
 
 
@@ -55,8 +60,8 @@ tot = loss_sh.detach().clone()
 dist.all_reduce(tot)
 ok &= close(tot, loss_full.detach(), "loss")
 for (n1, p1), (n2, p2) in zip(sh.model.named_parameters(), full.model.named_parameters()):
-    ok &= close(p1.grad, p2.grad, f"grad {n1}", rtol=5e-4, atol=5e-5)
-ok &= close(sh.embed.embeds.grad, full.embed.embeds.grad[lo:hi], "grad embedding shard", rtol=5e-4, atol=5e-5)
+    ok &= close(p1.grad, p2.grad, f"grad {n1}", rtol=2e-4, atol=3e-5)
+ok &= close(sh.embed.embeds.grad, full.embed.embeds.grad[lo:hi], "grad embedding shard", rtol=2e-4, atol=3e-5)
 # a few optimizer steps through the public API (eager + captured)
 for _ in range(3):
     l_sh = sh.step()
