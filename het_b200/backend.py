@@ -774,3 +774,111 @@ def relational_fused_gat_csr_compact_with_logits(graph, feat_compact, er_compact
         uniq["rel_ptrs_row"], incsr["row_ptrs"], incsr["eids"], uniq["incsr_inverse_idx_row"],
         uniq["incsr_inverse_idx_col"], bwd[0], bwd[1], bwd[2], bwd[3], feat_compact.contiguous(),
         er_compact.contiguous(), attn_l.contiguous(), s, exp, ret, slope, RGAT_COMPACT_BACKWARD_BY_ROWS)
+
+
+# ----- plan-based fused edge passes (csrc/edge_plan.cu): the bench default -----------------------
+USE_EDGE_PLAN = True  # False: the compact in-CSR / out-CSR walkers of csrc/edge_ops.cu (int64 indices, no max-subtraction)
+
+
+class HGTFusedAttentionAggregationPlan(th.autograd.Function):
+    """Same op as HGTFusedAttentionAggregationCSRCompact (inner product + edge softmax + message
+    aggregation, compact inputs) on the graph's walk plans: int32 indices, (destination, relation)-
+    sorted forward / (source, relation)-sorted backward walks, max-subtracted online softmax. Saved
+    for the backward: the raw score per edge and the log-sum-exp per (destination, head)."""
+
+    @staticmethod
+    def forward(ctx, graph, left_compact, k, message_compact, mu):
+        pl = graph.get_edge_plan()
+        n, e, h = graph.get_num_nodes(), graph.get_num_edges(), mu.size(1)
+        f = message_compact.size(2)
+        sc = graph.plan_scratch(h, h * f)
+        dev = mu.device
+        new_h = th.empty((n, h, f), dtype=th.float32, device=dev)
+        lse = th.empty((n, h), dtype=th.float32, device=dev)
+        attn = th.empty((e, h), dtype=th.float32, device=dev)
+        K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, left_compact, k, message_compact, mu, attn, lse,
+                                     new_h, sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"])
+        ctx.graph = graph
+        ctx.save_for_backward(left_compact, k, message_compact, mu, attn, lse, new_h)
+        return new_h
+
+    @staticmethod
+    def backward(ctx, gradout):
+        left, k, msg, mu, attn, lse, new_h = ctx.saved_tensors
+        graph = ctx.graph
+        pl = graph.get_edge_plan()
+        h, f = mu.size(1), msg.size(2)
+        sc = graph.plan_scratch(h, h * f)
+        f32 = dict(dtype=th.float32, device=mu.device)
+        grad_left = th.zeros(left.shape, **f32)
+        grad_mu = th.zeros(mu.shape, **f32)
+        grad_k = th.empty(k.shape, **f32)
+        grad_msg = th.empty(msg.shape, **f32)
+        K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
+                                     gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
+        return None, grad_left, grad_k, grad_msg, grad_mu
+
+
+def hgt_fused_attention_and_aggregation_plan(graph, left_compact, k, message_compact, mu):
+    return HGTFusedAttentionAggregationPlan.apply(graph, left_compact.contiguous(), k.contiguous(),
+                                                  message_compact.contiguous(), mu.contiguous())
+
+
+class RelationalFusedGatPlan(th.autograd.Function):
+    """relational_fused_gat_csr on compact inputs over the walk plans; with ``attn_l`` given the
+    el = <feat_compact, attn_l[r]> row-dot and its backward are part of the node (as in
+    RelationalFusedGatCSRCompactWithLogits). Saves only lse [N, H] and ret: no per-edge tensor."""
+
+    @staticmethod
+    def forward(ctx, graph, feat_compact, el_compact, er_compact, attn_l, slope):
+        pl = graph.get_edge_plan()
+        uniq = graph.get_separate_unique_node_indices_single_sided()
+        n = graph.get_num_nodes()
+        u, h, f = feat_compact.size(0), feat_compact.size(1), feat_compact.size(2)
+        w_l = None
+        if attn_l is not None:
+            el_compact = th.empty((u, h), dtype=th.float32, device=feat_compact.device)
+            w_l = attn_l.unsqueeze(-1).contiguous()
+            K.rgnn_relational_matmul_no_scatter_gather_list(uniq["rel_ptrs_row"], w_l, feat_compact.view(u, -1),
+                                                            el_compact)
+        el_compact = el_compact.view(u, h).contiguous()
+        er_compact = er_compact.reshape(-1, h).contiguous()
+        sc = graph.plan_scratch(h, h * f)
+        ret = th.empty((n, h, f), dtype=th.float32, device=feat_compact.device)
+        lse = th.empty((n, h), dtype=th.float32, device=feat_compact.device)
+        K.hetb200_rgat_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, feat_compact, el_compact, er_compact, slope, lse,
+                                      ret, sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"])
+        ctx.graph, ctx.slope, ctx.with_logits = graph, slope, attn_l is not None
+        ctx.save_for_backward(feat_compact, el_compact, er_compact, lse, ret, w_l if w_l is not None else lse)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        feat, el, er, lse, ret, w_l = ctx.saved_tensors
+        graph = ctx.graph
+        pl = graph.get_edge_plan()
+        u, h, f = feat.size(0), feat.size(1), feat.size(2)
+        sc = graph.plan_scratch(h, h * f)
+        grad_feat = th.empty_like(feat)
+        grad_el = th.empty_like(el)
+        grad_er = th.zeros_like(er)
+        K.hetb200_rgat_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, feat, el, er, lse, ret, gradout.contiguous(),
+                                      sc["gdot"], grad_feat, grad_el, grad_er, ctx.slope)
+        if not ctx.with_logits:
+            return None, grad_feat, grad_el.view(u, h, 1), grad_er.view(-1, h, 1), None, None
+        uniq = graph.get_separate_unique_node_indices_single_sided()
+        grad_wl = th.zeros_like(w_l)
+        K.hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate(
+            uniq["rel_ptrs_row"], th.transpose(w_l, 2, 3).contiguous(), feat.view(u, -1), grad_el.view(u, -1),
+            grad_feat.view(u, -1), grad_wl)
+        return None, grad_feat, None, grad_er.view(-1, h, 1), grad_wl.squeeze(-1), None
+
+
+def relational_fused_gat_plan(graph, feat_compact, el_compact, er_compact, slope):
+    return RelationalFusedGatPlan.apply(graph, feat_compact.contiguous(), el_compact.contiguous(),
+                                        er_compact.contiguous(), None, slope)
+
+
+def relational_fused_gat_plan_with_logits(graph, feat_compact, er_compact, attn_l, slope):
+    return RelationalFusedGatPlan.apply(graph, feat_compact.contiguous(), None, er_compact.contiguous(),
+                                        attn_l.contiguous(), slope)

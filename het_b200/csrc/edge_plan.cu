@@ -1,0 +1,704 @@
+// Plan-based fused edge passes (the benchmark's default path).
+//
+// A *walk plan* (include/hetb200.h: hetb_walk_plan) is built once per graph (het_b200/graph.py:
+// HetGraph.get_edge_plan) and holds int32-narrowed, position-aligned index arrays in the order the
+// kernel walks them, plus the work decomposition:
+//   * positions are sorted by (destination, relation) for the forward passes and by (source,
+//     relation) for the backward passes, so the compact (relation, node) row on the walked side is
+//     constant over a run of consecutive positions: it is fetched from DRAM once per run (the
+//     repeated per-position loads hit L1) and its gradient is a register accumulator;
+//   * work items are runs of ~32 consecutive positions whose boundaries are snapped to row / run
+//     starts, so only rows longer than an item (power-law hubs) are ever split across lane groups;
+//   * rows without positions are listed, not skipped over at run time; the row of an item's first
+//     position is stored, not searched.
+// Softmax is the max-subtracted online form (north star; the reference kernels overflow at
+// logit > 88: GAT/FusedGAT.cu.h:193-203, HGT/HGTForwardKernels.cu.h:499-508): a lane group carries
+// (running max m, sum s, accumulator acc) per row and head, rescaling on a new max. A row split
+// across items leaves one partial (m, s, acc) per item in a scratch slot and an atomic max of m in
+// the row's slot of `lse`; a second kernel, parallel over the partial slots, adds
+// exp(m - M)·(s, acc) into the row, a third normalises the split rows and leaves
+// lse = M + log(sum). The backward recomputes the normalised score as exp(x - lse[dst]), so the
+// per-edge exp() of the reference is never stored.
+//
+// T = float or __nv_bfloat16 is the STORAGE type of the gathered tables (the compact rows and the
+// node rows read per edge); all arithmetic and every accumulator / gradient is fp32.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace hetb {
+
+constexpr int kPThreads = 256;
+constexpr int kMaxSmemMuPlan = 4096;
+
+template <typename T>
+__device__ __forceinline__ float4 ld_row4(const T *base, int64_t row, int D, int l);
+
+template <>
+__device__ __forceinline__ float4 ld_row4<float>(const float *base, int64_t row, int D, int l) {
+  return ldg4(base + row * D + 4 * l);
+}
+template <>
+__device__ __forceinline__ float4 ld_row4<__nv_bfloat16>(const __nv_bfloat16 *base, int64_t row, int D, int l) {
+  const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(base + row * D + 4 * l));
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162 *>(&raw.x);
+  const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162 *>(&raw.y);
+  const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+  return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+
+// Sum over the `width` lanes of one head inside a lane group; only the lanes of `mask` take part,
+// so the lane groups of one warp may be at different trip counts.
+__device__ __forceinline__ float group_sum_m(float v, int width, unsigned mask) {
+  for (int o = width >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void atomic_max_float(float *addr, float v) {
+  if (v >= 0.f) atomicMax(reinterpret_cast<int *>(addr), __float_as_int(v));
+  else atomicMin(reinterpret_cast<unsigned *>(addr), __float_as_uint(v));
+}
+
+template <int LPR>
+__device__ __forceinline__ unsigned group_mask() {
+  if (LPR == 32) return 0xffffffffu;
+  const unsigned base = (threadIdx.x & 31) / LPR * LPR;
+  return ((1u << LPR) - 1u) << base;
+}
+
+constexpr float kNegInf = -3.0e38f;  // finite stand-in for -inf: exp(kNegInf - x) == 0, no inf - inf
+
+// ---------------------------------------------------------------------------
+// Pre-pass of a forward walk: rows listed in fix_rows (split across items) get ret = 0,
+// lse = -"inf" (atomic-max target), ssum = 0; rows in empty_rows get ret = 0, lse = 0.
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_fwd_prepare_kernel(const int *__restrict__ fix_rows, int num_fix, const int *__restrict__ empty_rows,
+                            int num_empty, float *__restrict__ ret, float *__restrict__ lse,
+                            float *__restrict__ ssum, int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int i = blockIdx.x * GROUPS + g;
+  if (i >= num_fix + num_empty) return;
+  const bool fix = i < num_fix;
+  const int64_t d = fix ? __ldg(fix_rows + i) : __ldg(empty_rows + (i - num_fix));
+  st4(ret + d * D + 4 * l, make_float4(0.f, 0.f, 0.f, 0.f));
+  if ((l % hw) == 0) {
+    lse[d * H + l / hw] = fix ? kNegInf : 0.f;
+    if (fix) ssum[d * H + l / hw] = 0.f;
+  }
+}
+
+// Partial slots of split rows -> the row: w = exp(m_slot - M_row); ret += w·acc, ssum += w·s.
+template <int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_fwd_merge_kernel(const int *__restrict__ pslot, const int *__restrict__ pslot_row, int num_pslots,
+                          const float *__restrict__ part_m, const float *__restrict__ part_s,
+                          const float *__restrict__ part_acc, const float *__restrict__ lse /* holds M */,
+                          float *__restrict__ ssum, float *__restrict__ ret, int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int i = blockIdx.x * GROUPS + g;
+  if (i >= num_pslots) return;
+  const int64_t x = __ldg(pslot + i), d = __ldg(pslot_row + i);
+  const int h = l / hw;
+  const float w = __expf(__ldg(part_m + x * H + h) - __ldg(lse + d * H + h));
+  const float4 a = ldcs4(part_acc + x * D + 4 * l);
+  red_add4(ret + d * D + 4 * l, make_float4(w * a.x, w * a.y, w * a.z, w * a.w));
+  if ((l % hw) == 0) atomicAdd(ssum + d * H + h, w * __ldg(part_s + x * H + h));
+}
+
+// Split rows: ret /= ssum; lse = M + log(ssum).
+template <int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_fwd_normalize_kernel(const int *__restrict__ fix_rows, int num_fix, const float *__restrict__ ssum,
+                              float *__restrict__ lse, float *__restrict__ ret, int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int i = blockIdx.x * GROUPS + g;
+  if (i >= num_fix) return;
+  const int64_t d = __ldg(fix_rows + i);
+  const int h = l / hw;
+  const float s = ssum[d * H + h];
+  const float inv = s > 0.f ? 1.f / s : 0.f;
+  float4 v = *reinterpret_cast<const float4 *>(ret + d * D + 4 * l);
+  st4(ret + d * D + 4 * l, make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv));
+  if ((l % hw) == 0) lse[d * H + h] = lse[d * H + h] + __logf(s);
+}
+
+// ---------------------------------------------------------------------------
+// HGT forward: attention score + edge softmax + weighted aggregation in one walk over the
+// (destination, relation)-sorted positions. For position p of destination d:
+//   a[p,h] = <left[L(p),h,:], kv[src(p),h,:]>            (RGNN/InnerProductEdgeParallel.cu.h:13-113)
+//   x      = a[p,h] · mu[rel(L(p)),h]                     (HGT/HGTForwardKernels.cu.h:425-587)
+//   ret[d,h,:] = Σ_p softmax_p(x) · msg[M(p),h,:]         (HGT/HGTForwardKernels.cu.h:244-369)
+// Saved for the backward: a (position order, 4·H bytes per edge) and lse[d,h].
+// MODE_RGAT (same walk, RGAT's logits): x = leaky_relu(el[M(p),h] + er[L(p),h]), msg = feat
+// (GAT/FusedGAT.cu.h:123-222,33-116); nothing per edge is saved (the backward recomputes x).
+// ---------------------------------------------------------------------------
+template <typename T, int LPR, bool MODE_RGAT>
+__global__ void __launch_bounds__(kPThreads)
+    plan_fwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
+                         const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
+                         const int *__restrict__ p_src, const int *__restrict__ p_msg,
+                         const int *__restrict__ p_left, const int *__restrict__ ucol_rel,
+                         const T *__restrict__ left, const T *__restrict__ kv, const T *__restrict__ msg,
+                         const float *__restrict__ mu,            // HGT: [R,H]
+                         const float *__restrict__ el, const float *__restrict__ er, float slope,  // RGAT
+                         float *__restrict__ attn, float *__restrict__ lse, float *__restrict__ ret,
+                         float *__restrict__ part_m, float *__restrict__ part_s, float *__restrict__ part_acc,
+                         int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  constexpr int U = 4;  // positions in flight per lane group
+  const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int g = blockIdx.x * GROUPS + grp;
+  if (g >= num_items) return;  // whole lane group leaves: its lanes are in no other group's mask
+  const unsigned gm = group_mask<LPR>();
+  const int h = l / hw;
+  const bool leader = (l % hw) == 0;
+  const int p0 = __ldg(item_ptr + g), p1 = __ldg(item_ptr + g + 1);
+  int j = __ldg(item_row + g);
+  int64_t d = __ldg(nz_rows + j) & 0x7fffffff;
+  int row_start = __ldg(nz_ptr + j), row_end = __ldg(nz_ptr + j + 1);
+  float m = kNegInf, s = 0.f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  auto flush = [&]() {
+    if (row_start >= p0 && row_end <= p1) {  // the whole row was walked here
+      const float inv = s > 0.f ? 1.f / s : 0.f;
+      st4(ret + d * D + 4 * l, make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv));
+      if (leader) lse[d * H + h] = m + __logf(s);
+    } else {  // a piece of a split row: partial (m, s, acc) into this item's head / tail slot
+      const int64_t x = 2 * (int64_t)g + (row_start < p0 ? 0 : 1);
+      stcs4(part_acc + x * D + 4 * l, acc);
+      if (leader) {
+        part_m[x * H + h] = m;
+        part_s[x * H + h] = s;
+        atomic_max_float(lse + d * H + h, m);
+      }
+    }
+  };
+
+  for (int p = p0; p < p1; p += U) {
+    int sn[U], mi[U], li[U];
+    float xs[U];
+    float4 lv[U], kvv[U], mv[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int pp = (p + q < p1) ? p + q : p1 - 1;  // clamp: the tail repeats the last position (masked below)
+      mi[q] = __ldg(p_msg + pp);
+      li[q] = __ldg(p_left + pp);
+      if (!MODE_RGAT) sn[q] = __ldg(p_src + pp);
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      mv[q] = ld_row4<T>(msg, mi[q], D, l);
+      if (!MODE_RGAT) {
+        lv[q] = ld_row4<T>(left, li[q], D, l);
+        kvv[q] = ld_row4<T>(kv, sn[q], D, l);
+        xs[q] = __ldg(mu + __ldg(ucol_rel + li[q]) * H + h);
+      } else {
+        xs[q] = __ldg(el + (int64_t)mi[q] * H + h) + __ldg(er + (int64_t)li[q] * H + h);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int pp = p + q;
+      if (pp < p1) {  // uniform inside the lane group
+        if (pp == row_end) {
+          flush();
+          ++j;
+          d = __ldg(nz_rows + j) & 0x7fffffff;
+          row_start = pp;
+          row_end = __ldg(nz_ptr + j + 1);
+          m = kNegInf; s = 0.f;
+          acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        float x;
+        if (!MODE_RGAT) {
+          const float a = group_sum_m(dot4(lv[q], kvv[q]), hw, gm);
+          if (leader) attn[(int64_t)pp * H + h] = a;
+          x = a * xs[q];
+        } else {
+          x = xs[q] > 0.f ? xs[q] : slope * xs[q];
+        }
+        const float mn = fmaxf(m, x);
+        const float sc = __expf(m - mn), w = __expf(x - mn);
+        acc.x = fmaf(acc.x, sc, w * mv[q].x);
+        acc.y = fmaf(acc.y, sc, w * mv[q].y);
+        acc.z = fmaf(acc.z, sc, w * mv[q].z);
+        acc.w = fmaf(acc.w, sc, w * mv[q].w);
+        s = fmaf(s, sc, w);
+        m = mn;
+      }
+    }
+  }
+  flush();
+}
+
+// ---------------------------------------------------------------------------
+// Pre-pass of a backward walk: zero the rows of `buf` ([*, D]) listed in rows[0..n).
+// ---------------------------------------------------------------------------
+template <int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_zero_rows_kernel(const int *__restrict__ rows, int n, float *__restrict__ buf, float *__restrict__ aux,
+                          int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int i = blockIdx.x * GROUPS + g;
+  if (i >= n) return;
+  const int64_t r = __ldg(rows + i) & 0x7fffffff;
+  st4(buf + r * D + 4 * l, make_float4(0.f, 0.f, 0.f, 0.f));
+  if (aux && (l % hw) == 0) aux[r * H + l / hw] = 0.f;
+}
+
+// <a[d,h,:], b[d,h,:]> per (row, head): the softmax Jacobian's per-destination term <gout, out>.
+template <int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_rowdot_kernel(const float *__restrict__ a, const float *__restrict__ b, int64_t num_rows,
+                       float *__restrict__ out, int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int64_t d = (int64_t)blockIdx.x * GROUPS + g;
+  if (d >= num_rows) return;
+  const unsigned gm = group_mask<LPR>();
+  const float4 x = ldg4(a + d * D + 4 * l), y = ldg4(b + d * D + 4 * l);
+  const float v = group_sum_m(dot4(x, y), hw, gm);
+  if ((l % hw) == 0) out[d * H + l / hw] = v;
+}
+
+// ---------------------------------------------------------------------------
+// HGT backward of plan_fwd_walk_kernel in ONE walk over the (source, relation)-sorted positions
+// (replaces HGTBackwardKernels.cu.h:343-440, 499-627 and InnerProductEdgeParallel.cu.h:119-202).
+// For position p of source s, run u = M(p) (compact (relation, source) row), destination d:
+//   nrm = exp(a[q]·mu − lse[d,h])  (q = the forward position of the edge)
+//   sg  = (<gout[d,h,:], msg[u,h,:]> − <gout[d,h,:], out[d,h,:]>) · nrm
+//   ga  = sg · mu[r,h];   grad_mu[r,h] += sg · a[q]
+//   grad_msg[u,h,:]    += nrm · gout[d,h,:]      register accumulator of the run, one store
+//   grad_kv[s,h,:]     += ga  · left[L(p),h,:]   register accumulator of the row, one store
+//   grad_left[L(p),h,:] += ga · kv[s,h,:]         vector reduction (destination side: the only
+//                                                 gradient the source-major order cannot own)
+// Rows / runs split across items (bit 31 of nz_rows[j] / urow_rel[u]) are pre-zeroed and reduced.
+// ---------------------------------------------------------------------------
+template <typename T, int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_hgt_bwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
+                             const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
+                             const int *__restrict__ p_dst, const int *__restrict__ p_left,
+                             const int *__restrict__ p_msg, const int *__restrict__ p_perm,
+                             const int *__restrict__ urow_rel, int num_rels, const T *__restrict__ left,
+                             const T *__restrict__ kv, const T *__restrict__ msg, const float *__restrict__ mu,
+                             const float *__restrict__ attn, const float *__restrict__ lse,
+                             const float *__restrict__ gdoto, const float *__restrict__ gout,
+                             float *__restrict__ grad_left, float *__restrict__ grad_kv,
+                             float *__restrict__ grad_msg, float *__restrict__ grad_mu, int H, int hw,
+                             int use_smem) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  constexpr int U = 2;
+  extern __shared__ float mu_acc[];
+  const int RH = num_rels * H;
+  if (use_smem) {
+    for (int i = threadIdx.x; i < RH; i += kPThreads) mu_acc[i] = 0.f;
+    __syncthreads();
+  }
+  const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int g = blockIdx.x * GROUPS + grp;
+  const unsigned gm = group_mask<LPR>();
+  const int h = l / hw;
+  const bool leader = (l % hw) == 0;
+  if (g < num_items) {
+    const int p0 = __ldg(item_ptr + g), p1 = __ldg(item_ptr + g + 1);
+    int j = __ldg(item_row + g);
+    int rowword = __ldg(nz_rows + j);
+    int64_t srow = rowword & 0x7fffffff;
+    int row_end = __ldg(nz_ptr + j + 1);
+    float4 kvr = ld_row4<T>(kv, srow, D, l);
+    float4 acc_k = make_float4(0.f, 0.f, 0.f, 0.f);
+    // run state
+    int cur_u = -1, relword = 0;
+    float4 msgr = make_float4(0.f, 0.f, 0.f, 0.f), acc_m = make_float4(0.f, 0.f, 0.f, 0.f);
+    float mu_r = 0.f, acc_mu = 0.f;
+
+    auto flush_run = [&]() {
+      if (cur_u < 0) return;
+      if (relword < 0) red_add4(grad_msg + (int64_t)cur_u * D + 4 * l, acc_m);  // split run
+      else st4(grad_msg + (int64_t)cur_u * D + 4 * l, acc_m);
+      if (leader) {
+        const int r = relword & 0x7fffffff;
+        if (use_smem) atomicAdd(&mu_acc[r * H + h], acc_mu);
+        else atomicAdd(grad_mu + r * H + h, acc_mu);
+      }
+    };
+    auto flush_row = [&]() {
+      if (rowword < 0) red_add4(grad_kv + srow * D + 4 * l, acc_k);  // split row
+      else st4(grad_kv + srow * D + 4 * l, acc_k);
+    };
+
+    for (int p = p0; p < p1; p += U) {
+      int dn[U], li[U], ui[U], pq[U];
+      float aa[U], ls[U], cc[U];
+      float4 go[U], lv[U];
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        const int pp = (p + q < p1) ? p + q : p1 - 1;
+        dn[q] = __ldg(p_dst + pp);
+        li[q] = __ldg(p_left + pp);
+        ui[q] = __ldg(p_msg + pp);
+        pq[q] = __ldg(p_perm + pp);
+      }
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        go[q] = ldg4(gout + (int64_t)dn[q] * D + 4 * l);
+        lv[q] = ld_row4<T>(left, li[q], D, l);
+        aa[q] = __ldg(attn + (int64_t)pq[q] * H + h);
+        ls[q] = __ldg(lse + (int64_t)dn[q] * H + h);
+        cc[q] = __ldg(gdoto + (int64_t)dn[q] * H + h);
+      }
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        const int pp = p + q;
+        if (pp < p1) {  // uniform inside the lane group
+          if (pp == row_end) {
+            flush_run();
+            cur_u = -1;
+            flush_row();
+            ++j;
+            rowword = __ldg(nz_rows + j);
+            srow = rowword & 0x7fffffff;
+            row_end = __ldg(nz_ptr + j + 1);
+            kvr = ld_row4<T>(kv, srow, D, l);
+            acc_k = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          if (ui[q] != cur_u) {
+            flush_run();
+            cur_u = ui[q];
+            relword = __ldg(urow_rel + cur_u);
+            msgr = ld_row4<T>(msg, cur_u, D, l);
+            mu_r = __ldg(mu + (relword & 0x7fffffff) * H + h);
+            acc_m = make_float4(0.f, 0.f, 0.f, 0.f);
+            acc_mu = 0.f;
+          }
+          const float sdot = group_sum_m(dot4(go[q], msgr), hw, gm) - cc[q];
+          const float nrm = __expf(aa[q] * mu_r - ls[q]);
+          const float sg = sdot * nrm;
+          const float ga = sg * mu_r;
+          acc_mu = fmaf(sg, aa[q], acc_mu);
+          fma4(acc_m, nrm, go[q]);
+          fma4(acc_k, ga, lv[q]);
+          red_add4(grad_left + (int64_t)li[q] * D + 4 * l,
+                   make_float4(ga * kvr.x, ga * kvr.y, ga * kvr.z, ga * kvr.w));
+        }
+      }
+    }
+    flush_run();
+    flush_row();
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < RH; i += kPThreads) {
+      const float v = mu_acc[i];
+      if (v != 0.f) atomicAdd(grad_mu + i, v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// RGAT backward in plan form: one walk over the positions grouped by compact (relation, source)
+// row u (GAT/FusedGATBackward.cu.h:31-148 restated): feat[u], el[u] are run constants,
+// grad_feat[u] / grad_el[u] register accumulators with one store per run; the normalised score
+// is recomputed as exp(lrelu(el[u] + er[L]) − lse[d]); <gout[d], ret[d]> comes from the pre-pass.
+// grad_er takes one scalar atomic per edge and head (destination side).
+// ---------------------------------------------------------------------------
+template <typename T, int LPR>
+__global__ void __launch_bounds__(kPThreads)
+    plan_rgat_bwd_walk_kernel(const int *__restrict__ item_ptr, int num_items, const int *__restrict__ p_dst,
+                              const int *__restrict__ p_left, const int *__restrict__ p_msg,
+                              const int *__restrict__ urow_rel, const T *__restrict__ feat,
+                              const float *__restrict__ el, const float *__restrict__ er,
+                              const float *__restrict__ lse, const float *__restrict__ gdotr,
+                              const float *__restrict__ gout, float *__restrict__ grad_feat,
+                              float *__restrict__ grad_el, float *__restrict__ grad_er, int H, int hw,
+                              float slope) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  constexpr int U = 4;
+  const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int g = blockIdx.x * GROUPS + grp;
+  if (g >= num_items) return;
+  const unsigned gm = group_mask<LPR>();
+  const int h = l / hw;
+  const bool leader = (l % hw) == 0;
+  const int p0 = __ldg(item_ptr + g), p1 = __ldg(item_ptr + g + 1);
+  int cur_u = -1, relword = 0;
+  float4 featr = make_float4(0.f, 0.f, 0.f, 0.f), acc_f = make_float4(0.f, 0.f, 0.f, 0.f);
+  float elr = 0.f, acc_el = 0.f;
+
+  auto flush_run = [&]() {
+    if (cur_u < 0) return;
+    if (relword < 0) {
+      red_add4(grad_feat + (int64_t)cur_u * D + 4 * l, acc_f);
+      if (leader) atomicAdd(grad_el + (int64_t)cur_u * H + h, acc_el);
+    } else {
+      st4(grad_feat + (int64_t)cur_u * D + 4 * l, acc_f);
+      if (leader) grad_el[(int64_t)cur_u * H + h] = acc_el;
+    }
+  };
+
+  for (int p = p0; p < p1; p += U) {
+    int dn[U], li[U], ui[U];
+    float ls[U], cc[U], erv[U];
+    float4 go[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int pp = (p + q < p1) ? p + q : p1 - 1;
+      dn[q] = __ldg(p_dst + pp);
+      li[q] = __ldg(p_left + pp);
+      ui[q] = __ldg(p_msg + pp);
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      go[q] = ldg4(gout + (int64_t)dn[q] * D + 4 * l);
+      ls[q] = __ldg(lse + (int64_t)dn[q] * H + h);
+      cc[q] = __ldg(gdotr + (int64_t)dn[q] * H + h);
+      erv[q] = __ldg(er + (int64_t)li[q] * H + h);
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      if (p + q < p1) {  // uniform inside the lane group
+        if (ui[q] != cur_u) {
+          flush_run();
+          cur_u = ui[q];
+          relword = __ldg(urow_rel + cur_u);
+          featr = ld_row4<T>(feat, cur_u, D, l);
+          elr = __ldg(el + (int64_t)cur_u * H + h);
+          acc_f = make_float4(0.f, 0.f, 0.f, 0.f);
+          acc_el = 0.f;
+        }
+        const float sdot = group_sum_m(dot4(go[q], featr), hw, gm) - cc[q];
+        const float x = elr + erv[q];
+        const float a = __expf((x > 0.f ? x : slope * x) - ls[q]);
+        fma4(acc_f, a, go[q]);
+        if (leader) {
+          const float v = sdot * a * (x > 0.f ? 1.f : slope);
+          acc_el += v;
+          atomicAdd(grad_er + (int64_t)li[q] * H + h, v);
+        }
+      }
+    }
+  }
+  flush_run();
+}
+
+static int plan_lpr(int H, int F) {
+  if (H <= 0 || F <= 0 || (F % 4) != 0) return 0;
+  if (!is_pow2(H) || !is_pow2(F)) return 0;
+  const int v = H * F / 4;
+  if (v < 4 || v > 32) return 0;
+  return v;
+}
+
+#define PLAN_LPR(lpr, CALL)                         \
+  switch (lpr) {                                    \
+    case 4: { constexpr int L = 4; CALL; } break;   \
+    case 8: { constexpr int L = 8; CALL; } break;   \
+    case 16: { constexpr int L = 16; CALL; } break; \
+    case 32: { constexpr int L = 32; CALL; } break; \
+    default: return HETB_EUNSUPPORTED;              \
+  }
+
+static inline unsigned grid_for(int64_t n, int groups) { return (unsigned)(n > 0 ? ceil_div64(n, groups) : 1); }
+
+template <typename T, bool RGAT>
+static int fwd_plan_launch(const hetb_walk_plan *pl, const T *left, const T *kv, const T *msg, const float *mu,
+                           const float *el, const float *er, float slope, float *attn, float *lse, float *ret,
+                           float *part_m, float *part_s, float *part_acc, float *ssum, int H, int F,
+                           cudaStream_t st) {
+  const int lpr = plan_lpr(H, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  const int groups = kPThreads / lpr;
+  const int hw = F / 4;
+  if (pl->num_fix_rows + pl->num_empty_rows > 0) {
+    PLAN_LPR(lpr, (plan_fwd_prepare_kernel<L><<<grid_for(pl->num_fix_rows + pl->num_empty_rows, groups), kPThreads,
+                                              0, st>>>(pl->fix_rows, pl->num_fix_rows, pl->empty_rows,
+                                                       pl->num_empty_rows, ret, lse, ssum, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  if (pl->num_items == 0) return HETB_OK;
+  PLAN_LPR(lpr, (plan_fwd_walk_kernel<T, L, RGAT><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
+                    pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_b,
+                    pl->idx_c, pl->row_rel, left, kv, msg, mu, el, er, slope, attn, lse, ret, part_m, part_s,
+                    part_acc, H, hw)));
+  HETB_LAUNCH_OK();
+  if (pl->num_pslots > 0) {
+    PLAN_LPR(lpr, (plan_fwd_merge_kernel<L><<<grid_for(pl->num_pslots, groups), kPThreads, 0, st>>>(
+                      pl->pslot, pl->pslot_row, pl->num_pslots, part_m, part_s, part_acc, lse, ssum, ret, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  if (pl->num_fix_rows > 0) {
+    PLAN_LPR(lpr, (plan_fwd_normalize_kernel<L><<<grid_for(pl->num_fix_rows, groups), kPThreads, 0, st>>>(
+                      pl->fix_rows, pl->num_fix_rows, ssum, lse, ret, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  return HETB_OK;
+}
+
+static bool plan_ok_fwd(const hetb_walk_plan *pl) {
+  return pl && pl->num_items >= 0 &&
+         (pl->num_items == 0 || (pl->item_ptr && pl->item_row && pl->nz_rows && pl->nz_ptr && pl->idx_b && pl->idx_c)) &&
+         (pl->num_fix_rows == 0 || pl->fix_rows) && (pl->num_empty_rows == 0 || pl->empty_rows) &&
+         (pl->num_pslots == 0 || (pl->pslot && pl->pslot_row));
+}
+
+}  // namespace hetb
+
+using namespace hetb;
+
+extern "C" int hetb_hgt_fused_fwd_plan(const hetb_walk_plan *plan, const void *left, const void *kv,
+                                       const void *msg, int table_dtype, const float *mu, float *attn, float *lse,
+                                       float *ret, float *part_m, float *part_s, float *part_acc, float *ssum,
+                                       int H, int F, void *stream) {
+  HETB_CHECK_ARG(plan_ok_fwd(plan) && lse && ret);
+  HETB_CHECK_ARG(plan->num_items == 0 || (left && kv && msg && mu && attn && plan->idx_a && plan->row_rel));
+  HETB_CHECK_ARG(plan->num_pslots == 0 || (part_m && part_s && part_acc && ssum));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (table_dtype == HETB_DTYPE_F32)
+    return fwd_plan_launch<float, false>(plan, (const float *)left, (const float *)kv, (const float *)msg, mu,
+                                         nullptr, nullptr, 0.f, attn, lse, ret, part_m, part_s, part_acc, ssum, H, F,
+                                         st);
+  if (table_dtype == HETB_DTYPE_BF16)
+    return fwd_plan_launch<__nv_bfloat16, false>(plan, (const __nv_bfloat16 *)left, (const __nv_bfloat16 *)kv,
+                                                 (const __nv_bfloat16 *)msg, mu, nullptr, nullptr, 0.f, attn, lse,
+                                                 ret, part_m, part_s, part_acc, ssum, H, F, st);
+  return HETB_EUNSUPPORTED;
+}
+
+extern "C" int hetb_rgat_fused_fwd_plan(const hetb_walk_plan *plan, const void *feat, int table_dtype,
+                                        const float *el, const float *er, float slope, float *lse, float *ret,
+                                        float *part_m, float *part_s, float *part_acc, float *ssum, int H, int F,
+                                        void *stream) {
+  HETB_CHECK_ARG(plan_ok_fwd(plan) && lse && ret);
+  HETB_CHECK_ARG(plan->num_items == 0 || (feat && el && er));
+  HETB_CHECK_ARG(plan->num_pslots == 0 || (part_m && part_s && part_acc && ssum));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (table_dtype == HETB_DTYPE_F32)
+    return fwd_plan_launch<float, true>(plan, nullptr, nullptr, (const float *)feat, nullptr, el, er, slope, nullptr,
+                                        lse, ret, part_m, part_s, part_acc, ssum, H, F, st);
+  if (table_dtype == HETB_DTYPE_BF16)
+    return fwd_plan_launch<__nv_bfloat16, true>(plan, nullptr, nullptr, (const __nv_bfloat16 *)feat, nullptr, el, er,
+                                                slope, nullptr, lse, ret, part_m, part_s, part_acc, ssum, H, F, st);
+  return HETB_EUNSUPPORTED;
+}
+
+template <typename T>
+static int hgt_bwd_plan_launch(const hetb_walk_plan *pl, int64_t num_rels, int64_t num_dst, const T *left,
+                               const T *kv, const T *msg, const float *mu, const float *attn, const float *lse,
+                               const float *out, const float *gout, float *gdoto, float *grad_left, float *grad_kv,
+                               float *grad_msg, float *grad_mu, int H, int F, cudaStream_t st) {
+  const int lpr = plan_lpr(H, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  const int groups = kPThreads / lpr;
+  const int hw = F / 4;
+  if (pl->num_fix_rows > 0) {
+    PLAN_LPR(lpr, (plan_zero_rows_kernel<L><<<grid_for(pl->num_fix_rows, groups), kPThreads, 0, st>>>(
+                      pl->fix_rows, pl->num_fix_rows, grad_kv, nullptr, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  if (pl->num_fix_runs > 0) {
+    PLAN_LPR(lpr, (plan_zero_rows_kernel<L><<<grid_for(pl->num_fix_runs, groups), kPThreads, 0, st>>>(
+                      pl->fix_runs, pl->num_fix_runs, grad_msg, nullptr, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  if (pl->num_items == 0) return HETB_OK;
+  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, out, num_dst, gdoto, H,
+                                                                                     hw)));
+  HETB_LAUNCH_OK();
+  const int use_smem = (num_rels * H <= kMaxSmemMuPlan) ? 1 : 0;
+  const size_t smem = use_smem ? (size_t)num_rels * H * sizeof(float) : 0;
+  PLAN_LPR(lpr, (plan_hgt_bwd_walk_kernel<T, L><<<grid_for(pl->num_items, groups), kPThreads, smem, st>>>(
+                    pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_c,
+                    pl->idx_b, pl->idx_d, pl->row_rel, (int)num_rels, left, kv, msg, mu, attn, lse, gdoto, gout,
+                    grad_left, grad_kv, grad_msg, grad_mu, H, hw, use_smem)));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+// grad_left and grad_mu must arrive zero-filled (every edge reduces into them); grad_kv and
+// grad_msg need no initialisation (every row is stored, split / empty rows are zeroed here).
+extern "C" int hetb_hgt_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_rels, int64_t num_dst,
+                                       const void *left, const void *kv, const void *msg, int table_dtype,
+                                       const float *mu, const float *attn, const float *lse, const float *out,
+                                       const float *gout, float *gdoto_scratch, float *grad_left, float *grad_kv,
+                                       float *grad_msg, float *grad_mu, int H, int F, void *stream) {
+  HETB_CHECK_ARG(plan && plan->num_items >= 0 && num_rels >= 0 && num_dst >= 0);
+  HETB_CHECK_ARG((plan->num_fix_rows == 0 || (plan->fix_rows && grad_kv)) &&
+                 (plan->num_fix_runs == 0 || (plan->fix_runs && grad_msg)));
+  HETB_CHECK_ARG(plan->num_items == 0 ||
+                 (plan->item_ptr && plan->item_row && plan->nz_rows && plan->nz_ptr && plan->idx_a && plan->idx_b &&
+                  plan->idx_c && plan->idx_d && plan->row_rel && left && kv && msg && mu && attn && lse && out &&
+                  gout && gdoto_scratch && grad_left && grad_kv && grad_msg && grad_mu && num_dst > 0));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (table_dtype == HETB_DTYPE_F32)
+    return hgt_bwd_plan_launch<float>(plan, num_rels, num_dst, (const float *)left, (const float *)kv,
+                                      (const float *)msg, mu, attn, lse, out, gout, gdoto_scratch, grad_left,
+                                      grad_kv, grad_msg, grad_mu, H, F, st);
+  if (table_dtype == HETB_DTYPE_BF16)
+    return hgt_bwd_plan_launch<__nv_bfloat16>(plan, num_rels, num_dst, (const __nv_bfloat16 *)left,
+                                              (const __nv_bfloat16 *)kv, (const __nv_bfloat16 *)msg, mu, attn, lse,
+                                              out, gout, gdoto_scratch, grad_left, grad_kv, grad_msg, grad_mu, H, F,
+                                              st);
+  return HETB_EUNSUPPORTED;
+}
+
+template <typename T>
+static int rgat_bwd_plan_launch(const hetb_walk_plan *pl, int64_t num_dst, const T *feat, const float *el,
+                                const float *er, const float *lse, const float *ret, const float *gout,
+                                float *gdotr, float *grad_feat, float *grad_el, float *grad_er, int H, int F,
+                                float slope, cudaStream_t st) {
+  const int lpr = plan_lpr(H, F);
+  if (!lpr) return HETB_EUNSUPPORTED;
+  const int groups = kPThreads / lpr;
+  const int hw = F / 4;
+  if (pl->num_fix_runs > 0) {
+    PLAN_LPR(lpr, (plan_zero_rows_kernel<L><<<grid_for(pl->num_fix_runs, groups), kPThreads, 0, st>>>(
+                      pl->fix_runs, pl->num_fix_runs, grad_feat, grad_el, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  if (pl->num_items == 0) return HETB_OK;
+  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, ret, num_dst, gdotr, H,
+                                                                                     hw)));
+  HETB_LAUNCH_OK();
+  PLAN_LPR(lpr, (plan_rgat_bwd_walk_kernel<T, L><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
+                    pl->item_ptr, pl->num_items, pl->idx_a, pl->idx_c, pl->idx_b, pl->row_rel, feat, el, er, lse,
+                    gdotr, gout, grad_feat, grad_el, grad_er, H, hw, slope)));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+// grad_er must arrive zero-filled; grad_feat / grad_el need no initialisation.
+extern "C" int hetb_rgat_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_dst, const void *feat,
+                                        int table_dtype, const float *el, const float *er, const float *lse,
+                                        const float *ret, const float *gout, float *gdotr_scratch,
+                                        float *grad_feat, float *grad_el, float *grad_er, int H, int F, float slope,
+                                        void *stream) {
+  HETB_CHECK_ARG(plan && plan->num_items >= 0 && num_dst >= 0);
+  HETB_CHECK_ARG(plan->num_fix_runs == 0 || (plan->fix_runs && grad_feat && grad_el));
+  HETB_CHECK_ARG(plan->num_items == 0 ||
+                 (plan->item_ptr && plan->idx_a && plan->idx_b && plan->idx_c && plan->row_rel && feat && el && er &&
+                  lse && ret && gout && gdotr_scratch && grad_feat && grad_el && grad_er && num_dst > 0));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (table_dtype == HETB_DTYPE_F32)
+    return rgat_bwd_plan_launch<float>(plan, num_dst, (const float *)feat, el, er, lse, ret, gout, gdotr_scratch,
+                                       grad_feat, grad_el, grad_er, H, F, slope, st);
+  if (table_dtype == HETB_DTYPE_BF16)
+    return rgat_bwd_plan_launch<__nv_bfloat16>(plan, num_dst, (const __nv_bfloat16 *)feat, el, er, lse, ret, gout,
+                                               gdotr_scratch, grad_feat, grad_el, grad_er, H, F, slope, st);
+  return HETB_EUNSUPPORTED;
+}

@@ -802,6 +802,135 @@ void hetb200_backward_hgt_fused_attention_aggregation_csr(
            op);
 }
 
+// ------------------------------------------------- plan-based fused edge passes ---
+// A walk plan travels as ONE int32 device tensor plus a host list of integers
+// (het_b200/graph.py: WalkPlan.blob / .meta): counts first, then the element offset of every array
+// inside the blob (-1 = absent), in the order of hetb_walk_plan's fields.
+constexpr int kPlanMetaLen = 21;
+
+hetb_walk_plan unpack_plan(const Tensor &blob, c10::IntArrayRef meta, const char *op) {
+  TORCH_CHECK(blob.is_cuda() && blob.scalar_type() == at::kInt && blob.is_contiguous(), "torch_hrt::", op,
+              ": the plan blob must be a contiguous int32 CUDA tensor");
+  TORCH_CHECK((int)meta.size() == kPlanMetaLen, "torch_hrt::", op, ": plan meta must hold ", kPlanMetaLen, " integers");
+  const int32_t *base = blob.data_ptr<int32_t>();
+  const int64_t n = blob.numel();
+  auto at_off = [&](int i) -> const int32_t * {
+    const int64_t o = meta[i];
+    TORCH_CHECK(o >= -1 && o < n, "torch_hrt::", op, ": plan offset out of range");
+    return o < 0 ? nullptr : base + o;
+  };
+  hetb_walk_plan pl;
+  pl.num_positions = meta[0];
+  pl.num_items = (int32_t)meta[1];
+  pl.num_nz_rows = (int32_t)meta[2];
+  pl.num_fix_rows = (int32_t)meta[3];
+  pl.num_empty_rows = (int32_t)meta[4];
+  pl.num_pslots = (int32_t)meta[5];
+  pl.num_fix_runs = (int32_t)meta[6];
+  pl.item_ptr = at_off(7);
+  pl.item_row = at_off(8);
+  pl.nz_rows = at_off(9);
+  pl.nz_ptr = at_off(10);
+  pl.fix_rows = at_off(11);
+  pl.empty_rows = at_off(12);
+  pl.pslot = at_off(13);
+  pl.pslot_row = at_off(14);
+  pl.fix_runs = at_off(15);
+  pl.idx_a = at_off(16);
+  pl.idx_b = at_off(17);
+  pl.idx_c = at_off(18);
+  pl.idx_d = at_off(19);
+  pl.row_rel = at_off(20);
+  return pl;
+}
+
+// fp32 or bf16 storage of a gathered table; returns the dtype tag of the C ABI
+int table_dtype(const Tensor &t, const char *op, const char *name) {
+  TORCH_CHECK(t.is_cuda() && t.is_contiguous(), "torch_hrt::", op, ": `", name, "` must be a contiguous CUDA tensor");
+  if (t.scalar_type() == at::kFloat) return HETB_DTYPE_F32;
+  if (t.scalar_type() == at::kBFloat16) return HETB_DTYPE_BF16;
+  TORCH_CHECK(false, "torch_hrt::", op, ": `", name, "` must be float32 or bfloat16");
+  return -1;
+}
+
+void hetb200_hgt_fused_fwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &left_compact, Tensor &k,
+                                Tensor &messages_compact, Tensor &mu, Tensor &attn, Tensor &lse, Tensor &ret,
+                                Tensor &part_m, Tensor &part_s, Tensor &part_acc, Tensor &ssum) {
+  const char *op = "hetb200_hgt_fused_fwd_plan";
+  const hetb_walk_plan pl = unpack_plan(plan, meta, op);
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(ret) / H);
+  const int dt = table_dtype(left_compact, op, "left_compact");
+  TORCH_CHECK(table_dtype(k, op, "k") == dt && table_dtype(messages_compact, op, "messages_compact") == dt,
+              "torch_hrt::", op, ": left_compact, k and messages_compact must share one dtype");
+  TORCH_CHECK(attn.numel() == pl.num_positions * H && part_m.numel() >= 2 * (int64_t)pl.num_items * H &&
+                  part_acc.numel() >= 2 * (int64_t)pl.num_items * H * F,
+              "torch_hrt::", op, ": attn / scratch sizes do not match the plan");
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_hgt_fused_fwd_plan(&pl, left_compact.data_ptr(), k.data_ptr(), messages_compact.data_ptr(), dt,
+                                   f32(mu, op, "mu"), f32w(attn, op, "attn"), f32w(lse, op, "lse"),
+                                   f32w(ret, op, "ret"), f32w(part_m, op, "part_m"), f32w(part_s, op, "part_s"),
+                                   f32w(part_acc, op, "part_acc"), f32w(ssum, op, "ssum"), H, F, stream_of(ret)),
+           op);
+}
+
+void hetb200_hgt_fused_bwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &left_compact, Tensor &k,
+                                Tensor &messages_compact, Tensor &mu, Tensor &attn, Tensor &lse, Tensor &out,
+                                Tensor &gradout, Tensor &gdoto_scratch, Tensor &grad_left, Tensor &grad_k,
+                                Tensor &grad_message_compact, Tensor &grad_mu) {
+  const char *op = "hetb200_hgt_fused_bwd_plan";
+  const hetb_walk_plan pl = unpack_plan(plan, meta, op);
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(out) / H);
+  const int dt = table_dtype(left_compact, op, "left_compact");
+  TORCH_CHECK(table_dtype(k, op, "k") == dt && table_dtype(messages_compact, op, "messages_compact") == dt,
+              "torch_hrt::", op, ": left_compact, k and messages_compact must share one dtype");
+  TORCH_CHECK(gdoto_scratch.numel() >= out.size(0) * H, "torch_hrt::", op, ": gdoto_scratch too small");
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_fused_bwd_plan(&pl, mu.size(0), out.size(0), left_compact.data_ptr(), k.data_ptr(),
+                                   messages_compact.data_ptr(), dt, f32(mu, op, "mu"), f32(attn, op, "attn"),
+                                   f32(lse, op, "lse"), f32(out, op, "out"), f32(gradout, op, "gradout"),
+                                   f32w(gdoto_scratch, op, "gdoto_scratch"), f32w(grad_left, op, "grad_left"),
+                                   f32w(grad_k, op, "grad_k"), f32w(grad_message_compact, op, "grad_message_compact"),
+                                   f32w(grad_mu, op, "grad_mu"), H, F, stream_of(gradout)),
+           op);
+}
+
+void hetb200_rgat_fused_fwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &feat_compact, Tensor &el, Tensor &er,
+                                 double slope, Tensor &lse, Tensor &ret, Tensor &part_m, Tensor &part_s,
+                                 Tensor &part_acc, Tensor &ssum) {
+  const char *op = "hetb200_rgat_fused_fwd_plan";
+  const hetb_walk_plan pl = unpack_plan(plan, meta, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(ret) / H);
+  TORCH_CHECK(part_m.numel() >= 2 * (int64_t)pl.num_items * H && part_acc.numel() >= 2 * (int64_t)pl.num_items * H * F,
+              "torch_hrt::", op, ": scratch sizes do not match the plan");
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_rgat_fused_fwd_plan(&pl, feat_compact.data_ptr(), table_dtype(feat_compact, op, "feat_compact"),
+                                    f32(el, op, "el"), f32(er, op, "er"), (float)slope, f32w(lse, op, "lse"),
+                                    f32w(ret, op, "ret"), f32w(part_m, op, "part_m"), f32w(part_s, op, "part_s"),
+                                    f32w(part_acc, op, "part_acc"), f32w(ssum, op, "ssum"), H, F, stream_of(ret)),
+           op);
+}
+
+void hetb200_rgat_fused_bwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &feat_compact, Tensor &el, Tensor &er,
+                                 Tensor &lse, Tensor &ret, Tensor &gradout, Tensor &gdotr_scratch, Tensor &grad_feat,
+                                 Tensor &grad_el, Tensor &grad_er, double slope) {
+  const char *op = "hetb200_rgat_fused_bwd_plan";
+  const hetb_walk_plan pl = unpack_plan(plan, meta, op);
+  const int H = (int)xlen(el);
+  const int F = (int)(xlen(ret) / H);
+  TORCH_CHECK(gdotr_scratch.numel() >= ret.size(0) * H, "torch_hrt::", op, ": gdotr_scratch too small");
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_rgat_fused_bwd_plan(&pl, ret.size(0), feat_compact.data_ptr(),
+                                    table_dtype(feat_compact, op, "feat_compact"), f32(el, op, "el"),
+                                    f32(er, op, "er"), f32(lse, op, "lse"), f32(ret, op, "ret"),
+                                    f32(gradout, op, "gradout"), f32w(gdotr_scratch, op, "gdotr_scratch"),
+                                    f32w(grad_feat, op, "grad_feat"), f32w(grad_el, op, "grad_el"),
+                                    f32w(grad_er, op, "grad_er"), H, F, (float)slope, stream_of(gradout)),
+           op);
+}
+
 // ---------------------------------------------------------------- loss ---
 // hetb200 extension: fused log_softmax + nll_loss (sum / denom) of the training step.
 void hetb200_softmax_cross_entropy(Tensor &logits, Tensor &labels, double denom, Tensor &lse, Tensor &loss) {
@@ -1028,6 +1157,10 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
   m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
         hetb200_backward_hgt_fused_attention_aggregation_csr);
+  m.def("hetb200_hgt_fused_fwd_plan", hetb200_hgt_fused_fwd_plan);
+  m.def("hetb200_hgt_fused_bwd_plan", hetb200_hgt_fused_bwd_plan);
+  m.def("hetb200_rgat_fused_fwd_plan", hetb200_rgat_fused_fwd_plan);
+  m.def("hetb200_rgat_fused_bwd_plan", hetb200_rgat_fused_bwd_plan);
   m.def("hetb200_column_sum", hetb200_column_sum);
   m.def("hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate",
         hetb200_backward_rgnn_relational_matmul_no_scatter_gather_list_accumulate);

@@ -145,6 +145,53 @@ class HetGraph:
             self._unique_single_sided = out
         return self._unique_single_sided
 
+    def get_edge_plan(self):
+        """Walk plans of the plan-based fused edge passes (het_b200/plan.py; csrc/edge_plan.cu):
+        ``fwd`` walks the positions sorted by (destination, relation, edge id), ``bwd`` by (source,
+        relation, edge id). Both orders are stable sorts of the relation-sorted separate COO (whose
+        position is the canonical edge id) by one endpoint, done with the library's radix sort; the
+        compact (relation, node) row of every position rides along as a payload."""
+        if getattr(self, "_edge_plan", None) is None:
+            from . import plan as P
+            u = self.get_separate_unique_node_indices_single_sided()
+            coo = self.separate_coo
+            dev = coo["rel_ptrs"].device
+            E = self.num_edges
+            assert max(E, self.num_nodes, self.num_src_nodes) < (1 << 31) - 1, "plan indices are int32"
+            eid = coo["eids"]
+            rels = torch.arange(self.num_rels, device=dev)
+            ucol_rel = torch.repeat_interleave(rels, u["rel_ptrs_col"][1:] - u["rel_ptrs_col"][:-1])
+            urow_rel = torch.repeat_interleave(rels, u["rel_ptrs_row"][1:] - u["rel_ptrs_row"][:-1])
+            f_src, f_urow, f_ucol, f_eid, f_ptr = K.hetb200_stable_sort_by_key(
+                coo["col_indices"], self.num_nodes, [coo["row_indices"], u["inverse_idx_row"], u["inverse_idx_col"], eid])
+            dst_sorted = torch.repeat_interleave(torch.arange(self.num_nodes, device=dev), f_ptr[1:] - f_ptr[:-1])
+            fwd_pos = torch.empty_like(eid)
+            fwd_pos[f_eid] = torch.arange(E, device=dev)
+            fwd = P.pack(P.forward_arrays(dst_sorted, self.num_nodes, f_src, f_urow, f_ucol, ucol_rel), dev)
+            b_dst, b_urow, b_ucol, b_eid, b_ptr = K.hetb200_stable_sort_by_key(
+                coo["row_indices"], self.num_src_nodes, [coo["col_indices"], u["inverse_idx_row"], u["inverse_idx_col"], eid])
+            src_sorted = torch.repeat_interleave(torch.arange(self.num_src_nodes, device=dev), b_ptr[1:] - b_ptr[:-1])
+            bwd = P.pack(P.backward_arrays(src_sorted, self.num_src_nodes, b_dst, b_urow, b_ucol, fwd_pos[b_eid],
+                                           urow_rel), dev)
+            self._edge_plan = {"fwd": fwd, "bwd": bwd, "fwd_eids": f_eid, "scratch": {}}
+        return self._edge_plan
+
+    def plan_scratch(self, H, D):
+        """Persistent scratch of the forward walks (partial slots of split rows, their sums) and the
+        backward pre-pass, shared by every layer / call on this graph (stream-ordered reuse)."""
+        pl = self.get_edge_plan()
+        key = (int(H), int(D))
+        if key not in pl["scratch"]:
+            dev = self.separate_coo["rel_ptrs"].device
+            G = max(1, pl["fwd"].num_items)
+            f32 = dict(dtype=torch.float32, device=dev)
+            pl["scratch"][key] = {
+                "part_m": torch.empty(2 * G * H, **f32), "part_s": torch.empty(2 * G * H, **f32),
+                "part_acc": torch.empty(2 * G * D, **f32), "ssum": torch.empty(self.num_nodes * H, **f32),
+                "gdot": torch.empty(self.num_nodes * H, **f32),
+            }
+        return pl["scratch"][key]
+
     def get_num_nodes(self):
         return self.num_nodes
 

@@ -117,13 +117,13 @@ class HET_RGATLayer(nn.Module):
                 feat_compact_dst.view(feat_compact_dst.size(0), -1))
         if self.linear_reorder_flag:
             # el row-dot + edge pass as one autograd node (one grad_feat buffer)
-            return B.relational_fused_gat_csr_compact_with_logits(
-                g, feat_compact, er_compact.view(-1, self.num_heads, 1), self.attn_l, self.leaky_relu_slope)
+            fn = B.relational_fused_gat_plan_with_logits if B.USE_EDGE_PLAN else B.relational_fused_gat_csr_compact_with_logits
+            return fn(g, feat_compact, er_compact.view(-1, self.num_heads, 1), self.attn_l, self.leaky_relu_slope)
         el_compact = B.rgnn_relational_matmul_no_scatter_gather_list(
             u["rel_ptrs_row"], self.attn_l.unsqueeze(-1), feat_compact.view(feat_compact.size(0), -1))
-        return B.relational_fused_gat_csr_compact(
-            g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
-            self.leaky_relu_slope)
+        fn = B.relational_fused_gat_plan if B.USE_EDGE_PLAN else B.relational_fused_gat_csr_compact
+        return fn(g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
+                  self.leaky_relu_slope)
 
     def _epilogue(self, h, inputs_dst):
         h = h.view(-1, self.out_feat)
@@ -342,8 +342,9 @@ class HET_HGTLayerHetero(nn.Module):
                 attn_weight_dst_product_compact = attn_weight_dst_product_compact.view(-1, self.num_heads, self.d_k)
                 message_compact = message_compact.view(-1, self.num_heads, self.d_k)
             if self.fused_attention_aggregation_flag:
-                new_h = B.hgt_fused_attention_and_aggregation_csr_compact(
-                    G, attn_weight_dst_product_compact, k, message_compact, self.relation_pri / self.sqrt_dk)
+                fn = (B.hgt_fused_attention_and_aggregation_plan if B.USE_EDGE_PLAN
+                      else B.hgt_fused_attention_and_aggregation_csr_compact)
+                new_h = fn(G, attn_weight_dst_product_compact, k, message_compact, self.relation_pri / self.sqrt_dk)
             else:
                 attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k, 2, "_col")
                 new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(

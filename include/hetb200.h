@@ -335,6 +335,78 @@ int hetb_stable_sort_by_key(const int64_t *key, int64_t num_edges,
 int hetb_expand_row_ptr(const int64_t *row_ptr, int64_t num_rows,
                         int64_t num_edges, int64_t *row_idx, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Walk plans and the plan-based fused edge passes (SURVEY.md §8(b) "hetb_graph_plan": the
+ * per-graph work decomposition and int32-narrowed index copies; §8(d) "i = 4")
+ * ---------------------------------------------------------------------- */
+
+#define HETB_DTYPE_F32 0
+#define HETB_DTYPE_BF16 1 /* storage type of the gathered tables; arithmetic and gradients stay fp32 */
+
+/* One walk over E positions. Built once per graph by the host (het_b200/graph.py:
+ * HetGraph.get_edge_plan, from the relation-sorted COO the reference's converters produce:
+ * MyHyb/MyHyb.h:1099-1150 + python/utils/coo_sorters.py:156-170, and the compact-as-of-node lists
+ * of python/utils_lite/mydgl_graph_methods.py:11-157). All arrays int32, device resident.
+ *   Forward plans walk positions sorted by (destination, relation): rows = destinations.
+ *     idx_a = source node, idx_b = compact (relation, source) row, idx_c = compact (relation,
+ *     destination) row of the position; row_rel[c] = relation of compact (relation, destination) row c.
+ *   Backward plans walk positions sorted by (source, relation): rows = sources, runs = compact
+ *     (relation, source) rows. idx_a = destination node, idx_b = compact (relation, source) row,
+ *     idx_c = compact (relation, destination) row, idx_d = forward position of the same edge;
+ *     row_rel[u] = relation of compact (relation, source) row u, bit 31 set when the run is split
+ *     across items (listed in fix_runs).
+ * Work items are [item_ptr[g], item_ptr[g+1]); item_row[g] indexes nz_rows / nz_ptr (the rows that
+ * have positions: nz_rows[j] = row id, bit 31 set when the row is split across items;
+ * nz_ptr[j] = first position). fix_rows: rows the pass accumulates into by reduction (pre-zeroed;
+ * a forward pass also merges and normalises them); a backward plan lists empty rows there too.
+ * empty_rows (forward): rows without positions (zero-filled). pslot / pslot_row (forward): the
+ * valid partial slots (2*item + {0: head row, 1: tail row}) of split rows and the row of each. */
+typedef struct hetb_walk_plan {
+  int64_t num_positions;
+  int32_t num_items, num_nz_rows, num_fix_rows, num_empty_rows, num_pslots, num_fix_runs;
+  const int32_t *item_ptr, *item_row, *nz_rows, *nz_ptr;
+  const int32_t *fix_rows, *empty_rows, *pslot, *pslot_row, *fix_runs;
+  const int32_t *idx_a, *idx_b, *idx_c, *idx_d, *row_rel;
+} hetb_walk_plan;
+
+/* HGT attention score + edge softmax (max-subtracted, online) + message aggregation in one walk:
+ * a5 + a10 + a11 of SURVEY.md §8(a) (rgnn_inner_product_right_node_separatecoo:
+ * OpExport/RGNNOps.inc.h:609-658; hgt_full_graph_edge_softmax_ops_csr: OpExport/HGTOps.inc.h:190-203;
+ * hgt_full_graph_message_mean_aggregation_csr: :180-188) on compact inputs (kind 2 direct indexing,
+ * kernel_enums.h:6-119).  left [Uc,H,F] compact (relation, destination) rows (W_att·q), kv [Nsrc,H,F]
+ * (k), msg [Ur,H,F] compact (relation, source) rows, mu [R,H].  Writes attn [E,H] (the raw score, in
+ * FORWARD-PLAN POSITION order), lse [N,H] (log-sum-exp of mu·attn per destination and head; replaces
+ * the reference's per-edge exp and per-node sum), ret [N,H,F].  Scratch: part_m / part_s
+ * [2*num_items,H], part_acc [2*num_items,H*F], ssum [N,H]. */
+int hetb_hgt_fused_fwd_plan(const hetb_walk_plan *plan, const void *left, const void *kv, const void *msg,
+                            int table_dtype, const float *mu, float *attn, float *lse, float *ret, float *part_m,
+                            float *part_s, float *part_acc, float *ssum, int H, int F, void *stream);
+
+/* Backward of the above in one walk (a6 + a12: backward_inner_product_right_node_separatecoo
+ * OpExport/RGNNOps.inc.h:1131-1181; backward_hgt_full_graph_{message_mean_aggregation,edge_softmax_ops}_csr
+ * OpExport/HGTOps.inc.h:477-487, 553-566). grad_left [Uc,H,F] and grad_mu [R,H] must arrive
+ * zero-filled; grad_kv [Nsrc,H,F] and grad_msg [Ur,H,F] are fully written. gdoto_scratch [N,H]. */
+int hetb_hgt_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_rels, int64_t num_dst, const void *left,
+                            const void *kv, const void *msg, int table_dtype, const float *mu, const float *attn,
+                            const float *lse, const float *out, const float *gout, float *gdoto_scratch,
+                            float *grad_left, float *grad_kv, float *grad_msg, float *grad_mu, int H, int F,
+                            void *stream);
+
+/* RGAT logits + edge softmax (max-subtracted, online) + aggregation in one walk: a7
+ * (relational_fused_gat_csr, OpExport/RGATOps.inc.h:251-277) on compact inputs: feat [Ur,H,F], el [Ur,H]
+ * compact (relation, source) rows, er [Uc,H] compact (relation, destination) rows. Writes lse [N,H],
+ * ret [N,H,F]; nothing per edge (the reference's exp [E,H] is recomputed by the backward). */
+int hetb_rgat_fused_fwd_plan(const hetb_walk_plan *plan, const void *feat, int table_dtype, const float *el,
+                             const float *er, float slope, float *lse, float *ret, float *part_m, float *part_s,
+                             float *part_acc, float *ssum, int H, int F, void *stream);
+
+/* Backward of the above (a9: backward_relational_fused_gat_csr, OpExport/RGATOps.inc.h:430-461).
+ * grad_er [Uc,H] must arrive zero-filled; grad_feat / grad_el are fully written. gdotr_scratch [N,H]. */
+int hetb_rgat_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_dst, const void *feat, int table_dtype,
+                             const float *el, const float *er, const float *lse, const float *ret,
+                             const float *gout, float *gdotr_scratch, float *grad_feat, float *grad_el,
+                             float *grad_er, int H, int F, float slope, void *stream);
+
 /* out[c] = sum_i x[i, c] for a row-major [num_rows, num_cols] matrix: the gradient of the layer
  * bias (h + b; hrt/python/RGAT/models.py:264-278, RGCN/RGCN.py:343-344). num_cols % 4 == 0. */
 int hetb_column_sum(const float *x, int64_t num_rows, int num_cols, float *out, void *stream);

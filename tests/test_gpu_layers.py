@@ -213,3 +213,50 @@ def test_hgt_fused_on_padded_shard_sources(cuda):
         outs.append([out.detach(), x.grad] + [p.grad for p in model.parameters()])
     for a, b in zip(*outs):
         close(a, b.double().cpu(), "fused vs op-by-op on a padded shard", **WGRAD_TOL)
+
+
+@pytest.mark.parametrize("kind,shape,scale,heads,layers", [
+    ("rgat", "bgs", 1.0, 1, 1),          # BASELINE configs[1] at FULL size
+    ("hgt", "mag", 1.0 / 16, 4, 2),      # configs[2] (and [4]'s graph) at 1/16: E = 1.3 M
+    ("rgat", "wikikg2", 1.0 / 16, 1, 1),  # configs[3] at 1/16: 535 Zipf(1.2) relations, most of them tiny
+])
+def test_baseline_configs_default_path(cuda, kind, shape, scale, heads, layers):
+    """The bench's default path (compact-as-of-node + linear operator reordering + plan-based fused
+    edge passes) on the BASELINE.json graphs themselves, against the fp64 layer oracle on the host:
+    output, input gradient and every parameter gradient."""
+    from het_b200.models import HET_HGT_DGLHetero, HET_RGATModel
+    coo, g = _graph(cuda, shape, scale)
+    src, dst, et = _coo_t(coo)
+    torch.manual_seed(3)
+    if kind == "rgat":
+        model = HET_RGATModel(coo.num_rels, 64, 64, 64, heads, layers, compact_as_of_node_flag=True,
+                              linear_reorder_flag=True).to(cuda)
+    else:
+        model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, 64, 64, heads, num_layers=layers,
+                                  compact_as_of_node_flag=True, fused_attention_aggregation_flag=True,
+                                  linear_reorder_flag=True).to(cuda)
+    unit_gain_init(model, seed=5)
+    x = (torch.rand(coo.num_nodes, 64, device=cuda) * 2 - 1).requires_grad_(True)
+    out = model(g, x)
+    gout = torch.randn_like(out)
+    out.backward(gout)
+    x64 = x.detach().double().cpu().requires_grad_(True)
+    h, ps = x64, []
+    offs = torch.from_numpy(coo.node_type_offsets)
+    for i, layer in enumerate(model.layers):
+        p = {k: v.detach().double().cpu().requires_grad_(True) for k, v in layer.named_parameters()}
+        ps.append(p)
+        if kind == "rgat":
+            h = M.rgat_layer(src, dst, et, h, p["conv_weights"], p["attn_l"], p["attn_r"], 0.2, p["h_bias"])
+            if i + 1 < len(model.layers):
+                h = torch.relu(h)
+        else:
+            h = M.hgt_layer(src, dst, et, offs, h, p["k_linears"], p["q_linears"], p["v_linears"], p["a_linears"],
+                            p["relation_pri"], p["relation_att"], p["relation_msg"], p["skip"])
+    h.backward(gout.double().cpu())
+    assert float(h.abs().max()) > 0.05
+    close(out, h, f"{kind} {shape} out")
+    close(x.grad, x64.grad, f"{kind} {shape} grad x", **GRAD_TOL)
+    for layer, p in zip(model.layers, ps):
+        for k, v in layer.named_parameters():
+            close(v.grad, p[k].grad, f"{kind} {shape} grad {k}", **WGRAD_TOL)
