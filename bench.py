@@ -305,6 +305,7 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
     read by the edge kernels through the direct-indexing maps. Compulsory bytes count every
     compact / node row once (unique-row granularity), every per-edge scalar and index once."""
     import torch
+    from het_b200 import backend as B
     from het_b200.kernels import K
     g, dev = trainer.g, trainer.device
     E, N, Ns, R = g.num_edges, g.num_nodes, g.num_src_nodes, g.num_rels
@@ -361,14 +362,32 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
             uniq_src * D * 4 + Ur * D * 4 + R * D * D * 4 + Ur * 8, "X_unique*D*s + U*D*s + R*D*D*s + U*i")
         el, er = torch.randn(Ur, H, 1, device=dev), torch.randn(Uc, H, 1, device=dev)
         ssum, ex, ret = torch.empty(N, H, device=dev), torch.empty(E, H, 1, device=dev), torch.empty(N, H, F, device=dev)
-        leg("rgat_edge_softmax_aggregate_fwd(in-CSR, compact)",
+        if B.USE_EDGE_PLAN:
+            pl, sc = g.get_edge_plan(), g.plan_scratch(H, D)
+            el2, er2, lse = el.view(Ur, H).contiguous(), er.view(Uc, H).contiguous(), torch.empty(N, H, device=dev)
+            leg("rgat_fused_fwd(plan walk: logits + online softmax + aggregate)",
+                lambda: K.hetb200_rgat_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, feat, el2, er2, 0.2, lse, ret,
+                                                      sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"]),
+                Ur * D * 4 + (Ur + Uc) * H * 4 + 2 * E * 4 + pl["fwd"].blob.numel() * 4 - 3 * E * 4 + N * H * 4 + N * D * 4,
+                "feat_c + el_c,er_c + int32 (urow,ucol) per position + items/rows ; lse + ret (nothing per edge)")
+            gout = torch.randn(N, H, F, device=dev)
+            gf, gel, ger = torch.empty_like(feat), torch.empty_like(el2), torch.zeros_like(er2)
+            leg("rgat_fused_bwd(plan walk over compact source rows)",
+                lambda: K.hetb200_rgat_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, feat, el2, er2, lse, ret, gout,
+                                                      sc["gdot"], gf, gel, ger, 0.2),
+                2 * Ur * D * 4 + 2 * (Ur + Uc) * H * 4 + 3 * N * H * 4 + 2 * N * D * 4 + 3 * E * 4
+                + (pl["bwd"].blob.numel() * 4 - 4 * E * 4),
+                "feat_c,el_c,er_c,lse,gdotr,ret,gout + int32 (dst,urow,ucol) per position ; grad_feat_c,grad_el_c,grad_er_c")
+            gf = gf.view(Ur, H, F)
+        else:
+          leg("rgat_edge_softmax_aggregate_fwd(in-CSR, compact)",
             lambda: K.hetb200_relational_fused_gat_csr_compact(ic["row_ptrs"], ic["eids"], iir, iic, feat, el, er, ssum, ex,
                                                                ret, 0.2),
             Ur * D * 4 + (Ur + Uc) * H * 4 + 3 * E * 8 + (N + 1) * 8 + E * H * 4 + N * H * 4 + N * D * 4,
             "feat_c + el_c,er_c + eid,inv_row,inv_col + row_ptr ; exp + sum + ret")
-        gout = torch.randn(N, H, F, device=dev)
-        gf, gel, ger = torch.zeros_like(feat), torch.zeros_like(el), torch.zeros_like(er)
-        leg("rgat_edge_bwd(compact-row walker)",
+          gout = torch.randn(N, H, F, device=dev)
+          gf, gel, ger = torch.zeros_like(feat), torch.zeros_like(el), torch.zeros_like(er)
+          leg("rgat_edge_bwd(compact-row walker)",
             lambda: K.hetb200_backward_relational_fused_gat_compact_rows(
                 u["urow_ptrs"], u["urow_dst"], u["urow_eids"], u["urow_inverse_idx_col"], feat, el, er, ssum, ex, ret,
                 gout, gf, gel, ger, 0.2),
@@ -390,7 +409,25 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
         new_h = torch.empty(N, H, F, device=dev)
         gout = torch.randn(N, H, F, device=dev)
         ssum = torch.empty(N, H, device=dev)
-        if getattr(layer, "fused_attention_aggregation_flag", False):
+        if getattr(layer, "fused_attention_aggregation_flag", False) and B.USE_EDGE_PLAN:
+            pl, sc = g.get_edge_plan(), g.plan_scratch(H, D)
+            attn, lse = torch.empty(E, H, device=dev), torch.empty(N, H, device=dev)
+            fixed_f = pl["fwd"].blob.numel() * 4 - 3 * E * 4   # items, rows, lists: everything but the 3 per-position arrays
+            leg("hgt_fused_fwd(plan walk: score + online softmax + aggregate)",
+                lambda: K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, wq, k, msg, mu, attn, lse, new_h,
+                                                     sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"]),
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 3 * E * 4 + fixed_f + E * H * 4 + N * H * 4 + N * D * 4,
+                "left_c + k_unique + msg_c + int32 (src,urow,ucol) per position + items/rows ; score + lse + out")
+            gl, gk, gm, gmu = torch.zeros_like(wq), torch.empty_like(k), torch.empty_like(msg), torch.zeros(R, H, device=dev)
+            fixed_b = pl["bwd"].blob.numel() * 4 - 4 * E * 4
+            leg("hgt_fused_bwd(plan walk over (source, relation) runs)",
+                lambda: K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, wq, k, msg, mu, attn, lse, new_h, gout,
+                                                     sc["gdot"], gl, gk, gm, gmu),
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 4 * E * 4 + fixed_b + E * H * 4 + 2 * N * H * 4 + 2 * N * D * 4
+                + Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4,
+                "left_c,k,msg_c + int32 (dst,urow,ucol,fwd pos) per position + score,lse,gdoto,out,gout ; "
+                "grad_left_c + grad_k + grad_msg_c")
+        elif getattr(layer, "fused_attention_aggregation_flag", False):
             attn, t = torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
             leg("hgt_fused_score_softmax_aggregate_fwd(in-CSR, compact)",
                 lambda: K.hetb200_hgt_fused_attention_aggregation_csr(
