@@ -663,8 +663,9 @@ def main():
         "config": {
             "workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s) fwd+loss+bwd+Adam, hidden 64, "
                         f"{heads} head(s), {coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
-            "parallelism": "single GPU" if world == 1 else f"destination-range shards x{world}, NCCL all-gather of "
-                           "source rows per layer, reduce-scatter in backward, all-reduce of weight grads",
+            "parallelism": "single GPU" if world == 1 else f"destination shards x{world} (rank p owns slice p of every node "
+                           "type's id range), one NCCL all-gather of the layer input per layer, reduce-scatter in "
+                           "backward, all-reduce of weight grads",
             "cuda_graph": use_graph, "compact_as_of_node": bool(args.compact), "fused_edge_pass": bool(args.fused and args.compact),
             "l2": "inputs larger than L2: per-edge tensors of one step total "
                   f"{coo.num_edges // world * 64 * 4 * 6 / 1e6:.0f} MB per GPU vs 126 MB L2 (no flush between steps)",

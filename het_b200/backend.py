@@ -654,6 +654,59 @@ def hgt_reordered_projections(g, h, k_linears, w_att, w_msg):
         u["node_indices_row"], h.contiguous(), k_linears.contiguous(), w_att.contiguous(), w_msg.contiguous())
 
 
+class HGTReorderedProjectionsSharded(th.autograd.Function):
+    """HGTReorderedProjections on a destination shard (het_b200/parallel.py): ``h`` are the owned rows,
+    ``hg`` the all-gathered layer input. k = hg.W_k[type] is computed HERE for every gathered row
+    (the typed linear over the gathered layout's (rank, type) segments) instead of being gathered
+    as a second tensor: one exchange per layer instead of two, at the price of a typed linear over
+    N instead of N/P rows. msg_c reads hg through the (relation, source) lists, left_c reads the
+    local h. Backward: the k and msg_c input gradients land in ONE [Ng, D] buffer (whose
+    reduce-scatter is the exchange's backward), the left_c gradient in grad_h."""
+
+    @staticmethod
+    def forward(ctx, gathered_type_ptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att, w_msg):
+        ng, d_out = hg.size(0), k_ext.size(1) * k_ext.size(3)
+        k = th.empty((ng, d_out), dtype=hg.dtype, device=hg.device)
+        K.rgnn_relational_matmul_no_scatter_gather_list(gathered_type_ptrs, k_ext, hg, k)
+        left = th.empty((nodes_col.numel(), w_att.size(1), w_att.size(3)), dtype=h.dtype, device=h.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col,
+                                  "unique_srcs_and_dests_node_indices": nodes_col}, 1, w_att, h, left, True)
+        msg = th.empty((nodes_row.numel(), w_msg.size(1), w_msg.size(3)), dtype=h.dtype, device=h.device)
+        K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row,
+                                  "unique_srcs_and_dests_node_indices": nodes_row}, 1, w_msg, hg, msg, True)
+        ctx.save_for_backward(gathered_type_ptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att,
+                              w_msg)
+        return k, left, msg
+
+    @staticmethod
+    def backward(ctx, grad_k, grad_left, grad_msg):
+        gptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att, w_msg = ctx.saved_tensors
+        grad_hg = th.empty_like(hg, memory_format=th.contiguous_format)  # the segments cover every gathered row
+        grad_wk = th.zeros_like(k_ext, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(
+            gptrs, th.transpose(k_ext, 2, 3).contiguous(), hg, grad_k.contiguous(), grad_hg, grad_wk)
+        grad_wmsg = th.zeros_like(w_msg, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row, "unique_srcs_and_dests_node_indices": nodes_row}, 1,
+            th.transpose(w_msg, 2, 3).contiguous(), hg, grad_msg.contiguous(), grad_hg, grad_wmsg, True)
+        grad_h = th.zeros_like(h, memory_format=th.contiguous_format)
+        grad_watt = th.zeros_like(w_att, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col, "unique_srcs_and_dests_node_indices": nodes_col}, 1,
+            th.transpose(w_att, 2, 3).contiguous(), h, grad_left.contiguous(), grad_h, grad_watt, True)
+        return None, None, None, None, None, grad_h, grad_hg, grad_wk, grad_watt, grad_wmsg
+
+
+def hgt_reordered_projections_sharded(g, h, hg, k_linears, w_att, w_msg):
+    """k_linears [T, 1, in, out] -> one weight per segment of the gathered layout: per rank the T
+    types and a zero matrix for its padding rows."""
+    u = g.get_separate_unique_node_indices_single_sided()
+    k_ext = th.cat([k_linears, th.zeros_like(k_linears[:1])], 0).repeat(g.world, 1, 1, 1)
+    return HGTReorderedProjectionsSharded.apply(
+        g.gathered_type_ptrs, u["rel_ptrs_col"], u["node_indices_col"], u["rel_ptrs_row"], u["node_indices_row"],
+        h.contiguous(), hg.contiguous(), k_ext.contiguous(), w_att.contiguous(), w_msg.contiguous())
+
+
 class RelationalMatmulCompactPair(th.autograd.Function):
     """Two compact typed linears of the SAME input as one autograd node (RGAT under linear operator
     reordering: X.W_r per unique (relation, source) and X.(W_r.a_r) per unique (relation,

@@ -294,7 +294,7 @@ class HET_HGTLayerHetero(nn.Module):
         offs = G.get_original_node_type_offsets()
         reorder = (self.linear_reorder_flag and self.compact_as_of_node_flag
                    and G.get_relation_node_types() is not None)
-        combined = reorder and gather is None  # k comes out of hgt_reordered_projections below
+        combined = reorder  # k comes out of hgt_reordered_projections[_sharded] below
         k = None if combined else B.rgnn_relational_matmul_no_scatter_gather_list(
             offs, self.k_linears, h).view(-1, self.num_heads, self.d_k)
         if reorder:
@@ -313,7 +313,7 @@ class HET_HGTLayerHetero(nn.Module):
             q = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.q_linears, h).view(-1, self.num_heads, self.d_k)
             v = B.rgnn_relational_matmul_no_scatter_gather_list(offs, self.v_linears, h).view(-1, self.num_heads, self.d_k)
             w_att, w_msg = self.relation_att, self.relation_msg
-        if gather is not None:
+        if gather is not None and not reorder:
             k, v = gather(k), gather(v)
         coo = G.get_separate_coo_original()
 
@@ -330,6 +330,11 @@ class HET_HGTLayerHetero(nn.Module):
                 # k and the two compact products read the same h: one autograd node, one grad_h buffer
                 k, attn_weight_dst_product_compact, message_compact = B.hgt_reordered_projections(
                     G, h, self.k_linears, w_att, w_msg)
+                k = k.view(-1, self.num_heads, self.d_k)
+            elif reorder:
+                # destination shard: ONE exchange (the layer input); k is computed for the gathered rows here
+                k, attn_weight_dst_product_compact, message_compact = B.hgt_reordered_projections_sharded(
+                    G, h, gather(h), self.k_linears, w_att, w_msg)
                 k = k.view(-1, self.num_heads, self.d_k)
             else:
                 attn_weight_dst_product_compact = B.rgnn_relational_matmul(

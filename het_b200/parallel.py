@@ -1,23 +1,23 @@
-"""Destination-range sharding of full-graph training over the GPUs of one box.
+"""Destination sharding of full-graph training over the GPUs of one box.
 
-The reference has no distributed code at all; this is the one
-parallelism BASELINE.json's north star adds: every rank owns a contiguous range
-of destination nodes (balanced by in-edge count), all in-edges of those
-destinations, the output rows and the per-edge tensors of those edges. Weights
-are replicated. Per layer there is ONE exchange step: the rows a layer gathers by
-*source* id (RGAT: the layer input; HGT: K and V) are all-gathered over NCCL
-(NVLink 5 / NVSwitch); its backward is the matching reduce-scatter. Weight
-gradients are all-reduced once per step.
+The reference has no distributed code at all; this is the one parallelism
+BASELINE.json's north star adds. Every rank owns a contiguous destination range OF EVERY NODE TYPE
+(rank p holds slice p of each type's id range), all in-edges of those destinations, their output
+rows and the per-edge tensors of those edges. Weights are replicated. Per layer there is ONE
+exchange: the layer input ``h`` is all-gathered (``ncclAllGather`` over NVLink 5 / NVSwitch); its
+backward is the matching ``ncclReduceScatter``. Weight gradients are all-reduced once per step.
 
-Layout of the gathered matrix (``layout`` of make_shard):
-* "global" (default): the gathered matrix is the full [N, D] matrix in global node-id order; rank
-  p contributes rows [bounds[p], bounds[p+1]) through a variable-size all-gather (one coalesced
-  group of NCCL broadcasts straight into the row slices, no staging copy). Destination ranges
-  balanced by in-edges have very different node counts on a power-law graph (2.0-2.4x between the
-  largest range and the mean at 4-8 ranks), so nothing is padded and the collective moves N rows.
-* "padded": rank p's rows sit at [p*max_rows, p*max_rows+n_p), one ``all_gather_into_tensor``;
-  the shard's source indices are remapped into that layout once, at plan time. Moves
-  world*max_rows rows; kept for equal-sized ranges and as the fallback.
+Why one slice per type rather than one range of the whole id space (round 1): node types differ
+10x in in-degree, so ranges balanced by in-edges differed 2.0-2.4x in node count — the typed linears
+were unbalanced and the exchange had to be a variable-size group of broadcasts / rooted reduces.
+With a slice of every type each rank holds N/P rows (+-T) AND, because hub ids are not clustered
+inside a type, ~E/P in-edges; the exchange is a plain equal-size all-gather / reduce-scatter, the
+collectives NCCL (and NVSwitch in-network reduction) is fastest at.
+
+Layout of the gathered matrix: rank q's rows at [q*max_rows, q*max_rows + n_q), type by type
+(``max_rows`` = the largest n_q; the <= T padding rows per rank are zeros). Source ids of a shard's
+edges are remapped into that layout once, at plan time. HGT gathers only ``h`` and computes K for
+the gathered rows locally (round 1 gathered K and h: twice the bytes).
 """
 from __future__ import annotations
 
@@ -30,71 +30,85 @@ import torch.distributed as dist
 from .graphs import HeteroCOO
 
 
-def partition_destinations(dst: np.ndarray, num_nodes: int, world: int) -> np.ndarray:
-    """bounds[world+1]: contiguous destination ranges with ~equal in-edge counts
-    (every range non-empty when num_nodes >= world)."""
-    indeg = np.bincount(dst, minlength=num_nodes).astype(np.int64)
-    csum = np.concatenate([[0], np.cumsum(indeg)])
-    total = int(csum[-1])
-    bounds = np.zeros(world + 1, dtype=np.int64)
-    bounds[world] = num_nodes
-    for p in range(1, world):
-        b = int(np.searchsorted(csum, total * p / world, side="left"))
-        bounds[p] = min(max(b, bounds[p - 1] + 1), num_nodes - (world - p))
-    return bounds
+def type_slices(node_type_offsets: np.ndarray, world: int) -> np.ndarray:
+    """cuts[t, p] .. cuts[t, p+1]: the id range of type t owned by rank p ([T, world+1], int64)."""
+    offs = np.asarray(node_type_offsets, dtype=np.int64)
+    T = offs.size - 1
+    cuts = np.zeros((T, world + 1), dtype=np.int64)
+    for t in range(T):
+        n = offs[t + 1] - offs[t]
+        cuts[t] = offs[t] + (n * np.arange(world + 1, dtype=np.int64)) // world
+    return cuts
 
 
 @dataclass
 class ShardPlan:
     rank: int
     world: int
-    bounds: np.ndarray      # [world+1] destination ranges
-    max_rows: int           # rows of the largest range (the per-rank slot of the padded layout)
-    lo: int
-    hi: int
-    src: np.ndarray         # local edges: source ids in the gathered layout
-    dst: np.ndarray         # local edges: destination ids relative to lo
+    cuts: np.ndarray               # [T, world+1] per-type ownership ranges (global ids)
+    max_rows: int                  # rows of the largest shard = the per-rank slot of the gathered layout
+    owned: np.ndarray              # [n_local] global ids of the owned nodes, in local order (type by type)
+    src: np.ndarray                # local edges: source ids in the gathered layout
+    dst: np.ndarray                # local edges: destination ids in local order
     etype: np.ndarray
-    node_type_offsets: np.ndarray  # [T+1] offsets of the owned rows, relative to lo
-    layout: str = "global"
+    node_type_offsets: np.ndarray  # [T+1] type offsets of the owned rows (local ids)
+    gathered_type_ptrs: np.ndarray  # [world*(T+1)+1] segments of the gathered layout: per rank T types + padding
+    edges_per_rank: np.ndarray     # [world] in-edges of every shard (balance report)
 
     @property
     def num_local_nodes(self) -> int:
-        return self.hi - self.lo
-
-    @property
-    def sizes(self) -> list:
-        return [int(v) for v in np.diff(self.bounds)]
+        return int(self.owned.size)
 
     @property
     def num_gathered_rows(self) -> int:
-        return int(self.bounds[-1]) if self.layout == "global" else self.world * self.max_rows
+        return self.world * self.max_rows
 
     @property
     def gathered_offset(self) -> int:
         """Row of this rank's first node inside the gathered matrix."""
-        return self.lo if self.layout == "global" else self.rank * self.max_rows
+        return self.rank * self.max_rows
+
+    @property
+    def num_ntypes(self) -> int:
+        return int(self.node_type_offsets.size - 1)
 
 
-def make_shard(coo: HeteroCOO, rank: int, world: int, layout: str = None) -> ShardPlan:
-    import os
-    layout = layout or os.environ.get("HETB_GATHER_LAYOUT", "global")
-    assert layout in ("global", "padded")
-    bounds = partition_destinations(coo.dst, coo.num_nodes, world)
-    sizes = np.diff(bounds)
-    max_rows = int(sizes.max())
-    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-    mine = (coo.dst >= lo) & (coo.dst < hi)
-    src_g = coo.src[mine]
-    if layout == "padded":
-        owner = np.searchsorted(bounds, src_g, side="right") - 1
-        src_p = owner * max_rows + (src_g - bounds[owner])
-    else:
-        src_p = src_g
-    offs = np.clip(coo.node_type_offsets, lo, hi) - lo
-    return ShardPlan(rank, world, bounds, max_rows, lo, hi, src_p.astype(np.int64),
-                     (coo.dst[mine] - lo).astype(np.int64), coo.etype[mine].astype(np.int64),
-                     offs.astype(np.int64), layout)
+def gathered_ids(cuts: np.ndarray, max_rows: int, ids: np.ndarray) -> np.ndarray:
+    """global node id -> row of the gathered matrix"""
+    T, world = cuts.shape[0], cuts.shape[1] - 1
+    ids = np.asarray(ids, dtype=np.int64)
+    t = np.searchsorted(cuts[:, 0], ids, side="right") - 1                     # node type
+    sizes = np.diff(cuts, axis=1)                                              # [T, world]
+    before = np.concatenate([np.zeros((1, world), dtype=np.int64), np.cumsum(sizes, axis=0)[:-1]], axis=0)
+    p = np.empty_like(ids)
+    for tt in range(T):                                                        # owner rank inside the type
+        m = t == tt
+        if m.any():
+            p[m] = np.searchsorted(cuts[tt], ids[m], side="right") - 1
+    return p * max_rows + before[t, p] + (ids - cuts[t, p])
+
+
+def make_shard(coo: HeteroCOO, rank: int, world: int) -> ShardPlan:
+    cuts = type_slices(coo.node_type_offsets, world)
+    T = cuts.shape[0]
+    sizes = np.diff(cuts, axis=1)                       # [T, world]
+    n_per_rank = sizes.sum(0)
+    max_rows = int(n_per_rank.max())
+    owned = np.concatenate([np.arange(cuts[t, rank], cuts[t, rank + 1], dtype=np.int64) for t in range(T)])
+    g_dst = gathered_ids(cuts, max_rows, coo.dst)
+    owner = g_dst // max_rows
+    mine = owner == rank
+    local_offs = np.zeros(T + 1, dtype=np.int64)
+    np.cumsum(sizes[:, rank], out=local_offs[1:])
+    ptrs = [0]
+    for q in range(world):
+        base = q * max_rows
+        ptrs += [base + int(v) for v in np.cumsum(sizes[:, q])]
+        ptrs.append(base + max_rows)                    # the padding rows of rank q (zero length when n_q == max_rows)
+    return ShardPlan(rank, world, cuts, max_rows, owned,
+                     gathered_ids(cuts, max_rows, coo.src[mine]), (g_dst[mine] - rank * max_rows).astype(np.int64),
+                     coo.etype[mine].astype(np.int64), local_offs, np.asarray(ptrs, dtype=np.int64),
+                     np.bincount(owner, minlength=world).astype(np.int64))
 
 
 def shard_graph(plan: ShardPlan, coo: HeteroCOO, device):
@@ -105,12 +119,16 @@ def shard_graph(plan: ShardPlan, coo: HeteroCOO, device):
         torch.from_numpy(plan.node_type_offsets), device)
     g.rel_src_type = torch.from_numpy(coo.rel_src_type).to(device)
     g.rel_dst_type = torch.from_numpy(coo.rel_dst_type).to(device)
+    # segments of the gathered matrix for typed linears on gathered rows: (T + 1) per rank, the last = padding
+    g.gathered_type_ptrs = torch.from_numpy(plan.gathered_type_ptrs).to(device)
+    g.num_ntypes_global = plan.num_ntypes
+    g.world = plan.world
     return g
 
 
 class _AllGatherRows(torch.autograd.Function):
-    """[n_local, ...] -> [world*max_rows, ...] (rank p at row p*max_rows); backward is the
-    reduce-scatter of the gradient of the gathered matrix."""
+    """[n_local, ...] -> [world*max_rows, ...] (rank p at row p*max_rows; padding rows zero);
+    backward = reduce-scatter of the gradient of the gathered matrix."""
 
     @staticmethod
     def forward(ctx, x, max_rows, group):
@@ -138,54 +156,12 @@ class _AllGatherRows(torch.autograd.Function):
         return mine[: ctx.n], None, None
 
 
-class _AllGatherRowsV(torch.autograd.Function):
-    """[n_p, ...] on rank p -> [sum n_p, ...] in rank order (variable sizes); backward is the
-    matching variable-size reduce-scatter. NCCL runs both as one coalesced group of
-    broadcasts / reduces on the row slices of the big tensor (no staging copy)."""
-
-    @staticmethod
-    def forward(ctx, x, sizes, group):
-        ctx.sizes, ctx.group = list(sizes), group
-        rank = dist.get_rank(group)
-        assert x.shape[0] == ctx.sizes[rank]
-        out = x.new_empty((sum(ctx.sizes),) + tuple(x.shape[1:]))
-        if dist.get_backend(group) == "nccl":
-            dist.all_gather(list(out.split(ctx.sizes)), x.contiguous(), group=group)
-        else:  # gloo (CPU tests): equal-size all_gather of padded parts, then slice
-            m = max(ctx.sizes)
-            part = x.new_zeros((m,) + tuple(x.shape[1:]))
-            part[: x.shape[0]] = x
-            parts = [torch.empty_like(part) for _ in ctx.sizes]
-            dist.all_gather(parts, part, group=group)
-            for dst, src, n in zip(out.split(ctx.sizes), parts, ctx.sizes):
-                dst.copy_(src[:n])
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        g = g.contiguous()
-        rank = dist.get_rank(ctx.group)
-        if dist.get_backend(ctx.group) == "nccl":
-            mine = g.new_empty((ctx.sizes[rank],) + tuple(g.shape[1:]))
-            dist.reduce_scatter(mine, list(g.split(ctx.sizes)), op=dist.ReduceOp.SUM, group=ctx.group)
-        else:  # gloo has no reduce_scatter
-            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=ctx.group)
-            mine = g.split(ctx.sizes)[rank]
-        return mine, None, None
-
-
 def all_gather_rows(x: torch.Tensor, max_rows: int, group=None) -> torch.Tensor:
     return _AllGatherRows.apply(x, max_rows, group)
 
 
-def all_gather_rows_v(x: torch.Tensor, sizes, group=None) -> torch.Tensor:
-    return _AllGatherRowsV.apply(x, sizes, group)
-
-
 def gather_rows(x: torch.Tensor, plan: "ShardPlan", group=None) -> torch.Tensor:
-    """The layer-input exchange for ``plan``'s layout."""
-    if plan.layout == "global":
-        return all_gather_rows_v(x, plan.sizes, group)
+    """The layer-input exchange."""
     return all_gather_rows(x, plan.max_rows, group)
 
 

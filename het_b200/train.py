@@ -41,11 +41,12 @@ class FullGraphTrainer:
             self.plan = parallel.make_shard(coo, rank, world)
             self.g = parallel.shard_graph(self.plan, coo, self.device)
             self.n_local = self.plan.num_local_nodes
-            self.lo = self.plan.lo
+            self.owned = torch.from_numpy(self.plan.owned)   # global ids of the owned rows, local order
         else:
             self.plan = None
             self.g = HetGraph(coo, self.device)
-            self.n_local, self.lo = coo.num_nodes, 0
+            self.n_local = coo.num_nodes
+            self.owned = torch.arange(coo.num_nodes)
         self.num_edges_local = self.g.num_edges
         if compact_as_of_node:  # build the unique (relation, node) lists now, outside any graph capture
             self.g.get_separate_unique_node_indices_single_sided()
@@ -74,8 +75,8 @@ class FullGraphTrainer:
         labels_full = torch.randint(0, out_dim, (coo.num_nodes,), generator=gen)
         self.embed = HET_RelGraphEmbed(self.n_local, hidden).to(self.device)
         with torch.no_grad():
-            self.embed.embeds.copy_(embed_full[self.lo:self.lo + self.n_local])
-        self.labels = labels_full[self.lo:self.lo + self.n_local].to(self.device)
+            self.embed.embeds.copy_(embed_full[self.owned])
+        self.labels = labels_full[self.owned].to(self.device)
         self.x_in = torch.zeros(self.n_local, hidden, device=self.device, requires_grad=True)
         self.labels_in = torch.zeros(self.n_local, dtype=torch.int64, device=self.device)
 

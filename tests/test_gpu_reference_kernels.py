@@ -241,14 +241,17 @@ def _ref_dw_rows(seg_ptrs, m):
 @pytest.mark.parametrize("n,e,r,H,K_,N_,tiny", [
     (300, 5000, 7, 1, 64, 64, False),     # RGAT BGS shape: 1 head, 64 -> 64
     (300, 5000, 40, 1, 64, 64, True),     # many tiny / empty segments
-    (200, 3000, 5, 4, 64, 16, False),     # RGAT multi-head: input one head, W [R,4,64,16]
     (100, 1000, 3, 1, 32, 128, False),
 ])
 def test_relational_matmul_vs_reference_kernel(cuda, n, e, r, H, K_, N_, tiny):
     """a1 / a2: HET_RGNNFeatPerEdgeFwProp, HET_RGNNDeltaNodeFeatInputBckProp, HET_RGNNDeltaWeightBckProp
     (RGNN/my_shmem_sgemm_func.cu.h:504,711,746) with InputNumHeadOneFlag = true (the RGAT use; with
     a multi-head input the reference reads head 0 for every head, MySGEMMNumHeadKind::AssertANumIsOne,
-    and offsets W by r*K*N instead of r*H*K*N, :519-523 — not comparable)."""
+    and offsets W by r*K*N instead of r*H*K*N, :519-523 — not comparable). One head only: with
+    num_heads > 1 the kernel divides by `blockDim.z / num_heads` = 1 / H = 0 (:185-190, blockDim where
+    gridDim is meant) and returns garbage for every row — measured here with H = 4, 96127 of 96128
+    output elements wrong — so the reference has no usable multi-head segment MM to pin against;
+    hetb200's multi-head path is pinned by the fp64 oracle (tests/test_gpu_segment_mm.py)."""
     from het_b200.kernels import K
     rel_ptrs = _segments(r, e, seed=e + r, tiny=tiny).to(cuda)
     e = int(rel_ptrs[-1])

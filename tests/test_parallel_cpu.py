@@ -11,16 +11,22 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 
-def test_partition_balances_in_edges():
+def test_type_slices_balance_nodes_and_edges():
+    """Every rank owns a slice of every node type: N/P rows (+-T) and, with hub ids spread inside a
+    type, ~E/P in-edges (up to the largest hubs)."""
     from het_b200 import graphs, parallel
-    coo = graphs.bgs_shaped(scale=0.05)
+    coo = graphs.mag_shaped(scale=0.01)
     for world in (2, 4, 8):
-        b = parallel.partition_destinations(coo.dst, coo.num_nodes, world)
-        assert b[0] == 0 and b[-1] == coo.num_nodes and np.all(np.diff(b) > 0)
-        per = np.array([((coo.dst >= b[p]) & (coo.dst < b[p + 1])).sum() for p in range(world)])
+        cuts = parallel.type_slices(coo.node_type_offsets, world)
+        assert np.array_equal(cuts[:, 0], coo.node_type_offsets[:-1]) and np.array_equal(cuts[:, -1], coo.node_type_offsets[1:])
+        assert np.all(np.diff(cuts, axis=1) >= 0)
+        n_per = np.diff(cuts, axis=1).sum(0)
+        assert n_per.sum() == coo.num_nodes and n_per.max() - n_per.min() <= coo.num_ntypes
+        plan = parallel.make_shard(coo, 0, world)
+        per = plan.edges_per_rank
         assert per.sum() == coo.num_edges
         hub = np.bincount(coo.dst).max()
-        assert per.max() <= coo.num_edges / world + hub + 1  # balanced up to one hub row
+        assert per.max() <= 1.25 * coo.num_edges / world + 4 * hub
 
 
 def test_shards_cover_every_edge_once_and_remap_sources():
@@ -28,24 +34,37 @@ def test_shards_cover_every_edge_once_and_remap_sources():
     coo = graphs.mag_shaped(scale=0.002)
     world = 3
     seen = 0
+    owned_all = []
     for r in range(world):
-        g = parallel.make_shard(coo, r, world)  # default layout: global ids, nothing padded
-        mine = (coo.dst >= g.lo) & (coo.dst < g.hi)
-        assert g.layout == "global" and np.array_equal(g.src, coo.src[mine])
-        assert g.num_gathered_rows == coo.num_nodes and sum(g.sizes) == coo.num_nodes
-        assert g.gathered_offset == g.lo
-        p = parallel.make_shard(coo, r, world, layout="padded")
+        p = parallel.make_shard(coo, r, world)
         seen += p.src.size
+        owned_all.append(p.owned)
         assert p.dst.min() >= 0 and p.dst.max() < p.num_local_nodes
-        # padded source id -> (owner, local row) -> global id round-trips
+        # every local edge's destination is owned, and maps back to the global edge list
+        mine = np.isin(coo.dst, p.owned)
+        assert mine.sum() == p.src.size
+        assert np.array_equal(p.owned[p.dst], coo.dst[mine])
+        # gathered source id -> (owner, local row) -> global id round-trips
         owner, local = p.src // p.max_rows, p.src % p.max_rows
-        glob = p.bounds[owner] + local
-        mine = (coo.dst >= p.lo) & (coo.dst < p.hi)
+        glob = np.empty_like(p.src)
+        for q in range(world):
+            pq = parallel.make_shard(coo, q, world)
+            m = owner == q
+            assert np.all(local[m] < pq.num_local_nodes)
+            glob[m] = pq.owned[local[m]]
         assert np.array_equal(glob, coo.src[mine])
-        assert np.all(local < np.diff(p.bounds)[owner])
-        # per-shard node type offsets are the global ones clipped to the range
-        assert p.node_type_offsets[0] == 0 and p.node_type_offsets[-1] == p.num_local_nodes
+        # local rows are sorted by type: per-shard type offsets partition them
+        offs = p.node_type_offsets
+        assert offs[0] == 0 and offs[-1] == p.num_local_nodes
+        for t in range(coo.num_ntypes):
+            ids = p.owned[offs[t]:offs[t + 1]]
+            assert np.all((ids >= coo.node_type_offsets[t]) & (ids < coo.node_type_offsets[t + 1]))
+        # segments of the gathered layout: per rank T types + its padding, covering world * max_rows rows
+        gp = p.gathered_type_ptrs
+        assert gp.size == world * (coo.num_ntypes + 1) + 1 and gp[0] == 0 and gp[-1] == p.num_gathered_rows
+        assert np.all(np.diff(gp) >= 0)
     assert seen == coo.num_edges
+    assert np.array_equal(np.sort(np.concatenate(owned_all)), np.arange(coo.num_nodes))
 
 
 def _free_port():
@@ -54,23 +73,24 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, q, layout="global"):
+def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from het_b200 import graphs, parallel
         coo = graphs.aifb_shaped(scale=0.2)
-        plan = parallel.make_shard(coo, rank, world, layout=layout)
+        plan = parallel.make_shard(coo, rank, world)
         torch.manual_seed(0)
         x_full = torch.randn(coo.num_nodes, 8, dtype=torch.float64)
         w = torch.randn(8, 4, dtype=torch.float64, requires_grad=True)
-        x_loc = x_full[plan.lo:plan.hi].clone().requires_grad_(True)
+        own = torch.from_numpy(plan.owned)
+        x_loc = x_full[own].clone().requires_grad_(True)
         xg = parallel.gather_rows(x_loc, plan)
         assert xg.shape[0] == plan.num_gathered_rows
         # a toy "layer": out[dst] += (x[src] @ w), loss = sum(out * c)
         src, dst = torch.from_numpy(plan.src), torch.from_numpy(plan.dst)
         out = torch.zeros(plan.num_local_nodes, 4, dtype=torch.float64).index_add(0, dst, xg[src] @ w)
-        c = torch.arange(coo.num_nodes * 4, dtype=torch.float64).view(-1, 4)[plan.lo:plan.hi] / 100
+        c = torch.arange(coo.num_nodes * 4, dtype=torch.float64).view(-1, 4)[own] / 100
         (out * c).sum().backward()
         parallel.all_reduce_grads([w])
         # unsharded reference
@@ -79,20 +99,19 @@ def _worker(rank, world, port, q, layout="global"):
         of = torch.zeros(coo.num_nodes, 4, dtype=torch.float64).index_add(
             0, torch.from_numpy(coo.dst), xf[torch.from_numpy(coo.src)] @ wf)
         (of * (torch.arange(coo.num_nodes * 4, dtype=torch.float64).view(-1, 4) / 100)).sum().backward()
-        ok = (torch.allclose(out, of[plan.lo:plan.hi].detach()) and torch.allclose(w.grad, wf.grad)
-              and torch.allclose(x_loc.grad, xf.grad[plan.lo:plan.hi]))
+        ok = (torch.allclose(out, of[own].detach()) and torch.allclose(w.grad, wf.grad)
+              and torch.allclose(x_loc.grad, xf.grad[own]))
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.timeout(180)
-@pytest.mark.parametrize("layout", ["global", "padded"])
-def test_all_gather_rows_autograd_gloo_world2(layout):
+def test_all_gather_rows_autograd_gloo_world2():
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, layout)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:

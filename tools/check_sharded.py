@@ -46,10 +46,10 @@ def close(a, b, what, rtol=1e-4, atol=2e-5):
 
 ok = True
 # forward
-lo, hi = sh.lo, sh.lo + sh.n_local
+own = sh.owned.to(dev)
 logits_sh = sh.forward(sh.embed())
 logits_full = full.forward(full.embed())
-ok &= close(logits_sh, logits_full[lo:hi], "logits shard")
+ok &= close(logits_sh, logits_full[own], "logits shard")
 # backward
 loss_sh = Fn.nll_loss(Fn.log_softmax(logits_sh, -1), sh.labels, reduction="sum") / coo.num_nodes
 loss_sh.backward()
@@ -61,7 +61,7 @@ dist.all_reduce(tot)
 ok &= close(tot, loss_full.detach(), "loss")
 for (n1, p1), (n2, p2) in zip(sh.model.named_parameters(), full.model.named_parameters()):
     ok &= close(p1.grad, p2.grad, f"grad {n1}", rtol=2e-4, atol=3e-5)
-ok &= close(sh.embed.embeds.grad, full.embed.embeds.grad[lo:hi], "grad embedding shard", rtol=2e-4, atol=3e-5)
+ok &= close(sh.embed.embeds.grad, full.embed.embeds.grad[own], "grad embedding shard", rtol=2e-4, atol=3e-5)
 # a few optimizer steps through the public API (eager + captured)
 for _ in range(3):
     l_sh = sh.step()
