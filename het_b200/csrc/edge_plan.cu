@@ -30,6 +30,23 @@ namespace hetb {
 
 constexpr int kPThreads = 256;
 constexpr int kMaxSmemMuPlan = 4096;
+// tuning knobs (tools/sweep_edge_plan.py rebuilds with -D...): positions in flight per lane group in the
+// forward / backward walks, resident CTAs per SM the register allocation is capped for
+#ifndef HETB_PLAN_FWD_U
+#define HETB_PLAN_FWD_U 1
+#endif
+#ifndef HETB_PLAN_BWD_U
+#define HETB_PLAN_BWD_U 1
+#endif
+#ifndef HETB_PLAN_FWD_MINB
+#define HETB_PLAN_FWD_MINB 6
+#endif
+#ifndef HETB_PLAN_BWD_MINB
+#define HETB_PLAN_BWD_MINB 4
+#endif
+#ifndef HETB_PLAN_PREFETCH
+#define HETB_PLAN_PREFETCH 1  // fetch the next batch's indices while this batch's rows are in flight
+#endif
 
 template <typename T>
 __device__ __forceinline__ float4 ld_row4(const T *base, int64_t row, int D, int l);
@@ -141,7 +158,7 @@ __global__ void __launch_bounds__(kPThreads)
 // (GAT/FusedGAT.cu.h:123-222,33-116); nothing per edge is saved (the backward recomputes x).
 // ---------------------------------------------------------------------------
 template <typename T, int LPR, bool MODE_RGAT>
-__global__ void __launch_bounds__(kPThreads)
+__global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
     plan_fwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
                          const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
                          const int *__restrict__ p_src, const int *__restrict__ p_msg,
@@ -154,7 +171,7 @@ __global__ void __launch_bounds__(kPThreads)
                          int H, int hw) {
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
-  constexpr int U = 4;  // positions in flight per lane group
+  constexpr int U = HETB_PLAN_FWD_U;  // positions in flight per lane group
   const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int g = blockIdx.x * GROUPS + grp;
   if (g >= num_items) return;  // whole lane group leaves: its lanes are in no other group's mask
@@ -184,17 +201,23 @@ __global__ void __launch_bounds__(kPThreads)
     }
   };
 
-  for (int p = p0; p < p1; p += U) {
-    int sn[U], mi[U], li[U];
-    float xs[U];
-    float4 lv[U], kvv[U], mv[U];
+  // Software pipeline: the index triple of batch b+1 is fetched while the rows of batch b are in
+  // flight, so a batch costs one memory round trip (the rows), not two (indices, then rows).
+  int sn[U], mi[U], li[U];
+  auto load_idx = [&](int p, int *s_, int *m_, int *l_) {
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int pp = (p + q < p1) ? p + q : p1 - 1;  // clamp: the tail repeats the last position (masked below)
-      mi[q] = __ldg(p_msg + pp);
-      li[q] = __ldg(p_left + pp);
-      if (!MODE_RGAT) sn[q] = __ldg(p_src + pp);
+      m_[q] = __ldg(p_msg + pp);
+      l_[q] = __ldg(p_left + pp);
+      if (!MODE_RGAT) s_[q] = __ldg(p_src + pp);
     }
+  };
+  if (HETB_PLAN_PREFETCH) load_idx(p0, sn, mi, li);
+  for (int p = p0; p < p1; p += U) {
+    float xs[U];
+    float4 lv[U], kvv[U], mv[U];
+    if (!HETB_PLAN_PREFETCH) load_idx(p, sn, mi, li);
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       mv[q] = ld_row4<T>(msg, mi[q], D, l);
@@ -206,6 +229,7 @@ __global__ void __launch_bounds__(kPThreads)
         xs[q] = __ldg(el + (int64_t)mi[q] * H + h) + __ldg(er + (int64_t)li[q] * H + h);
       }
     }
+    if (HETB_PLAN_PREFETCH && p + U < p1) load_idx(p + U, sn, mi, li);  // next batch (the loads above already hold their addresses)
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int pp = p + q;
@@ -288,7 +312,7 @@ __global__ void __launch_bounds__(kPThreads)
 // Rows / runs split across items (bit 31 of nz_rows[j] / urow_rel[u]) are pre-zeroed and reduced.
 // ---------------------------------------------------------------------------
 template <typename T, int LPR>
-__global__ void __launch_bounds__(kPThreads)
+__global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
     plan_hgt_bwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
                              const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
                              const int *__restrict__ p_dst, const int *__restrict__ p_left,
@@ -302,7 +326,7 @@ __global__ void __launch_bounds__(kPThreads)
                              int use_smem) {
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
-  constexpr int U = 2;
+  constexpr int U = HETB_PLAN_BWD_U;
   extern __shared__ float mu_acc[];
   const int RH = num_rels * H;
   if (use_smem) {
@@ -342,10 +366,8 @@ __global__ void __launch_bounds__(kPThreads)
       else st4(grad_kv + srow * D + 4 * l, acc_k);
     };
 
-    for (int p = p0; p < p1; p += U) {
-      int dn[U], li[U], ui[U], pq[U];
-      float aa[U], ls[U], cc[U];
-      float4 go[U], lv[U];
+    int dn[U], li[U], ui[U], pq[U];
+    auto load_idx = [&](int p) {
 #pragma unroll
       for (int q = 0; q < U; ++q) {
         const int pp = (p + q < p1) ? p + q : p1 - 1;
@@ -354,6 +376,13 @@ __global__ void __launch_bounds__(kPThreads)
         ui[q] = __ldg(p_msg + pp);
         pq[q] = __ldg(p_perm + pp);
       }
+    };
+    if (HETB_PLAN_PREFETCH) load_idx(p0);
+    for (int p = p0; p < p1; p += U) {
+      int lic[U], uic[U];
+      if (!HETB_PLAN_PREFETCH) load_idx(p);
+      float aa[U], ls[U], cc[U];
+      float4 go[U], lv[U];
 #pragma unroll
       for (int q = 0; q < U; ++q) {
         go[q] = ldg4(gout + (int64_t)dn[q] * D + 4 * l);
@@ -361,7 +390,10 @@ __global__ void __launch_bounds__(kPThreads)
         aa[q] = __ldg(attn + (int64_t)pq[q] * H + h);
         ls[q] = __ldg(lse + (int64_t)dn[q] * H + h);
         cc[q] = __ldg(gdoto + (int64_t)dn[q] * H + h);
+        lic[q] = li[q];
+        uic[q] = ui[q];
       }
+      if (HETB_PLAN_PREFETCH && p + U < p1) load_idx(p + U);  // indices of the next batch while this batch's rows are in flight
 #pragma unroll
       for (int q = 0; q < U; ++q) {
         const int pp = p + q;
@@ -377,9 +409,9 @@ __global__ void __launch_bounds__(kPThreads)
             kvr = ld_row4<T>(kv, srow, D, l);
             acc_k = make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          if (ui[q] != cur_u) {
+          if (uic[q] != cur_u) {
             flush_run();
-            cur_u = ui[q];
+            cur_u = uic[q];
             relword = __ldg(urow_rel + cur_u);
             msgr = ld_row4<T>(msg, cur_u, D, l);
             mu_r = __ldg(mu + (relword & 0x7fffffff) * H + h);
@@ -393,7 +425,7 @@ __global__ void __launch_bounds__(kPThreads)
           acc_mu = fmaf(sg, aa[q], acc_mu);
           fma4(acc_m, nrm, go[q]);
           fma4(acc_k, ga, lv[q]);
-          red_add4(grad_left + (int64_t)li[q] * D + 4 * l,
+          red_add4(grad_left + (int64_t)lic[q] * D + 4 * l,
                    make_float4(ga * kvr.x, ga * kvr.y, ga * kvr.z, ga * kvr.w));
         }
       }

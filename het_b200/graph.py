@@ -65,6 +65,7 @@ class HetGraph:
             "rel_ptrs": rel_ptrs, "row_indices": row, "col_indices": col, "eids": eid,
         }
         new_eid = remap  # edge id of original edge i
+        self.orig_to_canonical_eid = remap
         o_col, o_rel, o_eid, o_ptr = K.hetb200_stable_sort_by_key(src, self.num_src_nodes, [dst, rel, new_eid])
         self.out_csr = {"row_ptrs": o_ptr, "col_indices": o_col, "rel_types": o_rel, "eids": o_eid}
         i_col, i_rel, i_eid, i_ptr = K.hetb200_stable_sort_by_key(dst, self.num_nodes, [src, rel, new_eid])

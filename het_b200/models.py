@@ -125,6 +125,29 @@ class HET_RGATLayer(nn.Module):
         return fn(g, feat_compact, el_compact.view(-1, self.num_heads, 1), er_compact.view(-1, self.num_heads, 1),
                   self.leaky_relu_slope)
 
+    @th.no_grad()
+    def logit_signs(self, g, inputs, inputs_dst=None):
+        """Diagnostic: sign of the attention logit el + er of every edge ([E, H] bool, indexed by
+        canonical edge id), recomputed with the same typed-linear kernels the forward uses. Tests
+        hand it to the fp64 oracle so that both take the same side of the leaky-ReLU kink for the
+        few edges whose logit is within fp32 rounding of zero."""
+        if inputs_dst is None:
+            inputs_dst = inputs
+        u = g.get_separate_unique_node_indices_single_sided()
+        row = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"], "unique_srcs_and_dests_node_indices": u["node_indices_row"]}
+        col = {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"], "unique_srcs_and_dests_node_indices": u["node_indices_col"]}
+        feat_c = B.rgnn_relational_matmul(row, self.conv_weights, inputs, True, 1)
+        el = B.rgnn_relational_matmul_no_scatter_gather_list(u["rel_ptrs_row"], self.attn_l.unsqueeze(-1),
+                                                             feat_c.view(feat_c.size(0), -1))
+        if self.compact_as_of_node_flag and self.linear_reorder_flag:
+            w_r = th.einsum("rhkf,rhf->rhk", self.conv_weights, self.attn_r).unsqueeze(-1)
+            er = B.rgnn_relational_matmul(col, w_r, inputs_dst, True, 1).view(-1, self.num_heads)
+        else:
+            feat_d = B.rgnn_relational_matmul(col, self.conv_weights, inputs_dst, True, 1)
+            er = B.rgnn_relational_matmul_no_scatter_gather_list(u["rel_ptrs_col"], self.attn_r.unsqueeze(-1),
+                                                                 feat_d.view(feat_d.size(0), -1))
+        return (el.view(-1, self.num_heads)[u["inverse_idx_row"]] + er.view(-1, self.num_heads)[u["inverse_idx_col"]]) > 0
+
     def _epilogue(self, h, inputs_dst):
         h = h.view(-1, self.out_feat)
         if self.self_loop:

@@ -42,14 +42,16 @@ def _rel_mm(rows, w, etype):
     return out
 
 
-def rgat_layer(src, dst, etype, x, conv_w, attn_l, attn_r, slope, bias=None, kink_side=None, kink_eps=2e-5):
+def rgat_layer(src, dst, etype, x, conv_w, attn_l, attn_r, slope, bias=None, branch=None, kink_eps=2e-5):
     """x [N,Din]; conv_w [R,H,Din,F]; attn_* [R,H,F] -> [N,H*F].
 
-    ``kink_side``: leaky-ReLU is not differentiable at 0, and on a graph of a million edges a few
-    logits el + er land within fp32 rounding of it, where a correct fp32 kernel may take either
-    one-sided derivative. "hi" / "lo" evaluate every logit with |el + er| < kink_eps on the
-    positive / negative branch (the forward value moves by < 0.8 * kink_eps); a gradient check then
-    accepts anything between the two (oracle/testing.py: close_between). None = plain leaky-ReLU."""
+    ``branch`` ([E,H] bool, edge order of src/dst): leaky-ReLU is not differentiable at 0, and on a
+    graph of a million edges a few logits el + er land within fp32 rounding of it, where a correct
+    fp32 kernel may take either one-sided derivative (both are valid subgradients, and weight
+    gradients change by ~1e-3 with the choice). Where |el + er| < kink_eps the oracle takes the
+    branch given here — the sign the implementation under test computed for that edge
+    (HET_RGATLayer.logit_signs) — everywhere else its own; the forward value moves by
+    < 0.8 * kink_eps. None = plain leaky-ReLU."""
     n = x.shape[0]
     fs = _rel_mm(x[src], conv_w, etype)
     fd = _rel_mm(x[dst], conv_w, etype)
@@ -57,8 +59,8 @@ def rgat_layer(src, dst, etype, x, conv_w, attn_l, attn_r, slope, bias=None, kin
     er = (fd * attn_r[etype]).sum(-1)
     pre = el + er
     pos = pre > 0
-    if kink_side is not None:
-        pos = torch.where(pre.detach().abs() < kink_eps, torch.full_like(pos, kink_side == "hi"), pos)
+    if branch is not None:
+        pos = torch.where(pre.detach().abs() < kink_eps, branch, pos)
     a = _segment_softmax_sum(torch.exp(torch.where(pos, pre, slope * pre)), dst, n)
     out = torch.zeros(n, fs.shape[1], fs.shape[2], dtype=x.dtype).index_add_(0, dst, a.unsqueeze(-1) * fs)
     out = out.reshape(n, -1)

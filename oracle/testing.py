@@ -46,23 +46,3 @@ def unit_gain_init(model, seed=0):
             elif p.dim() >= 2:                        # [..., in, out]
                 b = (3.0 / p.shape[-2]) ** 0.5
                 p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) * b)
-
-
-def close_between(got, lo, hi, what, rtol=RTOL, atol=ATOL):
-    """``got`` lies in the elementwise interval spanned by the two one-sided oracle results ``lo`` and
-    ``hi`` (see oracle/models_ref.py: rgat_layer, kink_side), widened by atol * max|ref| + rtol * |ref|.
-    Where lo == hi (every coordinate no near-kink edge touches) this is exactly ``close``."""
-    g = got.detach().double().cpu().reshape(-1)
-    a = lo.detach().double().cpu().reshape(-1)
-    b = hi.detach().double().cpu().reshape(-1)
-    assert g.shape == a.shape == b.shape, f"{what}: shape {got.shape} vs {lo.shape}"
-    assert bool(torch.isfinite(g).all()), f"{what}: non-finite values in the result"
-    if a.numel() == 0:
-        return
-    lo_, hi_ = torch.minimum(a, b), torch.maximum(a, b)
-    scale = torch.maximum(a.abs().max(), b.abs().max())
-    dist = torch.clamp(lo_ - g, min=0) + torch.clamp(g - hi_, min=0)
-    bad = dist > (atol * scale + rtol * torch.maximum(a.abs(), b.abs()))
-    assert not bool(bad.any()), (f"{what}: max distance {dist.max():.3e} from the oracle interval vs max|ref| "
-                                 f"{scale:.3e}, {int(bad.sum())} of {a.numel()} bad "
-                                 f"({int((a != b).sum())} coordinates touched by near-kink edges)")
