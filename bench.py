@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--no-compact", dest="compact", action="store_false",
                     help="turn off the reference's compact_as_of_node_flag (default on: X.W_r is computed once "
                          "per unique (relation, node) pair instead of once per edge; same outputs)")
+    ap.add_argument("--bf16-tables", action="store_true",
+                    help="HGT: store the gathered tables (k, W_att.q, W_msg.v) as bf16 (fp32 arithmetic, outputs and "
+                         "gradients; parity bar 2e-2). Off by default: the headline is the fp32 path.")
     ap.add_argument("--no-fused", dest="fused", action="store_false",
                     help="HGT: run inner product, edge softmax and aggregation as three ops instead of one pass")
     return ap.parse_args()
@@ -577,7 +580,8 @@ def main():
     # whole-step CUDA-graph capture; with NCCL collectives inside only when asked for (HETB_GRAPH_MULTI=1)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("HETB_GRAPH_MULTI", "1") == "1")
     trainer = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, rank=rank, world=world,
-                               cuda_graph=use_graph, compact_as_of_node=args.compact, fused=args.fused)
+                               cuda_graph=use_graph, compact_as_of_node=args.compact, fused=args.fused,
+                               bf16_tables=args.bf16_tables)
 
     def barrier():
         if world > 1:
@@ -650,6 +654,41 @@ def main():
     e2e_ms_step = float(e_ms.item()) / args.steps
     e2e_value = coo.num_edges * layers / (e2e_ms_step * 1e-3)
 
+    # ---- exchange cost, collective by collective (N > 1): the same calls the step makes, timed alone ----
+    comm = None
+    if world > 1:
+        plan = trainer.plan
+        part = torch.randn(plan.max_rows, 64, device=dev)
+        full = torch.empty(plan.max_rows * world, 64, device=dev)
+        nparam = sum(p.numel() for p in trainer.model.parameters())
+        flat = torch.zeros(nparam, device=dev)
+
+        def t_coll(fn, reps=10):
+            for _ in range(3):
+                fn()
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            barrier()
+            t = torch.tensor([a.elapsed_time(b) / reps], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        ag = t_coll(lambda: dist.all_gather_into_tensor(full, part))
+        rs = t_coll(lambda: dist.reduce_scatter_tensor(part, full))
+        ar = t_coll(lambda: dist.all_reduce(flat))
+        nbytes = plan.max_rows * (world - 1) * 64 * 4
+        comm = {"all_gather_ms": ag, "reduce_scatter_ms": rs, "weight_all_reduce_ms": ar,
+                "rows_per_rank": int(plan.max_rows), "bytes_received_per_rank_per_collective": int(nbytes),
+                "all_gather_GBps_in": nbytes / (ag * 1e-3) / 1e9, "reduce_scatter_GBps_in": nbytes / (rs * 1e-3) / 1e9,
+                "collectives_per_step": {"all_gather": layers, "reduce_scatter": layers, "all_reduce": 1},
+                "comm_ms_per_step_if_fully_exposed": layers * (ag + rs) + ar,
+                "edges_per_rank": [int(v) for v in plan.edges_per_rank]}
+        del part, full, flat
+
     if rank != 0:
         _teardown(trainer, world)
         return
@@ -658,7 +697,7 @@ def main():
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": _scaling_label(args, scale), "vs_baseline": None,
-        "dtype": "f32",
+        "dtype": "f32 arithmetic, bf16 storage of the gathered tables" if args.bf16_tables else "f32",
         "data": "synthetic",
         "config": {
             "workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s) fwd+loss+bwd+Adam, hidden 64, "
@@ -680,6 +719,8 @@ def main():
         "gpu_launches_per_step": int(launches_per_step),
         "clocks": clocks, "loss": final_loss, "eager_first_loss": eager_loss,
     }
+    if comm is not None:
+        line["comm"] = comm
     if not args.no_roofline:
         legs = (kernel_rooflines_compact if (args.compact or kind == "rgcn") else kernel_rooflines)(trainer, peak, peak_src)
         # measured DRAM traffic per launch (one ncu --set full capture, profiles/ncu_traffic.json), only for

@@ -877,6 +877,75 @@ def hgt_fused_attention_and_aggregation_plan(graph, left_compact, k, message_com
                                                   message_compact.contiguous(), mu.contiguous())
 
 
+class HGTLayerCoreBF16Tables(th.autograd.Function):
+    """bf16 STORAGE mode of the HGT layer core (north star: "rtol 2e-2 in bf16"): the three typed
+    linears of HGTReorderedProjections write k, W_att.q and W_msg.v as bf16 straight from the
+    tcgen05 epilogue (fp32 accumulate, one rounding at the store), the plan-based edge passes gather
+    the bf16 rows (half the bytes of the dominant gathers) and accumulate in fp32. Everything else —
+    layer input, weights, scores, log-sum-exp, outputs and EVERY gradient — stays fp32. One autograd
+    node, so the fp32 gradients of the bf16 tables never pass through autograd's dtype cast."""
+
+    @staticmethod
+    def forward(ctx, graph, h, k_linears, w_att, w_msg, mu):
+        u = graph.get_separate_unique_node_indices_single_sided()
+        offs = graph.get_original_node_type_offsets()
+        pl = graph.get_edge_plan()
+        n, e, hh = graph.get_num_nodes(), graph.get_num_edges(), mu.size(1)
+        d = k_linears.size(1) * k_linears.size(3)
+        f = d // hh
+        dev = h.device
+        none = th.empty(0, dtype=th.int64, device=dev)
+        bf = dict(dtype=th.bfloat16, device=dev)
+        k = th.empty((h.size(0), hh, f), **bf)
+        K.hetb200_typed_linear_bf16out(offs, none, k_linears, h, k)
+        left = th.empty((u["node_indices_col"].numel(), hh, f), **bf)
+        K.hetb200_typed_linear_bf16out(u["rel_ptrs_col"], u["node_indices_col"], w_att, h, left)
+        msg = th.empty((u["node_indices_row"].numel(), hh, f), **bf)
+        K.hetb200_typed_linear_bf16out(u["rel_ptrs_row"], u["node_indices_row"], w_msg, h, msg)
+        sc = graph.plan_scratch(hh, d)
+        new_h = th.empty((n, hh, f), dtype=th.float32, device=dev)
+        lse = th.empty((n, hh), dtype=th.float32, device=dev)
+        attn = th.empty((e, hh), dtype=th.float32, device=dev)
+        K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu, attn, lse, new_h, sc["part_m"],
+                                     sc["part_s"], sc["part_acc"], sc["ssum"])
+        ctx.graph = graph
+        ctx.save_for_backward(h, k_linears, w_att, w_msg, mu, k, left, msg, attn, lse, new_h)
+        return new_h
+
+    @staticmethod
+    def backward(ctx, gradout):
+        h, k_linears, w_att, w_msg, mu, k, left, msg, attn, lse, new_h = ctx.saved_tensors
+        graph = ctx.graph
+        u = graph.get_separate_unique_node_indices_single_sided()
+        offs = graph.get_original_node_type_offsets()
+        pl = graph.get_edge_plan()
+        hh, f = mu.size(1), msg.size(2)
+        sc = graph.plan_scratch(hh, hh * f)
+        f32 = dict(dtype=th.float32, device=mu.device)
+        grad_left, grad_mu = th.zeros(left.shape, **f32), th.zeros(mu.shape, **f32)
+        grad_k, grad_msg = th.empty(k.shape, **f32), th.empty(msg.shape, **f32)
+        K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
+                                     gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
+        grad_h = th.empty_like(h, memory_format=th.contiguous_format)
+        grad_wk = th.zeros_like(k_linears, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(
+            offs, th.transpose(k_linears, 2, 3).contiguous(), h, grad_k.view(h.size(0), -1), grad_h, grad_wk)
+        grad_watt = th.zeros_like(w_att, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_col"], "unique_srcs_and_dests_node_indices": u["node_indices_col"]},
+            1, th.transpose(w_att, 2, 3).contiguous(), h, grad_left.view(grad_left.size(0), 1, -1), grad_h, grad_watt, True)
+        grad_wmsg = th.zeros_like(w_msg, memory_format=th.contiguous_format)
+        K.backward_rgnn_relational_matmul(
+            {"unique_srcs_and_dests_rel_ptrs": u["rel_ptrs_row"], "unique_srcs_and_dests_node_indices": u["node_indices_row"]},
+            1, th.transpose(w_msg, 2, 3).contiguous(), h, grad_msg.view(grad_msg.size(0), 1, -1), grad_h, grad_wmsg, True)
+        return None, grad_h, grad_wk, grad_watt, grad_wmsg, grad_mu
+
+
+def hgt_layer_core_bf16_tables(graph, h, k_linears, w_att, w_msg, mu):
+    return HGTLayerCoreBF16Tables.apply(graph, h.contiguous(), k_linears.contiguous(), w_att.contiguous(),
+                                        w_msg.contiguous(), mu.contiguous())
+
+
 class RelationalFusedGatPlan(th.autograd.Function):
     """relational_fused_gat_csr on compact inputs over the walk plans; with ``attn_l`` given the
     el = <feat_compact, attn_l[r]> row-dot and its backward are part of the node (as in

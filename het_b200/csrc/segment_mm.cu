@@ -587,6 +587,20 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
   return HETB_OK;
 }
 
+// Same contraction with the output stored as bf16 (plain store, no accumulation): the tables the
+// plan-based edge passes gather (k, W_att·q, W_msg·v per compact row). Tensor-core path only
+// (64-wide contraction and output); anything else is HETB_EUNSUPPORTED, there is no fallback.
+extern "C" int hetb_segment_mm_bf16out(const float *A, const int64_t *a_idx, int a_heads, const float *W,
+                                       void *Y_bf16, const int64_t *c_idx, const int64_t *seg_ptrs,
+                                       int64_t num_segs, int64_t num_rows, int H, int K, int N, void *stream) {
+  HETB_CHECK_ARG(num_rows >= 0 && num_segs >= 0 && H > 0 && K > 0 && N > 0);
+  HETB_CHECK_ARG(a_heads == 1 || a_heads == H);
+  if (num_rows == 0) return HETB_OK;
+  HETB_CHECK_ARG(A && W && Y_bf16 && seg_ptrs && num_segs > 0);
+  return hetb_segment_mm_tc(A, a_idx, a_heads, W, (float *)Y_bf16, c_idx, H, seg_ptrs, num_segs, num_rows, H, K, N, 0,
+                            3 | (1 << 12), stream);
+}
+
 extern "C" int hetb_segment_mm_grad_w(const float *A, const int64_t *a_idx,
                                       int a_heads, const float *G,
                                       const int64_t *g_idx, int g_heads,

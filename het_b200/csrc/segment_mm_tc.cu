@@ -34,6 +34,8 @@
 // tile is multiplied, only that piece's rows are stored). No host schedule, no
 // device->host copy of the segment offsets, no allocation (the reference needs all
 // three per call: OpExport/RGNNOps.inc.h:150-169).
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -120,7 +122,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     segmm_tc_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx,
                     const float *__restrict__ W, float *__restrict__ Y,
                     const int64_t *__restrict__ c_idx, const int64_t *__restrict__ seg_ptrs, int num_segs,
-                    int64_t M, int H, int K, int N, int bmode, int accumulate, int passes, int probe) {
+                    int64_t M, int H, int K, int N, int bmode, int accumulate, int passes, int probe, int y_bf16) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SW128 atoms need 1024 B alignment
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -364,9 +366,17 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (rr >= p0 && rr < p1 && !(probe & 4)) {
           const int pc = (c & 8) | ((c & 7) ^ (lr & 7));
           const float4 val = *reinterpret_cast<const float4 *>(stg + lr * 256 + pc * 16);
-          float *dst = Y + cr * NN + c * 4;
-          if (accumulate) red_add4(dst, val);
-          else st4(dst, val);
+          if (y_bf16) {  // bf16 storage of a table the edge passes gather (fp32 accumulate up to here)
+            const __nv_bfloat162 lo2 = __floats2bfloat162_rn(val.x, val.y), hi2 = __floats2bfloat162_rn(val.z, val.w);
+            uint2 packed;
+            packed.x = *reinterpret_cast<const uint32_t *>(&lo2);
+            packed.y = *reinterpret_cast<const uint32_t *>(&hi2);
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(Y) + cr * NN + c * 4) = packed;
+          } else {
+            float *dst = Y + cr * NN + c * 4;
+            if (accumulate) red_add4(dst, val);
+            else st4(dst, val);
+          }
         }
       }
       __syncwarp();
@@ -393,6 +403,9 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
                        const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
                        int64_t num_rows, int H, int K, int N, int accumulate, int passes, void *stream) {
   int bmode;
+  const int y_bf16 = (passes >> 12) & 1;  // bit 12: Y is __nv_bfloat16 (hetb_segment_mm_bf16out)
+  passes &= 0xfff;
+  if (y_bf16 && accumulate) return HETB_EUNSUPPORTED;
   const int probe = passes >> 4;
   passes &= 15;
   if (a_heads == H && c_heads == H && H * K == tc::KK && H * N == tc::NN)
@@ -414,7 +427,7 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
   const int64_t tiles = ceil_div64(num_rows, tc::TM);
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   tc::segmm_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, (cudaStream_t)stream>>>(
-      A, a_idx, W, Y, c_idx, seg_ptrs, (int)num_segs, num_rows, H, K, N, bmode, accumulate, passes, probe);
+      A, a_idx, W, Y, c_idx, seg_ptrs, (int)num_segs, num_rows, H, K, N, bmode, accumulate, passes, probe, y_bf16);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -802,6 +802,26 @@ void hetb200_backward_hgt_fused_attention_aggregation_csr(
            op);
 }
 
+// hetb200 extension: typed linear with the output stored as bf16 (a table the plan-based edge passes
+// gather). `gather` (int64 node list) may be an empty tensor: rows are then the segments' own rows
+// (the no_scatter_gather_list form). Tensor-core shapes only; fails loudly otherwise.
+void hetb200_typed_linear_bf16out(Tensor &seg_ptrs, Tensor &gather, Tensor &weights, Tensor &inputs, Tensor &ret) {
+  const char *op = "hetb200_typed_linear_bf16out";
+  TORCH_CHECK(weights.dim() == 4, op, ": weights must be [S,H,in,out/H]");
+  TORCH_CHECK(ret.is_cuda() && ret.is_contiguous() && ret.scalar_type() == at::kBFloat16, op,
+              ": `ret` must be a contiguous bfloat16 CUDA tensor");
+  const int H = (int)weights.size(1), K = (int)weights.size(2), N = (int)weights.size(3);
+  const int a_heads = (xlen(inputs) == (int64_t)H * K) ? H : 1;
+  const bool has_gather = gather.numel() > 0;
+  const int64_t M = has_gather ? gather.numel() : inputs.size(0);
+  TORCH_CHECK(ret.numel() == M * H * N, op, ": `ret` has the wrong size");
+  c10::cuda::CUDAGuard guard(ret.device());
+  check_rc(hetb_segment_mm_bf16out(f32(inputs, op, "inputs"), has_gather ? i64(gather, op, "gather") : nullptr, a_heads,
+                                   f32(weights, op, "weights"), ret.data_ptr(), nullptr,
+                                   i64(seg_ptrs, op, "seg_ptrs"), seg_ptrs.numel() - 1, M, H, K, N, stream_of(ret)),
+           op);
+}
+
 // ------------------------------------------------- plan-based fused edge passes ---
 // A walk plan travels as ONE int32 device tensor plus a host list of integers
 // (het_b200/graph.py: WalkPlan.blob / .meta): counts first, then the element offset of every array
@@ -1157,6 +1177,7 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
   m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
         hetb200_backward_hgt_fused_attention_aggregation_csr);
+  m.def("hetb200_typed_linear_bf16out", hetb200_typed_linear_bf16out);
   m.def("hetb200_hgt_fused_fwd_plan", hetb200_hgt_fused_fwd_plan);
   m.def("hetb200_hgt_fused_bwd_plan", hetb200_hgt_fused_bwd_plan);
   m.def("hetb200_rgat_fused_fwd_plan", hetb200_rgat_fused_fwd_plan);

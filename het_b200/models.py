@@ -277,8 +277,11 @@ class HET_RGCNModel(nn.Module):
 class HET_HGTLayerHetero(nn.Module):
     def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
                  compact_as_of_node_flag=False, compact_direct_indexing_flag=True,
-                 fused_attention_aggregation_flag=False, linear_reorder_flag=False):
+                 fused_attention_aggregation_flag=False, linear_reorder_flag=False, bf16_tables_flag=False):
         super().__init__()
+        # bf16 STORAGE of the gathered tables (k, W_att.q, W_msg.v): needs the compact + fused + reordered
+        # path on one GPU; arithmetic, outputs and gradients stay fp32 (backend.HGTLayerCoreBF16Tables)
+        self.bf16_tables_flag = bf16_tables_flag
         # Hector's linear operator reordering (compact path): (h.W_q[type]).W_att[r] = h.(W_q[type].W_att[r])
         # and the same for W_v / W_msg, so Q and V are never materialised; the composed [R, in, out]
         # weights cost R small products per step. Needs one (src type, dst type) pair per relation.
@@ -349,6 +352,13 @@ class HET_HGTLayerHetero(nn.Module):
             if not self.compact_direct_indexing_flag:
                 raise NotImplementedError("compact_as_of_node without direct indexing (binary search)")
             u = G.get_separate_unique_node_indices_single_sided()
+            if self.bf16_tables_flag:
+                if not (reorder and gather is None and self.fused_attention_aggregation_flag and B.USE_EDGE_PLAN):
+                    raise NotImplementedError("bf16_tables_flag needs compact + reorder + fused flags on one GPU")
+                new_h = B.hgt_layer_core_bf16_tables(G, h, self.k_linears, w_att, w_msg,
+                                                     self.relation_pri / self.sqrt_dk)
+                return B.rgnn_relational_matmul_no_scatter_gather_list(
+                    offs, th.sigmoid(self.skip) * self.a_linears, new_h.view(-1, self.out_dim))
             if reorder and gather is None:
                 # k and the two compact products read the same h: one autograd node, one grad_h buffer
                 k, attn_weight_dst_product_compact, message_compact = B.hgt_reordered_projections(

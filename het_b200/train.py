@@ -32,7 +32,7 @@ from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel, HET_RGC
 class FullGraphTrainer:
     def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
                  layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0,
-                 compact_as_of_node=False, fused=False):
+                 compact_as_of_node=False, fused=False, bf16_tables=False):
         assert kind in ("rgat", "hgt", "rgcn")
         self.kind, self.device, self.rank, self.world, self.group = kind, torch.device(device), rank, world, group
         self.num_nodes_total = coo.num_nodes
@@ -68,8 +68,8 @@ class FullGraphTrainer:
             self.model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, hidden, out_dim, heads, layers,
                                            compact_as_of_node_flag=compact_as_of_node,
                                            fused_attention_aggregation_flag=bool(fused and compact_as_of_node),
-                                           linear_reorder_flag=bool(fused and compact_as_of_node)
-                                           ).to(self.device)
+                                           linear_reorder_flag=bool(fused and compact_as_of_node),
+                                           bf16_tables_flag=bool(bf16_tables)).to(self.device)
         gen = torch.Generator().manual_seed(seed + 1)
         embed_full = torch.rand(coo.num_nodes, hidden, generator=gen) * 2 - 1
         labels_full = torch.randint(0, out_dim, (coo.num_nodes,), generator=gen)

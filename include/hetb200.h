@@ -66,6 +66,14 @@ int hetb_segment_mm(const float *A, const int64_t *a_idx, int a_heads,
                     int64_t num_rows, int H, int K, int N, int accumulate,
                     void *stream);
 
+/* hetb_segment_mm with Y stored as bf16 ([*, H, N] __nv_bfloat16, plain store): the tables the
+ * plan-based edge passes gather (north star: "2e-2 in bf16"). fp32 inputs, 3xTF32 products and fp32
+ * accumulation as above; only the final store rounds. Tensor-core shapes only (H*K' = H*N = 64);
+ * HETB_EUNSUPPORTED otherwise (no fallback). */
+int hetb_segment_mm_bf16out(const float *A, const int64_t *a_idx, int a_heads, const float *W, void *Y_bf16,
+                            const int64_t *c_idx, const int64_t *seg_ptrs, int64_t num_segs, int64_t num_rows,
+                            int H, int K, int N, void *stream);
+
 /* Implementation switch for hetb_segment_mm (testing / A-B measurement): 0 = automatic
  * (tcgen05 tensor-core kernel when the shape allows, else SIMT), 1 = SIMT kernels only,
  * 2 = tensor-core kernel only (HETB_EUNSUPPORTED if the shape is outside it). */

@@ -282,3 +282,42 @@ def test_baseline_configs_default_path(cuda, kind, shape, scale, heads, layers):
     for layer, p in zip(model.layers, ps):
         for k, v in layer.named_parameters():
             close(v.grad, p[k].grad, f"{kind} {shape} grad {k}", **WGRAD_TOL)
+
+
+@pytest.mark.parametrize("scale,layers", [(0.002, 1), (0.005, 2), (1.0 / 16, 2)])
+def test_hgt_bf16_table_storage(cuda, scale, layers):
+    """x1: bf16 storage of the gathered tables (k, W_att.q, W_msg.v) with fp32 arithmetic, outputs and
+    gradients. Tolerance is the north star's bf16 bar: rtol 2e-2 (+ 2e-2 of the tensor's max for
+    elements that cancel), against the same fp64 oracle as the fp32 path."""
+    from het_b200.models import HET_HGT_DGLHetero
+    coo, g = _graph(cuda, "mag", scale)
+    torch.manual_seed(1)
+    model = HET_HGT_DGLHetero(coo.num_ntypes, coo.num_rels, 64, 64, 4, num_layers=layers, compact_as_of_node_flag=True,
+                              fused_attention_aggregation_flag=True, linear_reorder_flag=True,
+                              bf16_tables_flag=True).to(cuda)
+    unit_gain_init(model)
+    x = (torch.rand(coo.num_nodes, 64, device=cuda) * 2 - 1).requires_grad_(True)
+    out = model(g, x)
+    assert out.dtype == torch.float32
+    gout = torch.randn_like(out)
+    out.backward(gout)
+    src, dst, et = _coo_t(coo)
+    offs = torch.from_numpy(coo.node_type_offsets)
+    x64 = x.detach().double().cpu().requires_grad_(True)
+    h, ps = x64, []
+    for layer in model.layers:
+        p = {k: v.detach().double().cpu().requires_grad_(True) for k, v in layer.named_parameters()}
+        ps.append(p)
+        h = M.hgt_layer(src, dst, et, offs, h, p["k_linears"], p["q_linears"], p["v_linears"], p["a_linears"],
+                        p["relation_pri"], p["relation_att"], p["relation_msg"], p["skip"])
+    h.backward(gout.double().cpu())
+    tol = dict(rtol=2e-2, atol=2e-2)
+    close(out, h, "hgt bf16-table out", **tol)
+    err = (out.double().cpu() - h).abs().max() / h.abs().max()
+    assert float(err) > 1e-5, "bf16 storage should be visible in the output: is the bf16 path running?"
+    close(x.grad, x64.grad, "hgt bf16-table grad x", **tol)
+    assert x.grad.dtype == torch.float32
+    for layer, p in zip(model.layers, ps):
+        for k, v in layer.named_parameters():
+            assert v.grad.dtype == torch.float32
+            close(v.grad, p[k].grad, f"hgt bf16-table grad {k}", **tol)

@@ -58,10 +58,13 @@ def run(rank, profile=False):
         with tprofile(activities=[ProfilerActivity.CUDA]) as prof:
             step()
             torch.cuda.synchronize()
-        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=12, max_name_column_width=60), flush=True)
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=22, max_name_column_width=60), flush=True)
     return ms
 
 
-times = [run(r) for r in range(world)]
-worst = max(range(world), key=lambda r: times[r])
-run(worst, profile=True)
+if len(sys.argv) > 4 and sys.argv[4] == "one":   # rank 0 only, with the kernel table
+    run(0, profile=True)
+else:
+    times = [run(r) for r in range(world)]
+    worst = max(range(world), key=lambda r: times[r])
+    run(worst, profile=True)
