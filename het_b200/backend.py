@@ -161,6 +161,32 @@ class RgnnInnerProductNodeCompactAndNode(th.autograd.Function):
         return None, None, None, None, None, grad_left, grad_right, None
 
 
+class RgnnInnerProductNodeCompactAndNodeBinarySearch(th.autograd.Function):
+    """rgnn_layers_and_funcs.py:202-348 with CompactAsOfNodeKind::Enabled (1): the compact left row of
+    an edge is found by binary search of its col node in the relation's sorted unique list."""
+
+    @staticmethod
+    def forward(ctx, unique_rel_ptrs, unique_node_indices, rel_ptrs, eids, row_indices, col_indices,
+                left_node_compact_data, right_node_vectors, ret):
+        ctx.save_for_backward(unique_rel_ptrs, unique_node_indices, rel_ptrs, eids, row_indices, col_indices,
+                              left_node_compact_data, right_node_vectors)
+        ctx.mark_dirty(ret)
+        K.rgnn_inner_product_right_node_separatecoo(
+            {"unique_srcs_and_dests_rel_ptrs": unique_rel_ptrs, "unique_srcs_and_dests_node_indices": unique_node_indices},
+            1, rel_ptrs, eids, row_indices, col_indices, left_node_compact_data, right_node_vectors, ret)
+        return ret
+
+    @staticmethod
+    def backward(ctx, gradout):
+        up, un, rel_ptrs, eids, row_indices, col_indices, left, right = ctx.saved_tensors
+        grad_left = th.zeros_like(left, memory_format=th.contiguous_format)
+        grad_right = th.zeros_like(right, memory_format=th.contiguous_format)
+        K.backward_inner_product_right_node_separatecoo(
+            {"unique_srcs_and_dests_rel_ptrs": up, "unique_srcs_and_dests_node_indices": un}, 1, rel_ptrs, eids,
+            row_indices, col_indices, left, right, gradout.contiguous(), grad_left, grad_right)
+        return None, None, None, None, None, None, grad_left, grad_right, None
+
+
 def rgnn_inner_product_right_node(graph, left_side_data, right_node_vectors, compact_as_of_node_kind,
                                   left_mapper_suffix=None):
     """rgnn_layers_and_funcs.py:498-530. Kind 0: left is per-edge; kind 2: left is compact
@@ -175,8 +201,16 @@ def rgnn_inner_product_right_node(graph, left_side_data, right_node_vectors, com
             uniq["inverse_idx" + (left_mapper_suffix or "_col")], coo["rel_ptrs"], coo["eids"],
             coo["row_indices"], coo["col_indices"], left_side_data.contiguous(),
             right_node_vectors.contiguous(), ret)
+    if compact_as_of_node_kind == 1:
+        uniq = graph.get_separate_unique_node_indices_single_sided()
+        sfx = left_mapper_suffix or "_col"
+        ret = th.empty([coo["eids"].numel(), right_node_vectors.size(1)], dtype=right_node_vectors.dtype,
+                       device=right_node_vectors.device)
+        return RgnnInnerProductNodeCompactAndNodeBinarySearch.apply(
+            uniq["rel_ptrs" + sfx], uniq["node_indices" + sfx], coo["rel_ptrs"], coo["eids"], coo["row_indices"],
+            coo["col_indices"], left_side_data.contiguous(), right_node_vectors.contiguous(), ret)
     if compact_as_of_node_kind != 0:
-        raise NotImplementedError("CompactAsOfNodeKind 1 (binary search) for the inner product")
+        raise NotImplementedError("CompactAsOfNodeKind > 2 for the inner product")
     ret = th.empty([coo["eids"].numel(), right_node_vectors.size(1)], dtype=right_node_vectors.dtype,
                    device=right_node_vectors.device)
     return RgnnInnerProductEdgeAndNode.apply(
@@ -317,6 +351,111 @@ def hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(graph, message_
         outcsr["row_ptrs"], outcsr["col_indices"], outcsr["eids"], outcsr["rel_types"],
         unnormalized_attn_score.contiguous(), mu.contiguous(), ssum, t, norm,
         message_per_edge.contiguous(), new_h)
+
+
+# ----- hgt_layers_and_funcs.py:9-295, 430-520: the separate-COO (edge-parallel) HGT ops (P1) -----
+class HGTFullGraphHeteroAttentionOps(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, separate_coo_row_indices,
+                separate_coo_col_indices, separate_coo_eids, separate_coo_relptrs, applied_klinear_node_features,
+                applied_qlinear_node_features, attn_score_weight):
+        e = separate_coo_row_indices.numel()
+        unnormalized_attn_score = th.empty((e, attn_score_weight.size(1)), dtype=attn_score_weight.dtype,
+                                           device=attn_score_weight.device)
+        attn_score_inner_product = th.empty((e, attn_score_weight.size(1), attn_score_weight.size(3)),
+                                            dtype=attn_score_weight.dtype, device=attn_score_weight.device)
+        K.hgt_full_graph_hetero_attention_ops_coo(
+            separate_coo_row_indices, separate_coo_col_indices, separate_coo_eids, separate_coo_relptrs,
+            applied_klinear_node_features, applied_qlinear_node_features, attn_score_weight, attn_score_inner_product,
+            unnormalized_attn_score)
+        ctx.save_for_backward(incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, separate_coo_row_indices,
+                              separate_coo_col_indices, separate_coo_eids, separate_coo_relptrs,
+                              applied_klinear_node_features, applied_qlinear_node_features, attn_score_inner_product,
+                              attn_score_weight)
+        return unnormalized_attn_score
+
+    @staticmethod
+    def backward(ctx, grad_unnorm_attn_score):
+        (incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, row, col, eids, relptrs, k, q, inner,
+         w) = ctx.saved_tensors
+        grad_w = th.zeros_like(w, memory_format=th.contiguous_format)
+        grad_k = th.zeros_like(k, memory_format=th.contiguous_format)
+        grad_q = th.zeros_like(q, memory_format=th.contiguous_format)
+        K.backward_hgt_full_graph_hetero_attention_ops_coo(
+            incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, row, col, eids, relptrs, grad_w,
+            th.transpose(w, 2, 3).contiguous(), k, q, inner, grad_unnorm_attn_score.contiguous(), grad_k, grad_q)
+        return (None,) * 8 + (grad_k, grad_q, grad_w)
+
+
+def hgt_full_graph_hetero_attention_ops_coo(graph, weight, applied_klinear_node_features,
+                                            applied_qlinear_node_features):
+    """hgt_layers_and_funcs.py:430-455: score[e,h] = <k[src]·W[rel,h], q[dst]> in one op."""
+    incsr, coo = graph.get_in_csr(), graph.get_separate_coo_original()
+    return HGTFullGraphHeteroAttentionOps.apply(
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], coo["row_indices"],
+        coo["col_indices"], coo["eids"], coo["rel_ptrs"], applied_klinear_node_features.contiguous(),
+        applied_qlinear_node_features.contiguous(), weight.contiguous())
+
+
+class HGTFullGraphMessageCalcEdgeSoftmaxAndMessageMeanAggregationCOO(th.autograd.Function):
+    @staticmethod
+    def forward(ctx, incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, separate_coo_relptrs,
+                separate_coo_row_indices, separate_coo_col_indices, separate_coo_eids, message_generation_weights,
+                inputs, unnormalized_attn_score, edgesoftmax_sum_per_node, mu,
+                mu_softmax_applied_unnormalized_attn_score, normalized_attn_score, new_h):
+        ctx.mark_dirty(new_h)
+        K.hgt_full_graph_edge_softmax_ops_separate_coo(
+            separate_coo_row_indices, separate_coo_col_indices, separate_coo_eids, separate_coo_relptrs,
+            unnormalized_attn_score, mu, edgesoftmax_sum_per_node, mu_softmax_applied_unnormalized_attn_score,
+            normalized_attn_score)
+        K.hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo(
+            separate_coo_relptrs, separate_coo_eids, separate_coo_row_indices, separate_coo_col_indices, inputs,
+            message_generation_weights, normalized_attn_score, new_h)
+        ctx.save_for_backward(incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, separate_coo_relptrs,
+                              separate_coo_row_indices, separate_coo_col_indices, separate_coo_eids,
+                              message_generation_weights, inputs, unnormalized_attn_score, mu, normalized_attn_score,
+                              new_h)
+        return new_h
+
+    USE_CSR_ENORM_BACKWARD = False  # the reference exposes both (`if 0:` picks the COO one, :253-290)
+
+    @staticmethod
+    def backward(ctx, gradout):
+        (incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, relptrs, row, col, eids, w, inputs, attn, mu,
+         norm, new_h) = ctx.saved_tensors
+        grad_w = th.zeros_like(w, memory_format=th.contiguous_format)
+        grad_input = th.zeros_like(inputs, memory_format=th.contiguous_format)
+        grad_norm = th.zeros_like(norm, memory_format=th.contiguous_format)
+        grad_attn = th.zeros_like(attn, memory_format=th.contiguous_format)
+        grad_mu = th.zeros_like(mu, memory_format=th.contiguous_format)
+        K.backward_hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo(
+            relptrs, eids, row, col, inputs, th.transpose(w, 2, 3).contiguous(), norm, new_h, grad_input, grad_w,
+            grad_norm, gradout.contiguous())
+        if HGTFullGraphMessageCalcEdgeSoftmaxAndMessageMeanAggregationCOO.USE_CSR_ENORM_BACKWARD:
+            K.backward_hgt_full_graph_enorm_to_unnormalized_attn_score_csr(
+                incsr_row_ptrs, incsr_col_indices, incsr_eids, incsr_reltypes, attn, norm, grad_norm, mu, grad_attn,
+                grad_mu)
+        else:
+            sumprod = th.zeros([incsr_row_ptrs.shape[0] - 1, attn.shape[1]], dtype=norm.dtype, device=norm.device)
+            K.backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo(
+                row, col, eids, relptrs, attn, norm, grad_norm, mu, grad_attn, grad_mu, sumprod)
+        return (None,) * 8 + (grad_w, grad_input, grad_attn, None, grad_mu, None, None, None)
+
+
+def hgt_full_graph_message_calc_edge_softmax_and_message_mean_aggregation_coo(
+        message_generation_weights, inputs, graph, mu, unnormalized_attn_score):
+    """hgt_layers_and_funcs.py:457-518: edge softmax over the COO + (typed linear fused with the
+    attention-weighted aggregation)."""
+    incsr, coo = graph.get_in_csr(), graph.get_separate_coo_original()
+    n, h = graph.get_num_nodes(), mu.size(1)
+    new_h = th.empty((n, h, message_generation_weights.size(3)), dtype=inputs.dtype, device=inputs.device)
+    ssum = th.empty((n, h), dtype=inputs.dtype, device=inputs.device)
+    t = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    norm = th.empty_like(unnormalized_attn_score, memory_format=th.contiguous_format)
+    return HGTFullGraphMessageCalcEdgeSoftmaxAndMessageMeanAggregationCOO.apply(
+        incsr["row_ptrs"], incsr["col_indices"], incsr["eids"], incsr["rel_types"], coo["rel_ptrs"],
+        coo["row_indices"], coo["col_indices"], coo["eids"], message_generation_weights.contiguous(),
+        inputs.contiguous(), unnormalized_attn_score.contiguous(), ssum, mu.contiguous(), t, norm, new_h)
 
 
 # ----- hetb200 extensions: compact-as-of-node (direct indexing) forms of the in-CSR ops -----

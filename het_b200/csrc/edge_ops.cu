@@ -1007,7 +1007,8 @@ __global__ void __launch_bounds__(kThreads)
                             const float *__restrict__ el,
                             const float *__restrict__ er,
                             float *__restrict__ sum,
-                            float *__restrict__ exp_out, int H, float slope) {
+                            float *__restrict__ exp_out, int H, float slope,
+                            const int64_t *__restrict__ elidx, const int64_t *__restrict__ eridx) {
   const int64_t total = E * H;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (int64_t t = (int64_t)blockIdx.x * kThreads + threadIdx.x; t < total;
@@ -1016,7 +1017,9 @@ __global__ void __launch_bounds__(kThreads)
     const int h = (int)(t % H);
     const int64_t e = __ldg(eids + i);
     const int64_t d = __ldg(col_idx + i);
-    const float w = leaky_exp(__ldg(el + e * H + h) + __ldg(er + e * H + h), slope);
+    // compact-as-of-node: el / er rows given per COO position (NULL: the edge id)
+    const int64_t ea = elidx ? __ldg(elidx + i) : e, eb = eridx ? __ldg(eridx + i) : e;
+    const float w = leaky_exp(__ldg(el + ea * H + h) + __ldg(er + eb * H + h), slope);
     exp_out[e * H + h] = w;
     atomicAdd(sum + d * H + h, w);
   }
@@ -1030,7 +1033,7 @@ __global__ void __launch_bounds__(kThreads)
                               const float *__restrict__ feat,
                               const float *__restrict__ sum,
                               const float *__restrict__ exp_in,
-                              float *__restrict__ ret, int H, int hw) {
+                              float *__restrict__ ret, int H, int hw, const int64_t *__restrict__ fidx) {
   constexpr int GROUPS = kThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -1041,7 +1044,7 @@ __global__ void __launch_bounds__(kThreads)
     const int64_t d = __ldg(col_idx + i);
     const float sd = __ldg(sum + d * H + h);
     const float a = sd != 0.f ? __ldg(exp_in + e * H + h) / sd : 0.f;
-    const float4 fv = ldcs4(feat + e * D + 4 * l);
+    const float4 fv = fidx ? ldg4(feat + __ldg(fidx + i) * D + 4 * l) : ldcs4(feat + e * D + 4 * l);
     red_add4(ret + d * D + 4 * l,
              make_float4(a * fv.x, a * fv.y, a * fv.z, a * fv.w));
   }
@@ -1407,10 +1410,12 @@ extern "C" int hetb_rgat_fwd_coo(const int64_t *col_idx, const int64_t *eids,
                                  const float *feat, const float *el,
                                  const float *er, float *sum, float *exp_out,
                                  float *ret, int H, int F, float slope,
-                                 void *stream) {
+                                 const hetb_compact_idx *cidx, void *stream) {
   HETB_CHECK_ARG(num_nodes >= 0 && num_edges >= 0);
   if (num_nodes == 0) return HETB_OK;
   HETB_CHECK_ARG(sum && ret);
+  const hetb_compact_idx none = {nullptr, nullptr, nullptr};
+  const hetb_compact_idx ci = cidx ? *cidx : none;
   const int lpr = lanes_per_row(H, F);
   if (!lpr) return HETB_EUNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1424,12 +1429,12 @@ extern "C" int hetb_rgat_fwd_coo(const int64_t *col_idx, const int64_t *eids,
   const int grid1 = edge_grid(num_edges * H, kThreads);
   rgat_coo_exp_sum_kernel<<<grid1, kThreads, 0, st>>>(col_idx, eids, num_edges,
                                                       el, er, sum, exp_out, H,
-                                                      slope);
+                                                      slope, ci.el_idx, ci.er_idx);
   HETB_LAUNCH_OK();
   const int grid2 = edge_grid(num_edges, kThreads / lpr);
   DISPATCH_LPR(lpr, (rgat_coo_aggregate_kernel<L><<<grid2, kThreads, 0, st>>>(
                         col_idx, eids, num_edges, feat, sum, exp_out, ret, H,
-                        F / 4)));
+                        F / 4, ci.feat_idx)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

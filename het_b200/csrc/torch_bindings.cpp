@@ -68,6 +68,18 @@ void not_implemented(const char *op) {
               "hot path implemented by hetb200");
 }
 
+Tensor compact_index_by_position(const char *op, const Tensor &node, const int64_t *rel_of_pos, const int64_t *rel_ptrs,
+                                 int64_t num_rels, const Tensor &unique_rel_ptrs, const Tensor &unique_nodes);
+
+// row id of every CSR position (CSR -> COO row expansion)
+Tensor expand_rows(const char *op, const Tensor &row_ptr, int64_t num_edges) {
+  Tensor rows = at::empty({num_edges}, row_ptr.options());
+  check_rc(hetb_expand_row_ptr(i64(row_ptr, op, "row_ptr"), row_ptr.numel() - 1, num_edges, rows.data_ptr<int64_t>(),
+                               stream_of(row_ptr)),
+           op);
+  return rows;
+}
+
 // ---------------------------------------------------------------- misc ---
 void build_debug_info() { std::printf("%s\n", hetb_build_info()); }
 int64_t hetb200_launch_count() { return hetb_launch_count(); }
@@ -245,14 +257,23 @@ void rgnn_inner_product_right_node_separatecoo(
     Tensor &row_indices, Tensor &col_indices, Tensor &left_side_data,
     Tensor &right_node_vectors, Tensor &edge_inner_product) {
   const char *op = "rgnn_inner_product_right_node_separatecoo";
-  (void)rel_ptrs; (void)col_indices;
   // kind 0: per-edge left data; kind 2 (EnabledWithDirectIndexing): compact left rows addressed
-  // through args["edata_idx_to_inverse_idx"]; kind 1 (binary search in the unique lists) is not built
-  if (kind != 0 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
+  // through args["edata_idx_to_inverse_idx"]; kind 1 (Enabled): the compact row of (relation, col
+  // node) found by binary search in the unique lists (InnerProductEdgeParallel.cu.h:36-56)
+  if (kind != 0 && kind != 1 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
   const int64_t *left_idx = nullptr;
+  Tensor searched;
   if (kind == 2) {
     TORCH_CHECK(args.contains("edata_idx_to_inverse_idx"), op, ": kind 2 needs args[edata_idx_to_inverse_idx]");
     left_idx = i64(args.at("edata_idx_to_inverse_idx"), op, "edata_idx_to_inverse_idx");
+  } else if (kind == 1) {
+    c10::cuda::CUDAGuard g1(edge_inner_product.device());
+    Tensor by_pos = compact_index_by_position(op, col_indices, nullptr, i64(rel_ptrs, op, "rel_ptrs"),
+                                              rel_ptrs.numel() - 1, args.at("unique_srcs_and_dests_rel_ptrs"),
+                                              args.at("unique_srcs_and_dests_node_indices"));
+    searched = at::empty_like(by_pos);
+    searched.index_put_({eids}, by_pos);  // the kernel addresses the map by edge id
+    left_idx = searched.data_ptr<int64_t>();
   }
   TORCH_CHECK(right_node_vectors.dim() == 3, op,
               ": right_node_vectors must be [N,H,F]");
@@ -274,12 +295,20 @@ void backward_inner_product_right_node_separatecoo(
     Tensor &right_node_vectors, Tensor &grad_inner_product,
     Tensor &grad_left_side_data, Tensor &grad_right_node_vectors) {
   const char *op = "backward_inner_product_right_node_separatecoo";
-  (void)rel_ptrs; (void)col_indices;
-  if (kind != 0 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
+  if (kind != 0 && kind != 1 && kind != 2) check_rc(HETB_EUNSUPPORTED, op);
   const int64_t *left_idx = nullptr;
+  Tensor searched;
   if (kind == 2) {
     TORCH_CHECK(args.contains("edata_idx_to_inverse_idx"), op, ": kind 2 needs args[edata_idx_to_inverse_idx]");
     left_idx = i64(args.at("edata_idx_to_inverse_idx"), op, "edata_idx_to_inverse_idx");
+  } else if (kind == 1) {
+    c10::cuda::CUDAGuard g1(grad_inner_product.device());
+    Tensor by_pos = compact_index_by_position(op, col_indices, nullptr, i64(rel_ptrs, op, "rel_ptrs"),
+                                              rel_ptrs.numel() - 1, args.at("unique_srcs_and_dests_rel_ptrs"),
+                                              args.at("unique_srcs_and_dests_node_indices"));
+    searched = at::empty_like(by_pos);
+    searched.index_put_({eids}, by_pos);
+    left_idx = searched.data_ptr<int64_t>();
   }
   const int H = (int)right_node_vectors.size(1), F = (int)right_node_vectors.size(2);
   c10::cuda::CUDAGuard guard(grad_inner_product.device());
@@ -304,21 +333,30 @@ void relational_fused_gat_csr(Tensor &incsr_row_ptr, Tensor &incsr_col_indices,
                               Tensor &ret, double slope,
                               bool compact_as_of_node) {
   const char *op = "relational_fused_gat_csr";
-  (void)incsr_col_indices; (void)incsr_reltypes; (void)unique_rel_ptrs;
-  (void)unique_node_indices;
-  // the binary-search compact form (unique lists) is not built; the direct-indexing form is
-  // hetb200_relational_fused_gat_csr_compact below
-  if (compact_as_of_node) check_rc(HETB_EUNSUPPORTED, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(feat_src) / H);
   c10::cuda::CUDAGuard guard(ret.device());
+  // CompactAsOfNodeFlag (CompactAsOfNodeKind::Enabled, RGATOps.inc.h:251-277): feat_src / el / er hold
+  // one row per (relation, unique node) of the double-sided list; the row of a position is found by
+  // binary search (kernel_enums.h:96-119), here once per call into position-aligned index arrays.
+  hetb_compact_idx ci = {nullptr, nullptr, nullptr};
+  Tensor src_idx, dst_idx;
+  if (compact_as_of_node) {
+    Tensor dst = expand_rows(op, incsr_row_ptr, incsr_eids.numel());
+    src_idx = compact_index_by_position(op, incsr_col_indices, i64(incsr_reltypes, op, "incsr_reltypes"), nullptr, 0,
+                                        unique_rel_ptrs, unique_node_indices);
+    dst_idx = compact_index_by_position(op, dst, i64(incsr_reltypes, op, "incsr_reltypes"), nullptr, 0,
+                                        unique_rel_ptrs, unique_node_indices);
+    ci.feat_idx = ci.el_idx = src_idx.data_ptr<int64_t>();
+    ci.er_idx = dst_idx.data_ptr<int64_t>();
+  }
   check_rc(hetb_rgat_fwd_csr(i64(incsr_row_ptr, op, "incsr_row_ptr"),
                              i64(incsr_eids, op, "incsr_eids"),
                              incsr_row_ptr.numel() - 1, incsr_eids.numel(),
                              f32(feat_src, op, "feat_src"), f32(el, op, "el"),
                              f32(er, op, "er"), f32w(sum, op, "sum"),
                              f32w(exp, op, "exp"), f32w(ret, op, "ret"), H, F,
-                             (float)slope, nullptr, stream_of(ret)),
+                             (float)slope, compact_as_of_node ? &ci : nullptr, stream_of(ret)),
            op);
 }
 
@@ -391,12 +429,22 @@ void backward_relational_fused_gat_csr(
     Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope,
     bool compact_as_of_node) {
   const char *op = "backward_relational_fused_gat_csr";
-  (void)outcsr_row_ptr; (void)outcsr_reltypes; (void)unique_rel_ptrs;
-  (void)unique_node_indices;
-  if (compact_as_of_node) check_rc(HETB_EUNSUPPORTED, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(feat_src) / H);
   c10::cuda::CUDAGuard guard(gradout.device());
+  // CompactAsOfNodeFlag: out-CSR rows are sources; the gradients of compact rows are summed over
+  // their edges, so grad_feat_src / grad_el / grad_er must arrive zero-filled (as the reference's do)
+  hetb_compact_idx ci = {nullptr, nullptr, nullptr};
+  Tensor src_idx, dst_idx;
+  if (compact_as_of_node) {
+    Tensor src = expand_rows(op, outcsr_row_ptr, outcsr_eids.numel());
+    src_idx = compact_index_by_position(op, src, i64(outcsr_reltypes, op, "outcsr_reltypes"), nullptr, 0,
+                                        unique_rel_ptrs, unique_node_indices);
+    dst_idx = compact_index_by_position(op, outcsr_col_indices, i64(outcsr_reltypes, op, "outcsr_reltypes"), nullptr, 0,
+                                        unique_rel_ptrs, unique_node_indices);
+    ci.feat_idx = ci.el_idx = src_idx.data_ptr<int64_t>();
+    ci.er_idx = dst_idx.data_ptr<int64_t>();
+  }
   check_rc(hetb_rgat_bwd(i64(outcsr_col_indices, op, "outcsr_col_indices"),
                          i64(outcsr_eids, op, "outcsr_eids"),
                          outcsr_eids.numel(), f32(feat_src, op, "feat_src"),
@@ -405,9 +453,46 @@ void backward_relational_fused_gat_csr(
                          f32(ret, op, "ret"), f32(gradout, op, "gradout"),
                          f32w(grad_feat_src, op, "grad_feat_src"),
                          f32w(grad_el, op, "grad_el"),
-                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, nullptr,
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, compact_as_of_node ? &ci : nullptr,
                          stream_of(gradout)),
            op);
+}
+
+// Compact rows of every COO position for the compact kinds of the separate-COO RGAT ops
+// (RGATOps.inc.h:170-245 dict keys): kind 1 one double-sided list, binary search; kind 3 dual lists
+// (row / col), binary search; kind 4 dual direct maps by edge id; kind 2 one direct map by edge id
+// (the reference then addresses source AND destination rows with it: kernel_enums.h:116-118).
+struct CooCompact {
+  Tensor src, dst;
+  hetb_compact_idx ci{nullptr, nullptr, nullptr};
+};
+CooCompact coo_compact_indices(const char *op, int64_t kind, TensorDict &args, Tensor &eids, Tensor &rel_ptrs,
+                               Tensor &row_indices, Tensor &col_indices) {
+  CooCompact c;
+  if (kind == 0) return c;
+  const int64_t *rp = i64(rel_ptrs, op, "rel_ptrs");
+  const int64_t R = rel_ptrs.numel() - 1;
+  if (kind == 1) {
+    Tensor up = args.at("unique_srcs_and_dests_rel_ptrs"), un = args.at("unique_srcs_and_dests_node_indices");
+    c.src = compact_index_by_position(op, row_indices, nullptr, rp, R, up, un);
+    c.dst = compact_index_by_position(op, col_indices, nullptr, rp, R, up, un);
+  } else if (kind == 3) {
+    c.src = compact_index_by_position(op, row_indices, nullptr, rp, R, args.at("unique_srcs_and_dests_rel_ptrs"),
+                                      args.at("unique_srcs_and_dests_node_indices_row"));
+    c.dst = compact_index_by_position(op, col_indices, nullptr, rp, R, args.at("unique_srcs_and_dests_rel_ptrs_col"),
+                                      args.at("unique_srcs_and_dests_node_indices_col"));
+  } else if (kind == 4) {
+    c.src = args.at("edata_idx_to_inverse_idx_row").index({eids}).contiguous();
+    c.dst = args.at("edata_idx_to_inverse_idx_col").index({eids}).contiguous();
+  } else if (kind == 2) {
+    c.src = args.at("edata_idx_to_inverse_idx").index({eids}).contiguous();
+    c.dst = c.src;
+  } else {
+    check_rc(HETB_EUNSUPPORTED, op);
+  }
+  c.ci.feat_idx = c.ci.el_idx = i64(c.src, op, "compact source index");
+  c.ci.er_idx = i64(c.dst, op, "compact destination index");
+  return c;
 }
 
 // OpExport/RGATOps.inc.h:170-245
@@ -418,17 +503,16 @@ void relational_fused_gat_separate_coo(Tensor &eids, Tensor &rel_ptrs,
                                        Tensor &sum, Tensor &exp, Tensor &ret,
                                        double slope) {
   const char *op = "relational_fused_gat_separate_coo";
-  (void)rel_ptrs; (void)row_indices; (void)args;
-  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(feat_src) / H);
   c10::cuda::CUDAGuard guard(ret.device());
+  CooCompact cc = coo_compact_indices(op, kind, args, eids, rel_ptrs, row_indices, col_indices);
   check_rc(hetb_rgat_fwd_coo(i64(col_indices, op, "col_indices"),
                              i64(eids, op, "eids"), ret.size(0), eids.numel(),
                              f32(feat_src, op, "feat_src"), f32(el, op, "el"),
                              f32(er, op, "er"), f32w(sum, op, "sum"),
                              f32w(exp, op, "exp"), f32w(ret, op, "ret"), H, F,
-                             (float)slope, stream_of(ret)),
+                             (float)slope, kind ? &cc.ci : nullptr, stream_of(ret)),
            op);
 }
 
@@ -439,11 +523,11 @@ void backward_relational_fused_gat_separate_coo(
     Tensor &sum, Tensor &exp, Tensor &ret, Tensor &gradout,
     Tensor &grad_feat_src, Tensor &grad_el, Tensor &grad_er, double slope) {
   const char *op = "backward_relational_fused_gat_separate_coo";
-  (void)rel_ptrs; (void)row_indices; (void)args;
-  if (kind != 0) check_rc(HETB_EUNSUPPORTED, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(feat_src) / H);
   c10::cuda::CUDAGuard guard(gradout.device());
+  // compact kinds: the gradients of compact rows are summed, grad_* must arrive zero-filled
+  CooCompact cc = coo_compact_indices(op, kind, args, eids, rel_ptrs, row_indices, col_indices);
   check_rc(hetb_rgat_bwd(i64(col_indices, op, "col_indices"),
                          i64(eids, op, "eids"), eids.numel(),
                          f32(feat_src, op, "feat_src"), f32(el, op, "el"),
@@ -452,7 +536,7 @@ void backward_relational_fused_gat_separate_coo(
                          f32(gradout, op, "gradout"),
                          f32w(grad_feat_src, op, "grad_feat_src"),
                          f32w(grad_el, op, "grad_el"),
-                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, nullptr,
+                         f32w(grad_er, op, "grad_er"), H, F, (float)slope, kind ? &cc.ci : nullptr,
                          stream_of(gradout)),
            op);
 }
@@ -951,6 +1035,233 @@ void hetb200_rgat_fused_bwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &fe
            op);
 }
 
+// ------------------------------------------------- P1: separate-COO HGT ops ---
+// Same maths as the P0 ops in the reference's other slicing; built on the existing kernels
+// (typed linear + inner product / weighted scatter). Per-edge temporaries live only inside the call.
+
+// compact row of every COO position by binary search in per-relation sorted unique lists
+// (CompactAsOfNodeKind::Enabled / EnabledWithDualList): position-aligned int64 tensor
+Tensor compact_index_by_position(const char *op, const Tensor &node, const int64_t *rel_of_pos, const int64_t *rel_ptrs,
+                                 int64_t num_rels, const Tensor &unique_rel_ptrs, const Tensor &unique_nodes) {
+  Tensor idx = at::empty({node.numel()}, node.options());
+  Tensor missing = at::zeros({1}, node.options().dtype(at::kInt));
+  check_rc(hetb_compact_index(i64(node, op, "node indices"), rel_of_pos, rel_ptrs, num_rels, node.numel(),
+                              i64(unique_rel_ptrs, op, "unique_srcs_and_dests_rel_ptrs"),
+                              i64(unique_nodes, op, "unique_srcs_and_dests_node_indices"), idx.data_ptr<int64_t>(),
+                              missing.data_ptr<int>(), stream_of(node)),
+           op);
+  return idx;
+}
+
+// OpExport/HGTOpsEdgeParallel.inc.h:95-158: inner[eid] = k[row]·W_att[rel]; score[eid,h] = <inner[eid,h,:], q[col,h,:]>
+void hgt_full_graph_hetero_attention_ops_coo(Tensor &row_indices, Tensor &col_indices, Tensor &eids, Tensor &rel_ptrs,
+                                             Tensor &applied_klinear_node_features,
+                                             Tensor &applied_qlinear_node_features, Tensor &attn_score_weight,
+                                             Tensor &attn_score_inner_product, Tensor &unnormalized_attn_score) {
+  const char *op = "hgt_full_graph_hetero_attention_ops_coo";
+  TORCH_CHECK(attn_score_weight.dim() == 4, op, ": attn_score_weight must be [R,H,in,out]");
+  const int H = (int)attn_score_weight.size(1), K = (int)attn_score_weight.size(2), N = (int)attn_score_weight.size(3);
+  c10::cuda::CUDAGuard guard(unnormalized_attn_score.device());
+  void *st = stream_of(unnormalized_attn_score);
+  check_rc(hetb_segment_mm(f32(applied_klinear_node_features, op, "k"), i64(row_indices, op, "row_indices"), H,
+                           f32(attn_score_weight, op, "attn_score_weight"),
+                           f32w(attn_score_inner_product, op, "attn_score_inner_product"), i64(eids, op, "eids"), H,
+                           i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, K, N, 0, st),
+           op);
+  check_rc(hetb_inner_product_fwd(i64(eids, op, "eids"), i64(col_indices, op, "col_indices"), nullptr, eids.numel(),
+                                  f32(attn_score_inner_product, op, "attn_score_inner_product"),
+                                  f32(applied_qlinear_node_features, op, "q"),
+                                  f32w(unnormalized_attn_score, op, "unnormalized_attn_score"), H, N, st),
+           op);
+}
+
+// OpExport/HGTOpsEdgeParallel.inc.h:166-293. grad_k / grad_q / grad_attn_score_weight arrive zero-filled.
+void backward_hgt_full_graph_hetero_attention_ops_coo(
+    Tensor &incsr_row_ptr, Tensor &incsr_col_indices, Tensor &incsr_eids, Tensor &incsr_reltypes,
+    Tensor &row_indices, Tensor &col_indices, Tensor &eids, Tensor &rel_ptrs, Tensor &grad_attn_score_weight,
+    Tensor &attn_score_weight_transposed, Tensor &applied_klinear_node_features,
+    Tensor &applied_qlinear_node_features, Tensor &attn_score_inner_product, Tensor &grad_unnorm_attn_score,
+    Tensor &grad_k, Tensor &grad_q) {
+  const char *op = "backward_hgt_full_graph_hetero_attention_ops_coo";
+  (void)incsr_row_ptr; (void)incsr_col_indices; (void)incsr_eids; (void)incsr_reltypes;
+  const int H = (int)attn_score_weight_transposed.size(1), N = (int)attn_score_weight_transposed.size(2),
+            K = (int)attn_score_weight_transposed.size(3);
+  c10::cuda::CUDAGuard guard(grad_k.device());
+  void *st = stream_of(grad_k);
+  Tensor grad_inner = at::empty_like(attn_score_inner_product);
+  check_rc(hetb_inner_product_bwd(i64(eids, op, "eids"), i64(col_indices, op, "col_indices"), nullptr, eids.numel(),
+                                  f32(attn_score_inner_product, op, "attn_score_inner_product"),
+                                  f32(applied_qlinear_node_features, op, "q"),
+                                  f32(grad_unnorm_attn_score, op, "grad_unnorm_attn_score"),
+                                  grad_inner.data_ptr<float>(), f32w(grad_q, op, "grad_q"), H, N, st),
+           op);
+  check_rc(hetb_segment_mm(grad_inner.data_ptr<float>(), i64(eids, op, "eids"), H,
+                           f32(attn_score_weight_transposed, op, "attn_score_weight_transposed"),
+                           f32w(grad_k, op, "grad_k"), i64(row_indices, op, "row_indices"), H,
+                           i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, N, K, 1, st),
+           op);
+  check_rc(hetb_segment_mm_grad_w(f32(applied_klinear_node_features, op, "k"), i64(row_indices, op, "row_indices"), H,
+                                  grad_inner.data_ptr<float>(), i64(eids, op, "eids"), H,
+                                  f32w(grad_attn_score_weight, op, "grad_attn_score_weight"),
+                                  i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, K, N, st),
+           op);
+}
+
+// OpExport/HGTOpsEdgeParallel.inc.h:18-32
+void hgt_full_graph_edge_softmax_ops_separate_coo(Tensor &row_indices, Tensor &col_indices, Tensor &eids,
+                                                  Tensor &rel_ptrs, Tensor &unnormalized_attn_score, Tensor &mu,
+                                                  Tensor &edgesoftmax_sum_per_node,
+                                                  Tensor &mu_softmax_applied_unnormalized_attn_score,
+                                                  Tensor &normalized_attn_score) {
+  const char *op = "hgt_full_graph_edge_softmax_ops_separate_coo";
+  (void)row_indices;
+  const int H = (int)mu.size(1);
+  c10::cuda::CUDAGuard guard(normalized_attn_score.device());
+  check_rc(hetb_hgt_edge_softmax_fwd_coo(
+               i64(col_indices, op, "col_indices"), i64(eids, op, "eids"), nullptr, i64(rel_ptrs, op, "rel_ptrs"),
+               rel_ptrs.numel() - 1, edgesoftmax_sum_per_node.size(0), eids.numel(),
+               f32(unnormalized_attn_score, op, "unnormalized_attn_score"), f32(mu, op, "mu"),
+               f32w(edgesoftmax_sum_per_node, op, "edgesoftmax_sum_per_node"),
+               f32w(mu_softmax_applied_unnormalized_attn_score, op, "mu_softmax_applied_unnormalized_attn_score"),
+               f32w(normalized_attn_score, op, "normalized_attn_score"), H, stream_of(normalized_attn_score)),
+           op);
+}
+
+// OpExport/HGTOpsEdgeParallel.inc.h:33-92: out[col] = sum_e edge_norm[eid,h] * (input[row]·W[rel])
+void hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo(
+    Tensor &rel_ptrs, Tensor &eids, Tensor &row_indices, Tensor &col_indices, Tensor &node_feat_input,
+    Tensor &weights, Tensor &edge_norm, Tensor &node_feat_output) {
+  const char *op = "hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo";
+  const int H = (int)weights.size(1), K = (int)weights.size(2), N = (int)weights.size(3);
+  c10::cuda::CUDAGuard guard(node_feat_output.device());
+  void *st = stream_of(node_feat_output);
+  Tensor msg = at::empty({eids.numel(), H, N}, node_feat_output.options());
+  check_rc(hetb_segment_mm(f32(node_feat_input, op, "node_feat_input"), i64(row_indices, op, "row_indices"), H,
+                           f32(weights, op, "weights"), msg.data_ptr<float>(), i64(eids, op, "eids"), H,
+                           i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, K, N, 0, st),
+           op);
+  check_rc(hetb_weighted_scatter_coo(i64(col_indices, op, "col_indices"), i64(eids, op, "eids"), eids.numel(),
+                                     node_feat_output.size(0), msg.data_ptr<float>(), f32(edge_norm, op, "edge_norm"),
+                                     f32w(node_feat_output, op, "node_feat_output"), H, N, st),
+           op);
+}
+
+// OpExport/HGTOpsEdgeParallel.inc.h:295-370. grad_* arrive zero-filled.
+void backward_hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo(
+    Tensor &rel_ptrs, Tensor &eids, Tensor &row_indices, Tensor &col_indices, Tensor &node_feat_input,
+    Tensor &weights_transposed, Tensor &edge_norm, Tensor &node_feat_output, Tensor &grad_node_feat_input,
+    Tensor &grad_weights, Tensor &grad_edge_norm, Tensor &grad_node_feat_output) {
+  const char *op = "backward_hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo";
+  (void)node_feat_output;
+  const int H = (int)weights_transposed.size(1), N = (int)weights_transposed.size(2), K = (int)weights_transposed.size(3);
+  c10::cuda::CUDAGuard guard(grad_node_feat_input.device());
+  void *st = stream_of(grad_node_feat_input);
+  Tensor weights = weights_transposed.transpose(2, 3).contiguous();
+  Tensor msg = at::empty({eids.numel(), H, N}, grad_node_feat_output.options());
+  check_rc(hetb_segment_mm(f32(node_feat_input, op, "node_feat_input"), i64(row_indices, op, "row_indices"), H,
+                           weights.data_ptr<float>(), msg.data_ptr<float>(), i64(eids, op, "eids"), H,
+                           i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, K, N, 0, st),
+           op);
+  // grad_edge_norm[eid,h] = <gout[col,h,:], msg[eid,h,:]>
+  check_rc(hetb_inner_product_fwd(i64(eids, op, "eids"), i64(col_indices, op, "col_indices"), nullptr, eids.numel(),
+                                  msg.data_ptr<float>(), f32(grad_node_feat_output, op, "grad_node_feat_output"),
+                                  f32w(grad_edge_norm, op, "grad_edge_norm"), H, N, st),
+           op);
+  // grad_msg[eid] = edge_norm[eid,h] * gout[col]  (overwrites msg)
+  check_rc(hetb_hgt_aggregate_bwd(i64(col_indices, op, "col_indices"), i64(eids, op, "eids"), eids.numel(),
+                                  f32(edge_norm, op, "edge_norm"), f32(grad_node_feat_output, op, "grad_node_feat_output"),
+                                  msg.data_ptr<float>(), H, N, nullptr, nullptr, st),
+           op);
+  check_rc(hetb_segment_mm(msg.data_ptr<float>(), i64(eids, op, "eids"), H,
+                           f32(weights_transposed, op, "weights_transposed"),
+                           f32w(grad_node_feat_input, op, "grad_node_feat_input"), i64(row_indices, op, "row_indices"), H,
+                           i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, N, K, 1, st),
+           op);
+  check_rc(hetb_segment_mm_grad_w(f32(node_feat_input, op, "node_feat_input"), i64(row_indices, op, "row_indices"), H,
+                                  msg.data_ptr<float>(), i64(eids, op, "eids"), H, f32w(grad_weights, op, "grad_weights"),
+                                  i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1, eids.numel(), H, K, N, st),
+           op);
+}
+
+// OpExport/HGTOps.inc.h:283-340 (in-CSR: rows = destinations)
+void backward_hgt_full_graph_enorm_to_unnormalized_attn_score_csr(
+    Tensor &incsr_row_ptr, Tensor &incsr_col_indices, Tensor &incsr_eids, Tensor &incsr_reltypes,
+    Tensor &unnormalized_attn_score, Tensor &normalized_attn_score, Tensor &grad_normalized_attn_score, Tensor &mu,
+    Tensor &grad_unnormalized_attn_score, Tensor &grad_mu) {
+  const char *op = "backward_hgt_full_graph_enorm_to_unnormalized_attn_score_csr";
+  (void)incsr_col_indices;
+  const int H = (int)mu.size(1);
+  const int64_t n = incsr_row_ptr.numel() - 1, e = incsr_eids.numel();
+  c10::cuda::CUDAGuard guard(grad_mu.device());
+  void *st = stream_of(grad_mu);
+  Tensor dst = at::empty({e}, incsr_eids.options());
+  check_rc(hetb_expand_row_ptr(i64(incsr_row_ptr, op, "incsr_row_ptr"), n, e, dst.data_ptr<int64_t>(), st), op);
+  Tensor scratch = at::empty({n * H}, mu.options());
+  check_rc(hetb_hgt_enorm_to_unnormalized_bwd(
+               dst.data_ptr<int64_t>(), i64(incsr_eids, op, "incsr_eids"), i64(incsr_reltypes, op, "incsr_reltypes"),
+               nullptr, mu.size(0), n, e, f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
+               f32(normalized_attn_score, op, "normalized_attn_score"),
+               f32(grad_normalized_attn_score, op, "grad_normalized_attn_score"), f32(mu, op, "mu"),
+               scratch.data_ptr<float>(), f32w(grad_unnormalized_attn_score, op, "grad_unnormalized_attn_score"),
+               f32w(grad_mu, op, "grad_mu"), H, st),
+           op);
+}
+
+// OpExport/HGTOps.inc.h:598-650 (separate COO: col_indices = destinations)
+void backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo(
+    Tensor &row_indices, Tensor &col_indices, Tensor &eids, Tensor &rel_ptrs, Tensor &unnormalized_attn_score,
+    Tensor &normalized_attn_score, Tensor &grad_normalized_attn_score, Tensor &mu,
+    Tensor &grad_unnormalized_attn_score, Tensor &grad_mu, Tensor &sum_incoming_edges_product_softmax_score) {
+  const char *op = "backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo";
+  (void)row_indices;
+  const int H = (int)mu.size(1);
+  c10::cuda::CUDAGuard guard(grad_mu.device());
+  check_rc(hetb_hgt_enorm_to_unnormalized_bwd(
+               i64(col_indices, op, "col_indices"), i64(eids, op, "eids"), nullptr, i64(rel_ptrs, op, "rel_ptrs"),
+               rel_ptrs.numel() - 1, sum_incoming_edges_product_softmax_score.size(0), eids.numel(),
+               f32(unnormalized_attn_score, op, "unnormalized_attn_score"),
+               f32(normalized_attn_score, op, "normalized_attn_score"),
+               f32(grad_normalized_attn_score, op, "grad_normalized_attn_score"), f32(mu, op, "mu"),
+               f32w(sum_incoming_edges_product_softmax_score, op, "sum_incoming_edges_product_softmax_score"),
+               f32w(grad_unnormalized_attn_score, op, "grad_unnormalized_attn_score"), f32w(grad_mu, op, "grad_mu"), H,
+               stream_of(grad_mu)),
+           op);
+}
+
+// OpExport/RGNNOps.inc.h:565-607: out[eid] = in[compact row of (relation, col node) of the edge]
+void rgnn_gather_compact_to_non_compact(TensorDict args, int64_t kind, Tensor &rel_ptrs, Tensor &eids,
+                                        Tensor &row_indices, Tensor &col_indices, Tensor &in_feat, Tensor &out_feat) {
+  const char *op = "rgnn_gather_compact_to_non_compact";
+  (void)row_indices;
+  c10::cuda::CUDAGuard guard(out_feat.device());
+  Tensor idx;  // position-aligned source row (undefined: the edge id itself)
+  if (kind == 2) {  // EnabledWithDirectIndexing: args[edata_idx_to_inverse_idx] is indexed by edge id
+    idx = args.at("edata_idx_to_inverse_idx").index({eids}).contiguous();
+  } else if (kind == 1) {  // Enabled: binary search of the col node in the relation's unique list
+    idx = compact_index_by_position(op, col_indices, nullptr, i64(rel_ptrs, op, "rel_ptrs"), rel_ptrs.numel() - 1,
+                                    args.at("unique_srcs_and_dests_rel_ptrs"),
+                                    args.at("unique_srcs_and_dests_node_indices"));
+  } else if (kind != 0) {
+    check_rc(HETB_EUNSUPPORTED, op);
+  }
+  check_rc(hetb_gather_rows(i64(eids, op, "eids"), idx.defined() ? idx.data_ptr<int64_t>() : nullptr, eids.numel(),
+                            f32(in_feat, op, "in_feat"), f32w(out_feat, op, "out_feat"), xlen(in_feat),
+                            stream_of(out_feat)),
+           op);
+}
+
+// ------------------------------------------------- P2: registered, outside the hot path ---
+// Same arities as the reference's registrations (tensor arguments, trailing double where the
+// reference has one) so that a call reaches the message below instead of a schema error.
+void seastar_rgcn_layer0_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6) { not_implemented("seastar_rgcn_layer0_csr"); }
+void seastar_backward_rgcn_layer0_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7) { not_implemented("seastar_backward_rgcn_layer0_csr"); }
+void seastar_rgcn_layer1_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7) { not_implemented("seastar_rgcn_layer1_csr"); }
+void seastar_backward_rgcn_layer1_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, Tensor &a9, Tensor &a10) { not_implemented("seastar_backward_rgcn_layer1_csr"); }
+void seastar_rgcn_layer1_coo(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7) { not_implemented("seastar_rgcn_layer1_coo"); }
+void seastar_backward_rgcn_layer1_coo(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, Tensor &a9, Tensor &a10) { not_implemented("seastar_backward_rgcn_layer1_coo"); }
+void fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, double slope) { not_implemented("fused_gat_csr"); }
+void backward_fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, Tensor &a9, Tensor &a10, Tensor &a11, Tensor &a12, double slope) { not_implemented("backward_fused_gat_csr"); }
+
 // ---------------------------------------------------------------- loss ---
 // hetb200 extension: fused log_softmax + nll_loss (sum / denom) of the training step.
 void hetb200_softmax_cross_entropy(Tensor &logits, Tensor &labels, double denom, Tensor &lse, Tensor &loss) {
@@ -1177,6 +1488,30 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_backward_hgt_fused_softmax_aggregation_csr", hetb200_backward_hgt_fused_softmax_aggregation_csr);
   m.def("hetb200_backward_hgt_fused_attention_aggregation_csr",
         hetb200_backward_hgt_fused_attention_aggregation_csr);
+  // P2 names: registered for interface compatibility, outside the hot path; calling one
+  // raises with the op's name (OpExport/RGCNOps.inc.h:681-699, GATOps.inc.h:130-135,
+  // UtilityAndPlayground.inc.h:101-108)
+  m.def("seastar_rgcn_layer1_coo", seastar_rgcn_layer1_coo);
+  m.def("seastar_backward_rgcn_layer1_coo", seastar_backward_rgcn_layer1_coo);
+  m.def("seastar_rgcn_layer1_csr", seastar_rgcn_layer1_csr);
+  m.def("seastar_backward_rgcn_layer1_csr", seastar_backward_rgcn_layer1_csr);
+  m.def("seastar_rgcn_layer0_csr", seastar_rgcn_layer0_csr);
+  m.def("seastar_backward_rgcn_layer0_csr", seastar_backward_rgcn_layer0_csr);
+  m.def("fused_gat_csr", fused_gat_csr);
+  m.def("backward_fused_gat_csr", backward_fused_gat_csr);
+  // P1 ops (OpExport/HGTOpsEdgeParallel.inc.h:380-400, HGTOps.inc.h:666-673, RGNNOps.inc.h:1202)
+  m.def("hgt_full_graph_hetero_attention_ops_coo", hgt_full_graph_hetero_attention_ops_coo);
+  m.def("backward_hgt_full_graph_hetero_attention_ops_coo", backward_hgt_full_graph_hetero_attention_ops_coo);
+  m.def("hgt_full_graph_edge_softmax_ops_separate_coo", hgt_full_graph_edge_softmax_ops_separate_coo);
+  m.def("hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo",
+        hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo);
+  m.def("backward_hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo",
+        backward_hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo);
+  m.def("backward_hgt_full_graph_enorm_to_unnormalized_attn_score_csr",
+        backward_hgt_full_graph_enorm_to_unnormalized_attn_score_csr);
+  m.def("backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo",
+        backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo);
+  m.def("rgnn_gather_compact_to_non_compact", rgnn_gather_compact_to_non_compact);
   m.def("hetb200_typed_linear_bf16out", hetb200_typed_linear_bf16out);
   m.def("hetb200_hgt_fused_fwd_plan", hetb200_hgt_fused_fwd_plan);
   m.def("hetb200_hgt_fused_bwd_plan", hetb200_hgt_fused_bwd_plan);

@@ -93,9 +93,25 @@ class HetGraph:
         return self.rel_src_type, self.rel_dst_type
 
     def get_separate_unique_node_indices(self):
-        # the double-sided lists (binary-search compact kinds) are not built; the
-        # non-compact ops ignore these tensors.
-        return {"rel_ptrs": self._empty, "node_indices": self._empty}
+        """Double-sided compact-as-of-node lists (reference:
+        generate_separate_unique_node_indices_for_each_etype,
+        hrt/python/utils_lite/mydgl_graph_methods.py:72-157): per relation the sorted unique nodes
+        that appear as source OR destination, back to back; the binary-search compact kinds
+        (CompactAsOfNodeKind::Enabled) locate the row of a (relation, node) pair in them. Needs one
+        id space for sources and destinations (not built on a destination shard)."""
+        if getattr(self, "_unique_double_sided", None) is None:
+            assert self.num_src_nodes == self.num_nodes, "double-sided lists need one node id space"
+            coo = self.separate_coo
+            dev = coo["rel_ptrs"].device
+            counts = coo["rel_ptrs"][1:] - coo["rel_ptrs"][:-1]
+            rel_of_edge = torch.repeat_interleave(torch.arange(self.num_rels, device=dev), counts)
+            n = self.num_nodes
+            uniq = torch.unique(torch.cat([rel_of_edge * n + coo["row_indices"], rel_of_edge * n + coo["col_indices"]]),
+                                sorted=True)
+            bounds = torch.arange(self.num_rels + 1, device=dev, dtype=torch.int64) * n
+            self._unique_double_sided = {"rel_ptrs": torch.searchsorted(uniq, bounds).contiguous(),
+                                         "node_indices": (uniq % n).contiguous()}
+        return self._unique_double_sided
 
     def get_separate_unique_node_indices_single_sided(self):
         """Compact-as-of-node lists, one side at a time (reference:

@@ -277,8 +277,24 @@ class HET_RGCNModel(nn.Module):
 class HET_HGTLayerHetero(nn.Module):
     def __init__(self, num_ntypes, num_rels, in_dim, out_dim, num_heads=1, dropout=0.0,
                  compact_as_of_node_flag=False, compact_direct_indexing_flag=True,
-                 fused_attention_aggregation_flag=False, linear_reorder_flag=False, bf16_tables_flag=False):
+                 fused_attention_aggregation_flag=False, linear_reorder_flag=False, bf16_tables_flag=False,
+                 hgt_fused_attn_score_flag=False, fused_message_mean_aggregation_flag=False,
+                 multiply_among_weights_first_flag=False):
         super().__init__()
+        # the reference's separate-COO op slicings (hrt/python/HGT/models.py:170-174, 251-259): the
+        # attention score as one op (k[src].W_att[r] and the inner product with q[dst]; note this op
+        # contracts W_att as k.W.q^T where the two-op path computes q.W.k^T), and edge softmax + typed
+        # linear + aggregation over the COO. Per-edge (non-compact) paths.
+        self.hgt_fused_attn_score_flag = hgt_fused_attn_score_flag
+        self.fused_message_mean_aggregation_flag = fused_message_mean_aggregation_flag
+        # multiply_among_weights_first_flag (hrt/python/HGT/models.py:124-155): compose the node-type and
+        # relation weights once per step so that Q and V are never materialised. The reference composes
+        # them with view() calls that "do not transpose" (its own FIXME, :137) and takes v_linears of the
+        # destination type; hetb200 implements the optimisation's maths as linear_reorder_flag (compact
+        # path), which this flag turns on.
+        if multiply_among_weights_first_flag:
+            linear_reorder_flag = True
+            compact_as_of_node_flag = True
         # bf16 STORAGE of the gathered tables (k, W_att.q, W_msg.v): needs the compact + fused + reordered
         # path on one GPU; arithmetic, outputs and gradients stay fp32 (backend.HGTLayerCoreBF16Tables)
         self.bf16_tables_flag = bf16_tables_flag
@@ -349,8 +365,6 @@ class HET_HGTLayerHetero(nn.Module):
                  "separate_coo_eids": coo["eids"]}, w, x, False, 0)
 
         if self.compact_as_of_node_flag:
-            if not self.compact_direct_indexing_flag:
-                raise NotImplementedError("compact_as_of_node without direct indexing (binary search)")
             u = G.get_separate_unique_node_indices_single_sided()
             if self.bf16_tables_flag:
                 if not (reorder and gather is None and self.fused_attention_aggregation_flag and B.USE_EDGE_PLAN):
@@ -384,15 +398,24 @@ class HET_HGTLayerHetero(nn.Module):
                       else B.hgt_fused_attention_and_aggregation_csr_compact)
                 new_h = fn(G, attn_weight_dst_product_compact, k, message_compact, self.relation_pri / self.sqrt_dk)
             else:
-                attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k, 2, "_col")
+                # CompactAsOfNodeKind 2 (direct indexing) or 1 (binary search in the unique lists)
+                attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_compact, k,
+                                                             2 if self.compact_direct_indexing_flag else 1, "_col")
                 new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr_compact(
                     G, message_compact, attn_score, self.relation_pri / self.sqrt_dk)
         else:
-            attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
-            attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")
-            message_per_edge = mm(coo["row_indices"], self.relation_msg, v)
-            new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(
-                G, message_per_edge, attn_score, self.relation_pri / self.sqrt_dk)
+            if self.hgt_fused_attn_score_flag:
+                attn_score = B.hgt_full_graph_hetero_attention_ops_coo(G, self.relation_att, k, q)
+            else:
+                attn_weight_dst_product_per_edge = mm(coo["col_indices"], self.relation_att, q)
+                attn_score = B.rgnn_inner_product_right_node(G, attn_weight_dst_product_per_edge, k, 0, "_col")
+            if self.fused_message_mean_aggregation_flag:
+                new_h = B.hgt_full_graph_message_calc_edge_softmax_and_message_mean_aggregation_coo(
+                    self.relation_msg, v, G, self.relation_pri / self.sqrt_dk, attn_score)
+            else:
+                message_per_edge = mm(coo["row_indices"], self.relation_msg, v)
+                new_h = B.hgt_full_graph_edge_softmax_and_message_mean_aggregation_csr(
+                    G, message_per_edge, attn_score, self.relation_pri / self.sqrt_dk)
         new_h = B.rgnn_relational_matmul_no_scatter_gather_list(
             offs, th.sigmoid(self.skip) * self.a_linears, new_h.view(-1, self.out_dim))
         return new_h

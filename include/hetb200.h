@@ -162,6 +162,7 @@ int hetb_rgat_fwd_coo(const int64_t *col_idx, const int64_t *eids,
                       int64_t num_nodes, int64_t num_edges, const float *feat,
                       const float *el, const float *er, float *sum,
                       float *exp_out, float *ret, int H, int F, float slope,
+                      const hetb_compact_idx *cidx /* NULL: per-edge inputs; else rows per COO position */,
                       void *stream);
 
 /* For every edge position p (dst d = dst_idx[p], e = eids[p]):
@@ -414,6 +415,50 @@ int hetb_rgat_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_dst, const 
                              const float *el, const float *er, const float *lse, const float *ret,
                              const float *gout, float *gdotr_scratch, float *grad_feat, float *grad_el,
                              float *grad_er, int H, int F, float slope, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Separate-COO (edge-parallel) forms of the HGT ops and compact-index helpers (SURVEY.md §8a a13/a14,
+ * §8f N2/N4). The relation of COO position i is rel_of_pos[i] when given, else the segment of
+ * rel_ptrs[num_rels+1] that holds i (the relation-sorted separate COO).
+ * ---------------------------------------------------------------------- */
+
+/* hgt_full_graph_edge_softmax_ops_separate_coo (OpExport/HGTOpsEdgeParallel.inc.h:18-32):
+ * t = exp(attn*mu[rel]), sum[dst] = sum t, norm = t / sum[dst]. Normalises over the in-edges of the
+ * DESTINATION (dst = the COO's col_indices); the reference's edge-parallel kernel keys the sum by
+ * row_indices (HGT/HGTForwardKernels.cu.h:619), documented quirk, not copied. t_out / norm_out may be NULL. */
+int hetb_hgt_edge_softmax_fwd_coo(const int64_t *dst, const int64_t *eids, const int64_t *rel_of_pos,
+                                  const int64_t *rel_ptrs, int64_t num_rels, int64_t num_nodes, int64_t num_edges,
+                                  const float *attn, const float *mu, float *sum, float *t_out, float *norm_out,
+                                  int H, void *stream);
+
+/* ret[dst[i],h,:] = sum_i w[eids[i],h] * feat[eids[i],h,:] (ret is zero-filled here): the aggregation
+ * half of hgt_full_graph_fused_message_calc_and_mean_aggregation_separate_coo
+ * (OpExport/HGTOpsEdgeParallel.inc.h:33-92; the typed linear half is hetb_segment_mm). */
+int hetb_weighted_scatter_coo(const int64_t *dst, const int64_t *eids, int64_t num_edges, int64_t num_dst,
+                              const float *feat, const float *w, float *ret, int H, int F, void *stream);
+
+/* backward_hgt_full_graph_enorm_to_unnormalized_attn_score_{csr,separate_coo}
+ * (OpExport/HGTOps.inc.h:283-340, 598-650): softmax Jacobian from grad of the normalised score to
+ * grad of the raw score and of mu. dst[i] = destination of position i. grad_mu must arrive
+ * zero-filled; sumprod_scratch [num_nodes, H] is zeroed here. */
+int hetb_hgt_enorm_to_unnormalized_bwd(const int64_t *dst, const int64_t *eids, const int64_t *rel_of_pos,
+                                       const int64_t *rel_ptrs, int64_t num_rels, int64_t num_nodes,
+                                       int64_t num_edges, const float *attn, const float *norm,
+                                       const float *grad_norm, const float *mu, float *sumprod_scratch,
+                                       float *grad_attn, float *grad_mu, int H, void *stream);
+
+/* rgnn_gather_compact_to_non_compact (OpExport/RGNNOps.inc.h:449-600):
+ * out[eids[i], :] = in[idx ? idx[i] : eids[i], :], rows of xlen floats (xlen % 4 == 0). */
+int hetb_gather_rows(const int64_t *eids, const int64_t *idx, int64_t num_edges, const float *in, float *out,
+                     int64_t xlen, void *stream);
+
+/* find_relational_compact_as_of_node_index with binary search (kernel_enums.h:96-119) for every
+ * position: out_idx[i] = row of (relation of i, node[i]) in the per-relation sorted unique lists, -1
+ * (and *missing_counter += 1) when the node is not listed. Turns CompactAsOfNodeKind::Enabled /
+ * EnabledWithDualList into the direct-indexing form the edge kernels take. */
+int hetb_compact_index(const int64_t *node, const int64_t *rel_of_pos, const int64_t *rel_ptrs, int64_t num_rels,
+                       int64_t num_edges, const int64_t *unique_rel_ptrs, const int64_t *unique_nodes,
+                       int64_t *out_idx, int *missing_counter, void *stream);
 
 /* out[c] = sum_i x[i, c] for a row-major [num_rows, num_cols] matrix: the gradient of the layer
  * bias (h + b; hrt/python/RGAT/models.py:264-278, RGCN/RGCN.py:343-344). num_cols % 4 == 0. */
