@@ -62,6 +62,7 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary lines (rgat_bgs, bf16 table storage)")
     ap.add_argument("--no-compact", dest="compact", action="store_false",
                     help="turn off the reference's compact_as_of_node_flag (default on: X.W_r is computed once "
                          "per unique (relation, node) pair instead of once per edge; same outputs)")
@@ -482,6 +483,45 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
 
 
 # ---------------------------------------------------------------------------
+def _sha1(path):
+    import hashlib
+    try:
+        with open(path, "rb") as f:
+            return hashlib.sha1(f.read()).hexdigest()
+    except OSError:
+        return None
+
+
+def _secondary_lines(args, dev, torch):
+    """Named secondary measurements beside the headline (resident arm only, same timing rules):
+    configs[1] (RGAT on the BGS-shaped graph) and the headline workload with bf16 table storage."""
+    from het_b200 import graphs
+    from het_b200.train import FullGraphTrainer
+    out = {}
+    for name, (kind, shape, heads, layers, kw) in {
+            "rgat_bgs (configs[1]) f32": ("rgat", "bgs", 1, 1, {}),
+            "hgt_mag (configs[2]) bf16 storage of the gathered tables, fp32 arithmetic (parity bar 2e-2)":
+                ("hgt", "mag", 4, 2, {"bf16_tables": True})}.items():
+        coo = graphs.SHAPES[shape](scale=1.0)
+        tr = FullGraphTrainer(kind, coo, dev, heads=heads, layers=layers, cuda_graph=not args.no_graph,
+                              compact_as_of_node=True, fused=True, **kw)
+        for _ in range(max(3, args.warmup)):
+            tr.step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(args.steps):
+            tr.step()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / args.steps
+        out[name] = {"ms_per_step": ms, "value": coo.num_edges * layers / (ms * 1e-3), "unit": UNIT,
+                     "edges_per_step": coo.num_edges * layers}
+        del tr
+        torch.cuda.empty_cache()
+    return out
+
+
 def _peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -725,11 +765,19 @@ def main():
         legs = (kernel_rooflines_compact if (args.compact or kind == "rgcn") else kernel_rooflines)(trainer, peak, peak_src)
         # measured DRAM traffic per launch (one ncu --set full capture, profiles/ncu_traffic.json), only for
         # the configuration it was captured on; "dram_frac" = that traffic / this run's kernel time / peak
+        # The file is stamped with the sha1 of the kernel sources it was captured from; a stale stamp
+        # (kernels edited since the capture) drops the traffic figures instead of reporting old ones.
+        traffic, traffic_note = {}, None
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-                traffic = json.load(f).get(args.workload, {}) if (scale == 1.0 and args.compact and args.fused) else {}
+                tj = json.load(f)
+            stale = [fn for fn, h in tj.get("source_sha1", {}).items() if _sha1(os.path.join(ROOT, fn)) != h]
+            if stale or not tj.get("source_sha1"):
+                traffic_note = f"profiles/ncu_traffic.json is stale for {stale or 'all sources (no stamp)'}: traffic omitted"
+            elif scale == 1.0 and args.compact and args.fused and world == 1 and not args.bf16_tables:
+                traffic = tj.get(args.workload, {})
         except (OSError, ValueError):
-            traffic = {}
+            traffic_note = "profiles/ncu_traffic.json missing"
         for d in legs:
             if d["kernel"] in traffic:
                 d["traffic"] = int(traffic[d["kernel"]])
@@ -737,7 +785,23 @@ def main():
         top = max(legs, key=lambda d: d["ms"])
         line["roofline"] = {k: top.get(k) for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "dram_frac",
                                                      "kernel", "ms", "algorithmic_bytes", "peak_source")}
+        if traffic_note:
+            line["roofline"]["traffic_note"] = traffic_note
         line["kernels"] = legs
+    # step-level roofline: SURVEY.md 8(d) "fused layer" compulsory bytes (layer input and output once, int32
+    # src / rel per edge, row pointers, the saved score per edge and head, log-sum-exp per node and head;
+    # backward = forward + the output gradient read and the input gradient written) over the step time
+    H_, D_ = heads, 64
+    n_l, e_l = trainer.n_local, trainer.num_edges_local
+    fwd_b = 2 * n_l * D_ * 4 + e_l * 8 + (n_l + 1) * 4 + e_l * H_ * 4 + n_l * H_ * 4
+    bwd_b = fwd_b + 2 * n_l * D_ * 4
+    step_bytes = layers * (fwd_b + bwd_b)
+    line["step_roofline"] = {"bound": "hbm", "algorithmic_bytes_per_gpu": int(step_bytes),
+                             "achieved": round(step_bytes / (ms_step * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
+                             "frac": round(step_bytes / (ms_step * 1e-3) / 1e9 / peak, 4),
+                             "note": "SURVEY 8(d) fused-layer compulsory bytes x layers x (fwd + bwd) / ms_per_step"}
+    if world == 1 and args.workload == "hgt_mag" and not args.no_extra and not args.bf16_tables:
+        line["extra"] = _secondary_lines(args, dev, torch)
     if world == 1 and not args.no_cpu_baseline:
         trainer = None
         torch.cuda.empty_cache()

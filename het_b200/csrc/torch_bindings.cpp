@@ -1262,6 +1262,49 @@ void seastar_backward_rgcn_layer1_coo(Tensor &a0, Tensor &a1, Tensor &a2, Tensor
 void fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, double slope) { not_implemented("fused_gat_csr"); }
 void backward_fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, Tensor &a9, Tensor &a10, Tensor &a11, Tensor &a12, double slope) { not_implemented("backward_fused_gat_csr"); }
 
+// ------------------------------------------------------------ optimizer / weight composition ---
+void hetb200_adam_bump_step(Tensor &step) {
+  const char *op = "hetb200_adam_bump_step";
+  c10::cuda::CUDAGuard guard(step.device());
+  check_rc(hetb_adam_bump_step(f32w(step, op, "step"), stream_of(step)), op);
+}
+
+void hetb200_adam_step(Tensor &param, Tensor &grad, Tensor &exp_avg, Tensor &exp_avg_sq, Tensor &step, double lr,
+                       double beta1, double beta2, double eps) {
+  const char *op = "hetb200_adam_step";
+  TORCH_CHECK(grad.numel() == param.numel() && exp_avg.numel() == param.numel() && exp_avg_sq.numel() == param.numel(),
+              op, ": tensor sizes differ");
+  c10::cuda::CUDAGuard guard(param.device());
+  check_rc(hetb_adam_step(f32w(param, op, "param"), f32(grad, op, "grad"), f32w(exp_avg, op, "exp_avg"),
+                          f32w(exp_avg_sq, op, "exp_avg_sq"), param.numel(), f32(step, op, "step"), (float)lr,
+                          (float)beta1, (float)beta2, (float)eps, stream_of(param)),
+           op);
+}
+
+// lin [T, 1, in, H*dk] (a typed-linear weight), rel [R, H, dk, dk] -> out [R, 1, in, H*dk]
+void hetb200_compose_weights(Tensor &lin, Tensor &type_of_rel, Tensor &rel, Tensor &out) {
+  const char *op = "hetb200_compose_weights";
+  const int H = (int)rel.size(1), dk = (int)rel.size(2), in_dim = (int)lin.size(2);
+  TORCH_CHECK(lin.size(3) == (int64_t)H * dk && rel.size(3) == dk && out.numel() == rel.size(0) * in_dim * H * dk, op,
+              ": shapes do not match");
+  c10::cuda::CUDAGuard guard(out.device());
+  check_rc(hetb_compose_weights_fwd(f32(lin, op, "lin"), i64(type_of_rel, op, "type_of_rel"), f32(rel, op, "rel"),
+                                    f32w(out, op, "out"), rel.size(0), in_dim, H, dk, stream_of(out)),
+           op);
+}
+
+void hetb200_backward_compose_weights(Tensor &gradout, Tensor &lin, Tensor &type_of_rel, Tensor &rel, Tensor &grad_lin,
+                                      Tensor &grad_rel) {
+  const char *op = "hetb200_backward_compose_weights";
+  const int H = (int)rel.size(1), dk = (int)rel.size(2), in_dim = (int)lin.size(2);
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_compose_weights_bwd(f32(gradout, op, "gradout"), f32(lin, op, "lin"),
+                                    i64(type_of_rel, op, "type_of_rel"), f32(rel, op, "rel"),
+                                    f32w(grad_lin, op, "grad_lin"), f32w(grad_rel, op, "grad_rel"), rel.size(0), in_dim,
+                                    H, dk, stream_of(gradout)),
+           op);
+}
+
 // ---------------------------------------------------------------- loss ---
 // hetb200 extension: fused log_softmax + nll_loss (sum / denom) of the training step.
 void hetb200_softmax_cross_entropy(Tensor &logits, Tensor &labels, double denom, Tensor &lse, Tensor &loss) {
@@ -1512,6 +1555,10 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo",
         backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo);
   m.def("rgnn_gather_compact_to_non_compact", rgnn_gather_compact_to_non_compact);
+  m.def("hetb200_adam_bump_step", hetb200_adam_bump_step);
+  m.def("hetb200_adam_step", hetb200_adam_step);
+  m.def("hetb200_compose_weights", hetb200_compose_weights);
+  m.def("hetb200_backward_compose_weights", hetb200_backward_compose_weights);
   m.def("hetb200_typed_linear_bf16out", hetb200_typed_linear_bf16out);
   m.def("hetb200_hgt_fused_fwd_plan", hetb200_hgt_fused_fwd_plan);
   m.def("hetb200_hgt_fused_bwd_plan", hetb200_hgt_fused_bwd_plan);

@@ -344,6 +344,8 @@ class HET_HGTLayerHetero(nn.Module):
             H, dk = self.num_heads, self.d_k
 
             def compose(lin, rel_w, types):  # [R, 1, in, out]: lin[type(r)] . blockdiag_h(rel_w[r, h])
+                if lin.is_cuda:
+                    return B.compose_weights(lin, types, rel_w)
                 w = th.einsum("rihd,rhde->rihe", lin[types, 0].view(-1, self.in_dim, H, dk), rel_w)
                 return w.reshape(-1, 1, self.in_dim, self.out_dim)
 

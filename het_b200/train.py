@@ -29,6 +29,46 @@ from .graphs import HeteroCOO
 from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel, HET_RGCNModel
 
 
+class HetbAdam:
+    """torch.optim.Adam's update (no weight decay, no amsgrad) as one hand-written kernel per tensor
+    (csrc/optim.cu), step count on the device so that the optimizer step is part of the captured step
+    graph. Same interface subset the trainer uses (step / zero_grad)."""
+
+    def __init__(self, params, lr=1e-2, betas=(0.9, 0.999), eps=1e-8):
+        from .kernels import K
+        self.K = K
+        self.params = [p for p in params]
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.state = {}
+        self.step_count = None
+
+    def _state(self, p):
+        if p not in self.state:
+            self.state[p] = (torch.zeros_like(p, memory_format=torch.contiguous_format),
+                             torch.zeros_like(p, memory_format=torch.contiguous_format))
+        return self.state[p]
+
+    @torch.no_grad()
+    def step(self):
+        live = [p for p in self.params if p.grad is not None]
+        if not live:
+            return
+        if self.step_count is None:
+            self.step_count = torch.zeros(1, dtype=torch.float32, device=live[0].device)
+        self.K.hetb200_adam_bump_step(self.step_count)
+        for p in live:
+            m, v = self._state(p)
+            g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+            self.K.hetb200_adam_step(p, g, m, v, self.step_count, self.lr, self.betas[0], self.betas[1], self.eps)
+
+    def zero_grad(self, set_to_none=True):
+        for p in self.params:
+            if set_to_none:
+                p.grad = None
+            elif p.grad is not None:
+                p.grad.zero_()
+
+
 class FullGraphTrainer:
     def __init__(self, kind: str, coo: HeteroCOO, device, *, hidden=64, out_dim=64, heads=1,
                  layers=1, lr=1e-2, rank=0, world=1, group=None, cuda_graph=True, seed=0,
@@ -81,9 +121,8 @@ class FullGraphTrainer:
         self.labels_in = torch.zeros(self.n_local, dtype=torch.int64, device=self.device)
 
         cap = bool(cuda_graph)
-        self.opt_embed = torch.optim.Adam(list(self.model.parameters()) + list(self.embed.parameters()),
-                                          lr=lr, capturable=cap, fused=True)
-        self.opt_feat = torch.optim.Adam(list(self.model.parameters()), lr=lr, capturable=cap, fused=True)
+        self.opt_embed = HetbAdam(list(self.model.parameters()) + list(self.embed.parameters()), lr=lr)
+        self.opt_feat = HetbAdam(list(self.model.parameters()), lr=lr)
         self.cuda_graph = cap
         self._graphs = {}
         self._loss = {}

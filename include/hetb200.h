@@ -460,6 +460,27 @@ int hetb_compact_index(const int64_t *node, const int64_t *rel_of_pos, const int
                        int64_t num_edges, const int64_t *unique_rel_ptrs, const int64_t *unique_nodes,
                        int64_t *out_idx, int *missing_counter, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Optimizer step and weight composition of the full-graph trainer
+ * ---------------------------------------------------------------------- */
+
+/* Adam (torch.optim.Adam's update, no weight decay / amsgrad) over one fp32 tensor; the optimizer of
+ * HET_RGNN_train (hrt/python/RGNNUtils/RGNNUtils.py:291-345). `step` is a device float holding the
+ * step count (hetb_adam_bump_step adds 1), so the update is capturable in a CUDA graph. Pointers
+ * 16-byte aligned. */
+int hetb_adam_bump_step(float *step, void *stream);
+int hetb_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n, const float *step,
+                   float lr, float beta1, float beta2, float eps, void *stream);
+
+/* out[r, i, h*dk+e] = sum_d lin[type_of_rel[r], i, h*dk+d] * rel[r, h, d, e]: the per-relation composed
+ * weights of HGT's linear operator reordering (hrt/python/HGT/models.py:124-155). lin [T, in_dim, H*dk],
+ * rel [R, H, dk, dk], out [R, in_dim, H*dk]. The backward fills grad_rel and ADDS into grad_lin
+ * (zero-filled by the caller). */
+int hetb_compose_weights_fwd(const float *lin, const int64_t *type_of_rel, const float *rel, float *out, int64_t R,
+                             int in_dim, int H, int dk, void *stream);
+int hetb_compose_weights_bwd(const float *gout, const float *lin, const int64_t *type_of_rel, const float *rel,
+                             float *grad_lin, float *grad_rel, int64_t R, int in_dim, int H, int dk, void *stream);
+
 /* out[c] = sum_i x[i, c] for a row-major [num_rows, num_cols] matrix: the gradient of the layer
  * bias (h + b; hrt/python/RGAT/models.py:264-278, RGCN/RGCN.py:343-344). num_cols % 4 == 0. */
 int hetb_column_sum(const float *x, int64_t num_rows, int num_cols, float *out, void *stream);

@@ -175,3 +175,42 @@ def test_column_sum(cuda, rows, cols):
     out = torch.full((cols,), 7.0, device=cuda)  # must be overwritten, not accumulated into
     K.hetb200_column_sum(x, out)
     close(out, x.double().sum(0).cpu(), "column sum", rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(1000, 64), (7,), (3, 1, 64, 64), (4097,)])
+def test_hetb_adam_matches_torch_adam(cuda, shape):
+    """HetbAdam (csrc/optim.cu) against torch.optim.Adam over several steps with changing gradients."""
+    from het_b200.train import HetbAdam
+    torch.manual_seed(0)
+    p0 = torch.randn(*shape, device=cuda)
+    a = torch.nn.Parameter(p0.clone())
+    b = torch.nn.Parameter(p0.double().clone())
+    oa, ob = HetbAdam([a], lr=1e-2), torch.optim.Adam([b], lr=1e-2)
+    for step in range(5):
+        g = torch.randn(*shape, device=cuda) * (1 + step)
+        a.grad, b.grad = g.clone(), g.double()
+        oa.step()
+        ob.step()
+        close(a, b, f"parameter after step {step + 1}", rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,R,H,dk", [(4, 8, 4, 16), (3, 5, 1, 64), (2, 7, 2, 32)])
+def test_compose_weights(cuda, T, R, H, dk):
+    """hetb200_compose_weights (+ backward) against the einsum it replaces, in fp64."""
+    from het_b200 import backend as B
+    torch.manual_seed(R)
+    D = H * dk
+    lin = torch.randn(T, 1, 64, D, device=cuda, requires_grad=True)
+    rel = torch.randn(R, H, dk, dk, device=cuda, requires_grad=True)
+    types = torch.randint(0, T, (R,), device=cuda)
+    out = B.compose_weights(lin, types, rel)
+    gout = torch.randn_like(out)
+    out.backward(gout)
+    l64, r64 = lin.detach().double().cpu().requires_grad_(True), rel.detach().double().cpu().requires_grad_(True)
+    ref = torch.einsum("rihd,rhde->rihe", l64[types.cpu(), 0].view(-1, 64, H, dk), r64).reshape(-1, 1, 64, D)
+    ref.backward(gout.double().cpu())
+    close(out, ref, "composed weights")
+    close(lin.grad, l64.grad, "grad lin")
+    close(rel.grad, r64.grad, "grad rel")
