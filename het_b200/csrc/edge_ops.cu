@@ -7,16 +7,16 @@
 // with warp shuffles inside the group, and nothing is accumulated through
 // global atomics unless the op's index format forces it (COO scatter).
 //
-// Destination-parallel kernels (in-CSR) assign one lane group per destination
-// row for rows of up to kHeavyDegree in-edges; heavier rows (power-law hubs)
-// are queued in shared memory and processed afterwards by the whole CTA with
-// a shared-memory tree merge, so one hub does not serialise a lane group.
+// The in-CSR / out-CSR kernels here are edge-balanced walkers: a lane group owns a fixed chunk of
+// consecutive CSR positions whatever the degree distribution, rows inside a chunk are reduced in
+// registers, rows crossing chunks (power-law hubs) through vector reductions. They serve the
+// reference-named ops (int64 indices, the reference's exp / sum outputs, hence no max subtraction);
+// the benchmark's default path is the plan-based walkers of edge_plan.cu.
 #include "common.cuh"
 
 namespace hetb {
 
 constexpr int kThreads = 256;
-constexpr int kHeavyDegree = 256;
 
 __device__ __forceinline__ float leaky_exp(float x, float slope) {
   return __expf(x > 0.f ? x : slope * x);

@@ -6,12 +6,15 @@ to the reference repo root). Only ``tests/``, ``__graft_entry__.smoke()`` and
 ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs may import this
 package; the product (``het_b200``) never does.
 
-Parity status: the reference ships NO golden vectors for these ops and its CUDA
-ops cannot be built in this image (needs glog, g++-9, cusp vs CUDA 12.9, and a
-GPU), so float parity is *unpinned by reference outputs*; it is pinned by
-(a) torch.autograd.gradcheck of these functions in fp64 and (b) analytical
-properties (softmax rows sum to 1). The integer converters ARE pinned: see
-``oracle/converters_ref.py`` and ``oracle/_ref`` (reference MyHyb.h compiled).
+Parity status: PINNED to the reference's own CUDA kernels. The reference ships no golden
+vectors for these ops and its CMake build cannot run here (glog, g++-9, cusp vs CUDA 12.9), but
+its kernel templates are header-only: ``oracle/ref_kernels_shim.cu`` instantiates them exactly as
+the reference's op wrappers do, ``oracle/build_ref.py`` compiles that for sm_100a into
+``oracle/_ref/libhet_ref_kernels.so``, and ``tests/test_gpu_reference_kernels.py`` checks on the
+B200 that reference kernel == this oracle == hetb200 for every function below (with the
+reference's defects — found by running it — either modelled or avoided, and named in the tests).
+The integer converters are pinned the same way: ``oracle/converters_ref.py`` and ``oracle/_ref``
+(reference MyHyb.h compiled).
 
 Documented deviations from reference bugs (oracle follows the maths):
   * inner-product backward sums into grad_right (reference stores, last edge wins:
