@@ -717,14 +717,23 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             return float(t.item())
 
-        ag = t_coll(lambda: dist.all_gather_into_tensor(full, part))
-        rs = t_coll(lambda: dist.reduce_scatter_tensor(part, full))
+        if plan.exchange == "halo":   # the all-to-all of the referenced rows and its reverse
+            sb = torch.randn(sum(plan.send_counts), 64, device=dev)
+            rb = torch.empty(sum(plan.recv_counts), 64, device=dev)
+            ag = t_coll(lambda: dist.all_to_all_single(rb, sb, plan.recv_counts, plan.send_counts))
+            rs = t_coll(lambda: dist.all_to_all_single(sb, rb, plan.send_counts, plan.recv_counts))
+            nbytes = (sum(plan.recv_counts) - plan.recv_counts[rank]) * 64 * 4
+            del sb, rb
+        else:
+            ag = t_coll(lambda: dist.all_gather_into_tensor(full, part))
+            rs = t_coll(lambda: dist.reduce_scatter_tensor(part, full))
+            nbytes = plan.max_rows * (world - 1) * 64 * 4
         ar = t_coll(lambda: dist.all_reduce(flat))
-        nbytes = plan.max_rows * (world - 1) * 64 * 4
-        comm = {"all_gather_ms": ag, "reduce_scatter_ms": rs, "weight_all_reduce_ms": ar,
+        comm = {"exchange": plan.exchange, "forward_exchange_ms": ag, "backward_exchange_ms": rs, "weight_all_reduce_ms": ar,
+                "rows_read_of_all_rows": round(plan.num_gathered_rows / (plan.max_rows * world), 4),
                 "rows_per_rank": int(plan.max_rows), "bytes_received_per_rank_per_collective": int(nbytes),
-                "all_gather_GBps_in": nbytes / (ag * 1e-3) / 1e9, "reduce_scatter_GBps_in": nbytes / (rs * 1e-3) / 1e9,
-                "collectives_per_step": {"all_gather": layers, "reduce_scatter": layers, "all_reduce": 1},
+                "forward_GBps_in": nbytes / (ag * 1e-3) / 1e9, "backward_GBps": nbytes / (rs * 1e-3) / 1e9,
+                "collectives_per_step": {"forward_exchange": layers, "backward_exchange": layers, "all_reduce": 1},
                 "comm_ms_per_step_if_fully_exposed": layers * (ag + rs) + ar,
                 "edges_per_rank": [int(v) for v in plan.edges_per_rank]}
         del part, full, flat

@@ -864,7 +864,10 @@ def hgt_reordered_projections_sharded(g, h, hg, k_linears, w_att, w_msg):
     """k_linears [T, 1, in, out] -> one weight per segment of the gathered layout: per rank the T
     types and a zero matrix for its padding rows."""
     u = g.get_separate_unique_node_indices_single_sided()
-    k_ext = th.cat([k_linears, th.zeros_like(k_linears[:1])], 0).repeat(g.world, 1, 1, 1)
+    if g.gathered_segments_per_rank == k_linears.size(0) + 1:   # all-gather layout: T types + padding per rank
+        k_ext = th.cat([k_linears, th.zeros_like(k_linears[:1])], 0).repeat(g.world, 1, 1, 1)
+    else:                                                        # halo table: T types per owner block
+        k_ext = k_linears.repeat(g.world, 1, 1, 1)
     return HGTReorderedProjectionsSharded.apply(
         g.gathered_type_ptrs, u["rel_ptrs_col"], u["node_indices_col"], u["rel_ptrs_row"], u["node_indices_row"],
         h.contiguous(), hg.contiguous(), k_ext.contiguous(), w_att.contiguous(), w_msg.contiguous())

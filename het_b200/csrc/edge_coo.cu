@@ -181,6 +181,31 @@ __global__ void __launch_bounds__(kCThreads)
   }
 }
 
+// out[i, :] = in[idx[i], :]  /  dst[idx[i], :] += src[i, :]: pack and unpack of the multi-GPU halo exchange
+__global__ void __launch_bounds__(kCThreads)
+    rows_gather_kernel(const int64_t *__restrict__ idx, int64_t n, const float *__restrict__ in,
+                       float *__restrict__ out, int xlen4) {
+  const int64_t total = n * xlen4;
+  const int64_t stride = (int64_t)gridDim.x * kCThreads;
+  for (int64_t t = (int64_t)blockIdx.x * kCThreads + threadIdx.x; t < total; t += stride) {
+    const int64_t i = t / xlen4;
+    const int c = (int)(t % xlen4);
+    stcs4(out + t * 4, ldg4(in + (__ldg(idx + i) * xlen4 + c) * 4));
+  }
+}
+
+__global__ void __launch_bounds__(kCThreads)
+    rows_scatter_add_kernel(const int64_t *__restrict__ idx, int64_t n, const float *__restrict__ src,
+                            float *__restrict__ dst, int xlen4) {
+  const int64_t total = n * xlen4;
+  const int64_t stride = (int64_t)gridDim.x * kCThreads;
+  for (int64_t t = (int64_t)blockIdx.x * kCThreads + threadIdx.x; t < total; t += stride) {
+    const int64_t i = t / xlen4;
+    const int c = (int)(t % xlen4);
+    red_add4(dst + (__ldg(idx + i) * xlen4 + c) * 4, ldcs4(src + t * 4));
+  }
+}
+
 static int coo_grid(int64_t n) {
   const int64_t need = ceil_div64(n, kCThreads);
   const int64_t cap = (int64_t)kNumSMs * 16;
@@ -293,6 +318,28 @@ extern "C" int hetb_compact_index(const int64_t *node, const int64_t *rel_of_pos
                  num_rels <= INT32_MAX);
   compact_index_kernel<<<coo_grid(num_edges), kCThreads, 0, (cudaStream_t)stream>>>(
       node, rel_of_pos, rel_ptrs, (int)num_rels, num_edges, unique_rel_ptrs, unique_nodes, out_idx, missing_counter);
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+extern "C" int hetb_rows_gather(const int64_t *idx, int64_t n, const float *in, float *out, int64_t xlen, void *stream) {
+  HETB_CHECK_ARG(n >= 0 && xlen > 0);
+  if (n == 0) return HETB_OK;
+  HETB_CHECK_ARG(idx && in && out);
+  if (xlen % 4) return HETB_EUNSUPPORTED;
+  rows_gather_kernel<<<coo_grid(n * (xlen / 4)), kCThreads, 0, (cudaStream_t)stream>>>(idx, n, in, out, (int)(xlen / 4));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+extern "C" int hetb_rows_scatter_add(const int64_t *idx, int64_t n, const float *src, float *dst, int64_t xlen,
+                                     void *stream) {
+  HETB_CHECK_ARG(n >= 0 && xlen > 0);
+  if (n == 0) return HETB_OK;
+  HETB_CHECK_ARG(idx && src && dst);
+  if (xlen % 4) return HETB_EUNSUPPORTED;
+  rows_scatter_add_kernel<<<coo_grid(n * (xlen / 4)), kCThreads, 0, (cudaStream_t)stream>>>(idx, n, src, dst,
+                                                                                           (int)(xlen / 4));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

@@ -1262,6 +1262,25 @@ void seastar_backward_rgcn_layer1_coo(Tensor &a0, Tensor &a1, Tensor &a2, Tensor
 void fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, double slope) { not_implemented("fused_gat_csr"); }
 void backward_fused_gat_csr(Tensor &a0, Tensor &a1, Tensor &a2, Tensor &a3, Tensor &a4, Tensor &a5, Tensor &a6, Tensor &a7, Tensor &a8, Tensor &a9, Tensor &a10, Tensor &a11, Tensor &a12, double slope) { not_implemented("backward_fused_gat_csr"); }
 
+// ------------------------------------------------------------ halo exchange pack / unpack ---
+void hetb200_gather_rows(Tensor &idx, Tensor &in, Tensor &out) {
+  const char *op = "hetb200_gather_rows";
+  TORCH_CHECK(out.size(0) == idx.numel() && xlen(out) == xlen(in), op, ": shapes do not match");
+  c10::cuda::CUDAGuard guard(out.device());
+  check_rc(hetb_rows_gather(i64(idx, op, "idx"), idx.numel(), f32(in, op, "in"), f32w(out, op, "out"), xlen(in),
+                            stream_of(out)),
+           op);
+}
+
+void hetb200_scatter_add_rows(Tensor &idx, Tensor &src, Tensor &dst) {
+  const char *op = "hetb200_scatter_add_rows";
+  TORCH_CHECK(src.size(0) == idx.numel() && xlen(src) == xlen(dst), op, ": shapes do not match");
+  c10::cuda::CUDAGuard guard(dst.device());
+  check_rc(hetb_rows_scatter_add(i64(idx, op, "idx"), idx.numel(), f32(src, op, "src"), f32w(dst, op, "dst"), xlen(src),
+                                 stream_of(dst)),
+           op);
+}
+
 // ------------------------------------------------------------ optimizer / weight composition ---
 void hetb200_adam_bump_step(Tensor &step) {
   const char *op = "hetb200_adam_bump_step";
@@ -1555,6 +1574,8 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo",
         backward_hgt_full_graph_enorm_to_unnormalized_attn_score_separate_coo);
   m.def("rgnn_gather_compact_to_non_compact", rgnn_gather_compact_to_non_compact);
+  m.def("hetb200_gather_rows", hetb200_gather_rows);
+  m.def("hetb200_scatter_add_rows", hetb200_scatter_add_rows);
   m.def("hetb200_adam_bump_step", hetb200_adam_bump_step);
   m.def("hetb200_adam_step", hetb200_adam_step);
   m.def("hetb200_compose_weights", hetb200_compose_weights);

@@ -452,6 +452,11 @@ int hetb_hgt_enorm_to_unnormalized_bwd(const int64_t *dst, const int64_t *eids, 
 int hetb_gather_rows(const int64_t *eids, const int64_t *idx, int64_t num_edges, const float *in, float *out,
                      int64_t xlen, void *stream);
 
+/* out[i, :] = in[idx[i], :] and dst[idx[i], :] += src[i, :] (rows of xlen floats, xlen % 4 == 0): pack /
+ * unpack of the multi-GPU halo exchange (het_b200/parallel.py; the reference has no distributed path). */
+int hetb_rows_gather(const int64_t *idx, int64_t n, const float *in, float *out, int64_t xlen, void *stream);
+int hetb_rows_scatter_add(const int64_t *idx, int64_t n, const float *src, float *dst, int64_t xlen, void *stream);
+
 /* find_relational_compact_as_of_node_index with binary search (kernel_enums.h:96-119) for every
  * position: out_idx[i] = row of (relation of i, node[i]) in the per-relation sorted unique lists, -1
  * (and *missing_counter += 1) when the node is not listed. Turns CompactAsOfNodeKind::Enabled /

@@ -73,13 +73,13 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, exchange="all_gather"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from het_b200 import graphs, parallel
         coo = graphs.aifb_shaped(scale=0.2)
-        plan = parallel.make_shard(coo, rank, world)
+        plan = parallel.make_shard(coo, rank, world, exchange=exchange)
         torch.manual_seed(0)
         x_full = torch.randn(coo.num_nodes, 8, dtype=torch.float64)
         w = torch.randn(8, 4, dtype=torch.float64, requires_grad=True)
@@ -106,12 +106,48 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def test_halo_plan_is_consistent_across_ranks():
+    """exchange="halo": what rank p sends to rank q is what q expects from p, the halo table holds
+    exactly the rows q's edges reference (ascending in the all-gather layout), and the remapped
+    source ids point at the right global nodes."""
+    from het_b200 import graphs, parallel
+    coo = graphs.mag_shaped(scale=0.002)
+    world = 4
+    plans = [parallel.make_shard(coo, r, world, exchange="halo") for r in range(world)]
+    full = [parallel.make_shard(coo, r, world, exchange="all_gather") for r in range(world)]
+    for q in range(world):
+        pq = plans[q]
+        assert pq.exchange == "halo" and pq.num_gathered_rows == pq.halo_ids.size == sum(pq.recv_counts)
+        assert np.all(np.diff(pq.halo_ids) > 0)
+        assert np.array_equal(np.unique(full[q].src), pq.halo_ids)           # exactly the referenced rows
+        assert np.array_equal(pq.halo_ids[pq.src], full[q].src)              # remap round-trips
+        off = 0
+        for p in range(world):
+            n = pq.recv_counts[p]
+            assert plans[p].send_counts[q] == n
+            so = int(np.sum(plans[p].send_counts[:q]))
+            sent_local = plans[p].send_idx[so:so + n]
+            assert np.array_equal(sent_local + p * pq.max_rows, pq.halo_ids[off:off + n])
+            off += n
+        gp = pq.gathered_type_ptrs
+        assert gp.size == world * coo.num_ntypes + 1 and gp[0] == 0 and gp[-1] == pq.halo_ids.size
+        assert np.all(np.diff(gp) >= 0) and pq.segments_per_rank == coo.num_ntypes
+        # every halo row of segment (owner p, type t) is a node of type t
+        owned = [plans[p].owned for p in range(world)]
+        for p in range(world):
+            for t in range(coo.num_ntypes):
+                ids = pq.halo_ids[gp[p * coo.num_ntypes + t]:gp[p * coo.num_ntypes + t + 1]]
+                glob = owned[p][ids - p * pq.max_rows]
+                assert np.all((glob >= coo.node_type_offsets[t]) & (glob < coo.node_type_offsets[t + 1]))
+
+
 @pytest.mark.timeout(180)
-def test_all_gather_rows_autograd_gloo_world2():
+@pytest.mark.parametrize("exchange", ["all_gather", "halo"])
+def test_all_gather_rows_autograd_gloo_world2(exchange):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, exchange)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:
