@@ -95,11 +95,13 @@ def gathered_ids(cuts: np.ndarray, max_rows: int, ids: np.ndarray) -> np.ndarray
 
 
 def make_shard(coo: HeteroCOO, rank: int, world: int, exchange: str = None) -> ShardPlan:
-    """``exchange``: "all_gather" (default; env HETB_EXCHANGE overrides) gathers every rank's rows with one
-    equal-size all-gather; "halo" exchanges only the rows each shard's in-edges reference, with one
-    all-to-all (at 8 ranks a shard of the mag-shaped graph reads 60 % of the nodes, at 2 ranks 90 %)."""
+    """``exchange``: "all_gather" gathers every rank's rows with one equal-size all-gather; "halo"
+    exchanges only the rows each shard's in-edges reference, with one all-to-all (at 8 ranks a shard of
+    the mag-shaped graph reads 60 % of the nodes, at 4 ranks 76 %, at 2 ranks 90 %). Default (env
+    HETB_EXCHANGE overrides): halo from 8 ranks up, where it is measured faster (8.1 vs 9.5 ms/step on
+    HGT-mag; equal at 4 ranks), all-gather below."""
     import os
-    exchange = exchange or os.environ.get("HETB_EXCHANGE", "all_gather")
+    exchange = exchange or os.environ.get("HETB_EXCHANGE") or ("halo" if world >= 8 else "all_gather")
     assert exchange in ("all_gather", "halo")
     cuts = type_slices(coo.node_type_offsets, world)
     T = cuts.shape[0]
