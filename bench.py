@@ -634,7 +634,10 @@ def main():
     eager_loss = None
     if use_graph:  # count this library's launches per step once, eagerly (graph replays bypass the host counter)
         trainer.cuda_graph = False
-        eager_loss = float(trainer.step())
+        el = trainer.step().clone()
+        if world > 1:
+            dist.all_reduce(el)
+        eager_loss = float(el)
         trainer.cuda_graph = True
     launches_per_step = launch_count() - l0
     for _ in range(max(3, args.warmup)):
@@ -654,6 +657,8 @@ def main():
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
     ms_step = float(ms_total.item()) / args.steps
     clocks = sampler.stop() if sampler else None
+    if world > 1:   # each rank holds its shard's share of the (sum / N_total) loss
+        loss = loss.clone(); dist.all_reduce(loss)
     final_loss = float(loss.item())
     value = coo.num_edges * layers / (ms_step * 1e-3)
 
@@ -752,8 +757,9 @@ def main():
             "workload": f"{args.workload} ({cfg}): {kind.upper()} {layers} layer(s) fwd+loss+bwd+Adam, hidden 64, "
                         f"{heads} head(s), {coo.name} x{scale:g} N={coo.num_nodes} R={coo.num_rels} E={coo.num_edges}",
             "parallelism": "single GPU" if world == 1 else f"destination shards x{world} (rank p owns slice p of every node "
-                           "type's id range), one NCCL all-gather of the layer input per layer, reduce-scatter in "
-                           "backward, all-reduce of weight grads",
+                           "type's id range), per layer one NCCL " + ("all-to-all of the layer-input rows each shard's "
+                           "in-edges reference (halo) and its reverse in backward" if trainer.plan.exchange == "halo" else
+                           "all-gather of the layer input and a reduce-scatter in backward") + ", all-reduce of weight grads",
             "cuda_graph": use_graph, "compact_as_of_node": bool(args.compact), "fused_edge_pass": bool(args.fused and args.compact),
             "l2": "inputs larger than L2: per-edge tensors of one step total "
                   f"{coo.num_edges // world * 64 * 4 * 6 / 1e6:.0f} MB per GPU vs 126 MB L2 (no flush between steps)",
