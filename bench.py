@@ -47,7 +47,7 @@ METRIC = "rgnn_fullgraph_fwd_bwd_edges_per_s"
 UNIT = "edges/s"
 
 
-def parse_args():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -71,7 +71,7 @@ def parse_args():
                          "gradients; parity bar 2e-2). Off by default: the headline is the fp32 path.")
     ap.add_argument("--no-fused", dest="fused", action="store_false",
                     help="HGT: run inner product, edge softmax and aggregation as three ops instead of one pass")
-    return ap.parse_args()
+    return ap.parse_args(argv)
 
 
 class ClockSampler:
