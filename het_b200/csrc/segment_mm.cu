@@ -462,6 +462,11 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
                        const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
                        int64_t num_rows, int H, int K, int N, int accumulate, int passes, void *stream);
 
+// defined in segment_mm_tc_wide.cu (tcgen05 path for contraction / output widths above 64)
+int hetb_segment_mm_tc_wide(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
+                            const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
+                            int64_t num_rows, int H, int K, int N, int accumulate, void *stream);
+
 int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads, const float *G,
                               const int64_t *g_idx, int g_heads, float *dW, const int64_t *seg_ptrs,
                               int64_t num_segs, int64_t num_rows, int H, int K, int N, int probe, void *stream);
@@ -499,7 +504,13 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
       const int passes = g_segmm_impl >= 16 ? (g_segmm_impl >> 4) : (g_segmm_impl == 3 ? 1 : (g_segmm_impl == 4 ? 0 : 3));
       const int rc = hetb_segment_mm_tc(A, a_idx, a_heads, W, Y, c_idx, c_heads, seg_ptrs, num_segs,
                                         num_rows, H, K, N, accumulate, passes, stream);
-      if (rc != HETB_EUNSUPPORTED || g_segmm_impl >= 2) return rc;
+      if (rc != HETB_EUNSUPPORTED || g_segmm_impl >= 16) return rc;
+      if (passes == 3) {  // hidden sizes above 64: both operands streamed, 128 x 256 accumulator tiles
+        const int rcw = hetb_segment_mm_tc_wide(A, a_idx, a_heads, W, Y, c_idx, c_heads, seg_ptrs, num_segs, num_rows,
+                                                H, K, N, accumulate, stream);
+        if (rcw != HETB_EUNSUPPORTED) return rcw;
+      }
+      if (g_segmm_impl >= 2) return rc;
     }
   }
 

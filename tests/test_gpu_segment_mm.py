@@ -206,3 +206,63 @@ def test_tensor_core_grad_w_no_gather(cuda, force_tc):
     gX_ref, gW_ref = R.segment_mm_bwd(X.cpu(), None, W.cpu(), None, offs, gout.cpu(), 1)
     close(gX, gX_ref, "grad_input")
     close(gW, gW_ref, "grad_weight", rtol=2e-4, atol=2e-5)
+
+
+# ---------------------------------------------------------------------------
+# tcgen05 path for hidden sizes above 64 (csrc/segment_mm_tc_wide.cu): both operands streamed,
+# 128 x 256 / 128 / 64 accumulator tiles. Forced with impl=2; 3xTF32, same fp32 tolerance.
+# ---------------------------------------------------------------------------
+WIDE_SHAPES = [
+    # (nodes, edges, relations, heads, K, N, input_num_head_one)
+    (300, 5000, 3, 1, 128, 128, True),     # NT = 128, 4 K panels, tiles straddle segments
+    (300, 4097, 40, 1, 256, 256, True),    # NT = 256, many small segments, ragged last tile
+    (200, 3000, 5, 1, 512, 512, True),     # two N tiles of 256, 16 K panels
+    (200, 3000, 5, 4, 128, 64, True),      # RGAT multi-head: one 128-wide input row, 4 x 64 out (NT = 256)
+    (100, 1500, 2, 1, 64, 192, True),      # NT = 64 (192 = 3 x 64), K = 64
+    (100, 1500, 2, 1, 96, 64, True),       # K = 96 (3 panels), N = 64
+    (64, 7, 3, 1, 256, 128, True),         # fewer rows than a tile
+]
+
+
+@pytest.mark.parametrize("n,e,r,H,Kd,Nd,head_one", WIDE_SHAPES)
+def test_wide_tensor_core_segment_mm(cuda, force_tc, n, e, r, H, Kd, Nd, head_one):
+    from het_b200.kernels import K
+    g = build(cuda, n, e, r, seed=e + Kd + 2)
+    sc = g.get_separate_coo_original()
+    torch.manual_seed(Kd * Nd + e)
+    W = torch.randn(r, H, Kd, Nd, device=cuda) / Kd ** 0.5
+    for gather_name in ("row_indices", "eids"):
+        gather = sc[gather_name]
+        rows_in = n if gather_name == "row_indices" else e
+        X = torch.randn(rows_in, 1, Kd, device=cuda)
+        args = {"separate_coo_rel_ptrs": sc["rel_ptrs"], "separate_coo_node_indices": gather,
+                "separate_coo_eids": sc["eids"]}
+        ret = torch.full((e, H, Nd), float("nan"), device=cuda)
+        K.rgnn_relational_matmul(args, 0, W, X, ret, head_one)
+        want = R.segment_mm(X.cpu(), gather.cpu(), W.cpu(), sc["eids"].cpu(), sc["rel_ptrs"].cpu(), e, 1)
+        close(ret, want, f"wide fwd/{gather_name}")
+
+
+@pytest.mark.parametrize("sizes,Kd,Nd", [([1000, 0, 3000, 77], 128, 128), ([4099], 256, 256), ([700, 900], 512, 512),
+                                          ([300, 300, 300], 256, 64)])
+def test_wide_typed_linear_fwd_bwd(cuda, force_tc, sizes, Kd, Nd):
+    """The a3 op (rows sorted by node type) at hidden 128 / 256 / 512: forward and delta-input run the wide
+    tcgen05 kernel (the latter accumulating), delta-W the SIMT kernel."""
+    from het_b200.kernels import K
+    T, M = len(sizes), sum(sizes)
+    offs = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int64)
+    torch.manual_seed(M + Kd)
+    W = torch.randn(T, 1, Kd, Nd, device=cuda) / Kd ** 0.5
+    X = torch.randn(M, Kd, device=cuda)
+    ret = torch.full((M, Nd), float("nan"), device=cuda)
+    offs_d = offs.to(cuda)
+    K.rgnn_relational_matmul_no_scatter_gather_list(offs_d, W, X, ret)
+    want = R.segment_mm(X.cpu(), None, W.cpu(), None, offs, M, 1)
+    close(ret, want, "wide fwd")
+    gout = torch.randn(M, Nd, device=cuda)
+    gX, gW = torch.zeros_like(X), torch.zeros_like(W)
+    K.hetb200_set_segment_mm_impl(0)  # delta-W has no wide tensor-core kernel: automatic dispatch
+    K.backward_rgnn_relational_matmul_no_scatter_gather_list(offs_d, W.transpose(2, 3).contiguous(), X, gout, gX, gW)
+    gX_ref, gW_ref = R.segment_mm_bwd(X.cpu(), None, W.cpu(), None, offs, gout.cpu(), 1)
+    close(gX, gX_ref, "wide grad_input")
+    close(gW, gW_ref, "wide grad_weight", rtol=2e-4, atol=2e-5)
