@@ -24,8 +24,8 @@
 //                          B_s panel read as it lies in memory ([k][n], n contiguous: 32-bit loads
 //                          coalesced along n, four consecutive k per lane) and stored TRANSPOSED as the
 //                          K-major operand with one 128-bit store per 4 k — no workspace, no pre-pass.
-//                          Two register sets: the loads of stage n+2 are in flight while stage n is
-//                          split and stored.
+//                          A rows (HBM) are loaded two stages ahead into two register sets, the B_s
+//                          panel (L2) one stage ahead into one.
 #include "common.cuh"
 #include "tc_items.cuh"
 #include "tc_ptx.cuh"
@@ -75,7 +75,7 @@ struct StageIter {
   }
 };
 
-template <int NT>
+template <int NT, bool GATHER>
 __global__ void __launch_bounds__(kThreads, 1)
     segmm_tc_wide_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx, const float *__restrict__ W,
                          float *__restrict__ Y, const int64_t *__restrict__ c_idx, const int64_t *__restrict__ seg_ptrs,
@@ -132,74 +132,92 @@ __global__ void __launch_bounds__(kThreads, 1)
     constexpr int RA = TM / 32;             // 4 A rows per thread
     constexpr int RB = NT / 32;             // B: column i*32 + lane, k chunk pw, per thread
     StageIter ahead(pieces, ntiles, kpanels);  // the stage whose loads are issued next (two ahead of the stores)
-    PieceIter it_ix = pieces;  // one piece ahead of `ahead`: gather indices arrive before they are needed
-    int ixA[RA], ixN[RA];
-
-    auto load_ix = [&](int *ix) {  // gather indices (or row numbers) of the next piece; -1 = no row
-      int t0, a0, a1, sg;
-      const bool v = it_ix.next(t0, a0, a1, sg);
+    // Row numbers of the current piece (-1 = no row). With a gather list they are loaded when `ahead` enters
+    // a piece (one exposed load per piece: K/32 x Nt/NT stages); a prefetch one piece ahead made the compiler
+    // rotate load-written registers every stage, and with six scoreboards per warp that false dependency
+    // stalled every stage on the A rows just issued (profiles/r02j_segmm_wide_ncu_summary.txt).
+    int ixA[RA];
+    auto load_ix = [&]() {
 #pragma unroll
       for (int i = 0; i < RA; ++i) {
-        const int rr = t0 + rA + 32 * i;
-        const bool ok = v && rr >= a0 && rr < a1;
+        const int rr = ahead.t0 + rA + 32 * i;
+        const bool ok = rr >= ahead.p0 && rr < ahead.p1;
         const int64_t gr = row_base + rr;
         int x = ok ? (int)gr : -1;  // a row index fits 31 bits
-        if (ok && a_idx) x = (int)__ldg(a_idx + gr);
-        ix[i] = x;
+        if (GATHER) {
+          if (ok) x = (int)__ldg(a_idx + gr);
+        }
+        ixA[i] = x;
       }
     };
-    auto issue = [&](float4 *va, float4 *vb) -> int {  // loads of stage `ahead`; 1 if there was one
+    // A rows come from HBM (gathered): two register sets, loads issued two stages ahead. B_s comes from L2
+    // (every CTA of a segment reads the same weight): one register set, loaded one stage ahead, right after
+    // the previous panel has been stored — two B sets would not fit the 128 registers a 13-warp CTA gets.
+    struct BNext { int seg, nt, kp, valid; } nb = {0, 0, 0, 0};  // the stage whose B panel is loaded next
+    float4 vb[RB];
+    auto issue_a = [&](float4 *va) -> int {  // loads of stage `ahead`; 1 if there was one
       const int had = ahead.valid ? 1 : 0;
       if (ahead.valid) {
-        if (ahead.kp == 0 && ahead.nt == 0) {
-#pragma unroll
-          for (int i = 0; i < RA; ++i) ixA[i] = ixN[i];
-          load_ix(ixN);
-        }
+        if (ahead.kp == 0 && ahead.nt == 0) load_ix();
         const float *ap = A + ahead.kp * 32 + chunkA * 4;
 #pragma unroll
         for (int i = 0; i < RA; ++i) {
           va[i] = make_float4(0.f, 0.f, 0.f, 0.f);
           if (ixA[i] >= 0) va[i] = ldg4(ap + (int64_t)ixA[i] * K);
         }
-        const int k0 = ahead.kp * 32 + pw * 4;
-#pragma unroll
-        for (int i = 0; i < RB; ++i) {
-          const int cb = ahead.nt * NT + i * 32;         // first output column of this warp's 32 (one head: N % 32 == 0)
-          const int h = (H == 1) ? 0 : cb / N;           // head cb / N, column c - h N of W[seg, head]
-          const float *wp = W + (((int64_t)ahead.seg * H + h) * K + k0) * N + (cb - h * N + lane);
-          vb[i] = make_float4(__ldg(wp), __ldg(wp + N), __ldg(wp + 2 * (int64_t)N), __ldg(wp + 3 * (int64_t)N));
-        }
       }
-      ahead.advance();
       return had;
     };
+    auto issue_b = [&]() {
+      if (nb.valid) {
+        const int k0 = nb.kp * 32 + pw * 4;
+        if (H == 1) {  // one pointer per k row, the 32-column groups at immediate offsets
+          const float *w0 = W + ((int64_t)nb.seg * K + k0) * N + (nb.nt * NT + lane);
+          const float *w1 = w0 + N, *w2 = w1 + N, *w3 = w2 + N;
+#pragma unroll
+          for (int i = 0; i < RB; ++i)
+            vb[i] = make_float4(__ldg(w0 + i * 32), __ldg(w1 + i * 32), __ldg(w2 + i * 32), __ldg(w3 + i * 32));
+        } else {
+#pragma unroll
+          for (int i = 0; i < RB; ++i) {
+            const int cb = nb.nt * NT + i * 32;  // first output column of this warp's 32 (one head: N % 32 == 0)
+            const int h = cb / N;                // head cb / N, column c - h N of W[seg, head]
+            const float *wp = W + (((int64_t)nb.seg * H + h) * K + k0) * N + (cb - h * N + lane);
+            vb[i] = make_float4(__ldg(wp), __ldg(wp + N), __ldg(wp + 2 * (int64_t)N), __ldg(wp + 3 * (int64_t)N));
+          }
+        }
+      }
+    };
+    auto snapshot = [&]() { nb.seg = ahead.seg; nb.nt = ahead.nt; nb.kp = ahead.kp; nb.valid = ahead.valid ? 1 : 0; };
     uint32_t stage = 0, phase = 0;
-    int inflight = 0;  // stages loaded into registers, not yet stored
-    auto step = [&](float4 *va, float4 *vb) -> bool {
+    int inflight = 0;  // stages whose A rows are in registers, not yet stored
+    auto step = [&](float4 *va) -> bool {
       if (inflight == 0) return false;
       --inflight;
       mbar_wait(empty_bar(stage), phase ^ 1);
       uint8_t *gs = gbase + stage * C::kStageBytes;
-#pragma unroll
-      for (int i = 0; i < RA; ++i) {
-        const int r = rA + 32 * i;
-        const uint32_t off = (uint32_t)(r * 128 + ((chunkA ^ (r & 7)) << 4));
-        const float4 x = va[i];
-        const float4 lo = make_float4(x.x - tf32_hi(x.x), x.y - tf32_hi(x.y), x.z - tf32_hi(x.z), x.w - tf32_hi(x.w));
-        *reinterpret_cast<float4 *>(gs + off) = x;  // raw = hi: the tensor core drops the low 13 bits
-        *reinterpret_cast<float4 *>(gs + C::kOffAlo + off) = lo;
-      }
 #pragma unroll
       for (int i = 0; i < RB; ++i) {
         const int r = i * 32 + lane;
         const uint32_t off = (uint32_t)(r * 128 + ((pw ^ (r & 7)) << 4));
         const float4 x = vb[i];
         const float4 lo = make_float4(x.x - tf32_hi(x.x), x.y - tf32_hi(x.y), x.z - tf32_hi(x.z), x.w - tf32_hi(x.w));
-        *reinterpret_cast<float4 *>(gs + C::kOffB + off) = x;
+        *reinterpret_cast<float4 *>(gs + C::kOffB + off) = x;  // raw = hi: the tensor core drops the low 13 bits
         *reinterpret_cast<float4 *>(gs + C::kOffBlo + off) = lo;
       }
-      inflight += issue(va, vb);  // stage n + 2 into the registers just drained
+      issue_b();  // B panel of stage n + 1 (nb), into the registers just drained
+#pragma unroll
+      for (int i = 0; i < RA; ++i) {
+        const int r = rA + 32 * i;
+        const uint32_t off = (uint32_t)(r * 128 + ((chunkA ^ (r & 7)) << 4));
+        const float4 x = va[i];
+        const float4 lo = make_float4(x.x - tf32_hi(x.x), x.y - tf32_hi(x.y), x.z - tf32_hi(x.z), x.w - tf32_hi(x.w));
+        *reinterpret_cast<float4 *>(gs + off) = x;
+        *reinterpret_cast<float4 *>(gs + C::kOffAlo + off) = lo;
+      }
+      snapshot();                 // stage n + 2: its B panel is loaded by the next step
+      inflight += issue_a(va);    // A rows of stage n + 2
+      ahead.advance();
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) mbar_arrive(full_bar(stage));
@@ -210,13 +228,17 @@ __global__ void __launch_bounds__(kThreads, 1)
       return true;
     };
 
-    float4 a0[RA], a1[RA], b0[RB], b1[RB];
-    load_ix(ixN);  // piece 0 (moved into ixA by the first issue)
-    inflight += issue(a0, b0);
-    inflight += issue(a1, b1);
+    float4 a0[RA], a1[RA];
+    snapshot();    // stage 0
+    inflight += issue_a(a0);
+    ahead.advance();
+    issue_b();     // B panel of stage 0
+    snapshot();    // stage 1
+    inflight += issue_a(a1);
+    ahead.advance();
     for (;;) {
-      if (!step(a0, b0)) break;
-      if (!step(a1, b1)) break;
+      if (!step(a0)) break;
+      if (!step(a1)) break;
     }
   } else if (warp == kEpiWarps) {
     // ===================== MMA issuer =====================
@@ -316,23 +338,31 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 }
 
-template <int NT>
-static int launch_wide(const float *A, const int64_t *a_idx, const float *W, float *Y, const int64_t *c_idx,
+template <int NT, bool GATHER>
+static int launch_wide_g(const float *A, const int64_t *a_idx, const float *W, float *Y, const int64_t *c_idx,
                        const int64_t *seg_ptrs, int num_segs, int64_t num_rows, int H, int K, int N, int accumulate,
                        cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(segmm_tc_wide_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t ce = cudaFuncSetAttribute(segmm_tc_wide_kernel<NT, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)Cfg<NT>::kSmemBytes);
     if (ce != cudaSuccess) return (int)ce;
     attr_set = true;
   }
   const int64_t tiles = ceil_div64(num_rows, TM);
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
-  segmm_tc_wide_kernel<NT><<<grid, kThreads, Cfg<NT>::kSmemBytes, st>>>(A, a_idx, W, Y, c_idx, seg_ptrs, num_segs,
+  segmm_tc_wide_kernel<NT, GATHER><<<grid, kThreads, Cfg<NT>::kSmemBytes, st>>>(A, a_idx, W, Y, c_idx, seg_ptrs, num_segs,
                                                                         num_rows, H, K, N, accumulate);
   HETB_LAUNCH_OK();
   return HETB_OK;
+}
+
+template <int NT>
+static int launch_wide(const float *A, const int64_t *a_idx, const float *W, float *Y, const int64_t *c_idx,
+                       const int64_t *seg_ptrs, int num_segs, int64_t num_rows, int H, int K, int N, int accumulate,
+                       cudaStream_t st) {
+  return a_idx ? launch_wide_g<NT, true>(A, a_idx, W, Y, c_idx, seg_ptrs, num_segs, num_rows, H, K, N, accumulate, st)
+               : launch_wide_g<NT, false>(A, a_idx, W, Y, c_idx, seg_ptrs, num_segs, num_rows, H, K, N, accumulate, st);
 }
 
 }  // namespace tcw
