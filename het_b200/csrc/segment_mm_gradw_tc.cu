@@ -143,6 +143,10 @@ struct RowItems {
     }                                  \
   } while (0)
 
+// GATHER = false: neither operand has a gather list; row numbers are computed, never loaded (a
+// predicated-off index load still makes its register a load destination, and the scoreboard it shares
+// with the row loads stalls the consumer: see segment_mm_tc.cu).
+template <bool GATHER>
 __global__ void __launch_bounds__(kThreads, 1)
     gradw_tc_kernel(const float *__restrict__ A, const int64_t *__restrict__ a_idx, int a_heads,
                     const float *__restrict__ G, const int64_t *__restrict__ g_idx, float *__restrict__ dW,
@@ -223,7 +227,9 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int64_t r = rb + kProdWarps * i;
         // a row index fits 31 bits: 2^31 rows of 256 B would be 550 GB
         int v = ok ? (int)r : -1;
-        if (ok && !ident) v = (int)__ldg(idxbase + r);
+        if (GATHER) {
+          if (ok && !ident) v = (int)__ldg(idxbase + r);
+        }
         ix[i] = v;
       }
     };
@@ -387,8 +393,11 @@ int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads,
   if (num_segs > INT32_MAX) return HETB_EUNSUPPORTED;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(tcgw::gradw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t ce = cudaFuncSetAttribute(tcgw::gradw_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)tcgw::kSmemBytes);
+    if (ce != cudaSuccess) return (int)ce;
+    ce = cudaFuncSetAttribute(tcgw::gradw_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)tcgw::kSmemBytes);
     if (ce != cudaSuccess) return (int)ce;
     attr_set = true;
   }
@@ -397,9 +406,12 @@ int hetb_segment_mm_grad_w_tc(const float *A, const int64_t *a_idx, int a_heads,
   const int64_t rows_per_cta = ceil_div64(num_rows, ctas);
   if (rows_per_cta > INT32_MAX) return HETB_EUNSUPPORTED;
   ctas = ceil_div64(num_rows, rows_per_cta);
-  tcgw::gradw_tc_kernel<<<(unsigned)ctas, tcgw::kThreads, tcgw::kSmemBytes, (cudaStream_t)stream>>>(
-      A, a_idx, a_heads, G, g_idx, dW, seg_ptrs, (int)num_segs, num_rows, H, K, N, rows_per_cta, probe,
-      g_gradw_dbg);
+  if (a_idx || g_idx)
+    tcgw::gradw_tc_kernel<true><<<(unsigned)ctas, tcgw::kThreads, tcgw::kSmemBytes, (cudaStream_t)stream>>>(
+        A, a_idx, a_heads, G, g_idx, dW, seg_ptrs, (int)num_segs, num_rows, H, K, N, rows_per_cta, probe, g_gradw_dbg);
+  else
+    tcgw::gradw_tc_kernel<false><<<(unsigned)ctas, tcgw::kThreads, tcgw::kSmemBytes, (cudaStream_t)stream>>>(
+        A, a_idx, a_heads, G, g_idx, dW, seg_ptrs, (int)num_segs, num_rows, H, K, N, rows_per_cta, probe, g_gradw_dbg);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
