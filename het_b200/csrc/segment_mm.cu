@@ -153,6 +153,26 @@ __global__ void __launch_bounds__(kMMThreads)
 // N == 1 (RGAT attention logits el/er = <feat[e,h,:], attn[r,h,:]>):
 // lane group per row, 128-bit loads, shuffle reduction per head.
 // ---------------------------------------------------------------------------
+// A CTA owns a contiguous range of rows and each lane group walks it with stride GROUPS, so the
+// segment of a row is found by binary search once and then advanced (535 relations on the
+// wikikg2-shaped graph made the per-row search a 10-deep dependent load chain: 3x the roofline time).
+struct SegCursor {
+  const int64_t *__restrict__ ptrs;
+  int num_segs, s;
+  int64_t end;  // first row past segment s
+  __device__ SegCursor(const int64_t *p, int n, int64_t row, int64_t M) : ptrs(p), num_segs(n), s(0), end(M) {
+    s = segment_of(ptrs, num_segs, row);
+    end = (s + 1 < num_segs) ? __ldg(ptrs + s + 1) : M;
+  }
+  __device__ __forceinline__ int at(int64_t row, int64_t M) {  // rows must not decrease between calls
+    while (row >= end && s + 1 < num_segs) {
+      ++s;
+      end = (s + 1 < num_segs) ? __ldg(ptrs + s + 1) : M;
+    }
+    return s;
+  }
+};
+
 template <int LPR>
 __global__ void __launch_bounds__(kMMThreads)
     segmm_rowdot_kernel(const float *__restrict__ A,
@@ -160,30 +180,52 @@ __global__ void __launch_bounds__(kMMThreads)
                         const float *__restrict__ W, float *__restrict__ Y,
                         const int64_t *__restrict__ c_idx,
                         const int64_t *__restrict__ seg_ptrs, int num_segs,
-                        int64_t M, int H, int hw, int accumulate) {
+                        int64_t M, int H, int hw, int accumulate, int64_t rows_per_cta) {
   constexpr int GROUPS = kMMThreads / LPR;
   constexpr int D = LPR * 4;
+  constexpr int U = 4;  // rows in flight per lane group
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
-  const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  const int64_t iters = ceil_div64(M, stride);
-  int64_t i = (int64_t)blockIdx.x * GROUPS + g;
-  for (int64_t it = 0; it < iters; ++it, i += stride) {
-    const bool ok = i < M;
-    float v = 0.f;
-    if (ok) {
-      const int s = segment_of(seg_ptrs, num_segs, i);
-      const int64_t ar = a_idx ? __ldg(a_idx + i) : i;
-      v = dot4(ldcs4(A + ar * D + 4 * l), ldg4(W + (int64_t)s * D + 4 * l));
+  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;  // rows_per_cta is a multiple of GROUPS * U
+  const int64_t row1 = (row0 + rows_per_cta < M) ? row0 + rows_per_cta : M;
+  if (row0 >= row1) return;
+  SegCursor cur(seg_ptrs, num_segs, row0 + g < M ? row0 + g : M - 1, M);
+  for (int64_t base = row0; base < row1; base += U * GROUPS) {  // uniform trip count: the shuffles need the whole warp
+    const int64_t i = base + g;
+    float4 a[U], w[U];
+    bool ok[U];
+    int sg[U];
+    // segments first, row loads after: the cursor's `end` can be written by a load, and a compare on it
+    // placed between the row loads waits (shared scoreboard) for the rows just requested — that kept one
+    // row per lane group in flight instead of U (ncu source view: 60 % of the samples on those compares)
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t r = i + j * GROUPS;
+      ok[j] = r < row1;
+      sg[j] = ok[j] ? cur.at(r, M) : 0;
     }
-    v = group_sum(v, hw);
-    if (ok && leader) {
-      const int64_t cr = c_idx ? __ldg(c_idx + i) : i;
-      if (accumulate)
-        atomicAdd(Y + cr * H + h, v);
-      else
-        Y[cr * H + h] = v;
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t r = i + j * GROUPS;
+      a[j] = w[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok[j]) {
+        const int64_t ar = a_idx ? __ldg(a_idx + r) : r;
+        a[j] = ldcs4(A + ar * D + 4 * l);
+        w[j] = ldg4(W + (int64_t)sg[j] * D + 4 * l);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const float v = group_sum(dot4(a[j], w[j]), hw);
+      if (ok[j] && leader) {
+        const int64_t r = i + j * GROUPS;
+        const int64_t cr = c_idx ? __ldg(c_idx + r) : r;
+        if (accumulate)
+          atomicAdd(Y + cr * H + h, v);
+        else
+          Y[cr * H + h] = v;
+      }
     }
   }
 }
@@ -196,23 +238,49 @@ __global__ void __launch_bounds__(kMMThreads)
                         const float *__restrict__ W, float *__restrict__ Y,
                         const int64_t *__restrict__ c_idx,
                         const int64_t *__restrict__ seg_ptrs, int num_segs,
-                        int64_t M, int H, int hw, int accumulate) {
+                        int64_t M, int H, int hw, int accumulate, int64_t rows_per_cta) {
   constexpr int GROUPS = kMMThreads / LPR;
   constexpr int D = LPR * 4;
+  constexpr int U = 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int h = l / hw;
-  const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  for (int64_t i = (int64_t)blockIdx.x * GROUPS + g; i < M; i += stride) {
-    const int s = segment_of(seg_ptrs, num_segs, i);
-    const int64_t ar = a_idx ? __ldg(a_idx + i) : i;
-    const int64_t cr = c_idx ? __ldg(c_idx + i) : i;
-    const float a = __ldg(A + ar * H + h);
-    const float4 w = ldg4(W + (int64_t)s * D + 4 * l);
-    const float4 y = make_float4(a * w.x, a * w.y, a * w.z, a * w.w);
-    if (accumulate)
-      red_add4(Y + cr * D + 4 * l, y);
-    else
-      stcs4(Y + cr * D + 4 * l, y);
+  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t row1 = (row0 + rows_per_cta < M) ? row0 + rows_per_cta : M;
+  if (row0 + g >= row1) return;
+  SegCursor cur(seg_ptrs, num_segs, row0 + g, M);
+  for (int64_t i = row0 + g; i < row1; i += U * GROUPS) {
+    float a[U];
+    float4 w[U];
+    int64_t cr[U];
+    int sg[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {  // segments first, loads after (see segmm_rowdot_kernel)
+      const int64_t r = i + j * GROUPS;
+      sg[j] = r < row1 ? cur.at(r, M) : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t r = i + j * GROUPS;
+      cr[j] = -1;
+      a[j] = 0.f;
+      w[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < row1) {
+        const int64_t ar = a_idx ? __ldg(a_idx + r) : r;
+        cr[j] = c_idx ? __ldg(c_idx + r) : r;
+        a[j] = __ldg(A + ar * H + h);
+        w[j] = ldg4(W + (int64_t)sg[j] * D + 4 * l);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      if (cr[j] >= 0) {
+        const float4 y = make_float4(a[j] * w[j].x, a[j] * w[j].y, a[j] * w[j].z, a[j] * w[j].w);
+        if (accumulate)
+          red_add4(Y + cr[j] * D + 4 * l, y);
+        else
+          stcs4(Y + cr[j] * D + 4 * l, y);
+      }
+    }
   }
 }
 
@@ -518,13 +586,15 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
   if (N == 1 && a_heads == H && c_heads == H && is_pow2(H) && is_pow2(K) &&
       K >= 4 && pick_lpr(H * K)) {
     const int lpr = pick_lpr(H * K);
-    const int64_t need = ceil_div64(num_rows, kMMThreads / lpr);
-    const int grid = (int)(need < kNumSMs * 16 ? need : kNumSMs * 16);
+    const int64_t chunk = (int64_t)(kMMThreads / lpr) * 4;  // rows one CTA pass covers (GROUPS x U)
+    int64_t rows_per_cta = ceil_div64(ceil_div64(num_rows, (int64_t)kNumSMs * 16), chunk) * chunk;
+    const int grid = (int)ceil_div64(num_rows, rows_per_cta);
     switch (lpr) {
 #define ROWDOT(L)                                                              \
   case L:                                                                      \
     segmm_rowdot_kernel<L><<<grid, kMMThreads, 0, st>>>(                       \
-        A, a_idx, W, Y, c_idx, seg_ptrs, S, num_rows, H, K / 4, accumulate);   \
+        A, a_idx, W, Y, c_idx, seg_ptrs, S, num_rows, H, K / 4, accumulate,    \
+        rows_per_cta);                                                         \
     break;
       ROWDOT(4) ROWDOT(8) ROWDOT(16) ROWDOT(32)
 #undef ROWDOT
@@ -536,13 +606,15 @@ extern "C" int hetb_segment_mm(const float *A, const int64_t *a_idx,
   if (K == 1 && a_heads == H && c_heads == H && is_pow2(H) && is_pow2(N) &&
       N >= 4 && pick_lpr(H * N)) {
     const int lpr = pick_lpr(H * N);
-    const int64_t need = ceil_div64(num_rows, kMMThreads / lpr);
-    const int grid = (int)(need < kNumSMs * 16 ? need : kNumSMs * 16);
+    const int64_t chunk = (int64_t)(kMMThreads / lpr) * 4;
+    int64_t rows_per_cta = ceil_div64(ceil_div64(num_rows, (int64_t)kNumSMs * 16), chunk) * chunk;
+    const int grid = (int)ceil_div64(num_rows, rows_per_cta);
     switch (lpr) {
 #define EXPAND(L)                                                              \
   case L:                                                                      \
     segmm_expand_kernel<L><<<grid, kMMThreads, 0, st>>>(                       \
-        A, a_idx, W, Y, c_idx, seg_ptrs, S, num_rows, H, N / 4, accumulate);   \
+        A, a_idx, W, Y, c_idx, seg_ptrs, S, num_rows, H, N / 4, accumulate,    \
+        rows_per_cta);                                                         \
     break;
       EXPAND(4) EXPAND(8) EXPAND(16) EXPAND(32)
 #undef EXPAND
