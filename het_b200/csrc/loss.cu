@@ -16,30 +16,67 @@ __global__ void __launch_bounds__(kLossThreads)
     xent_fwd_kernel(const float *__restrict__ logits, const int64_t *__restrict__ labels, int64_t n, int C,
                     float inv_denom, float *__restrict__ lse, float *__restrict__ loss) {
   constexpr int GROUPS = kLossThreads / kLossLPR;
+  constexpr int U = 4;  // rows in flight per lane group (one row at a time ran at 1.8 TB/s)
   const int g = threadIdx.x / kLossLPR, l = threadIdx.x % kLossLPR;
   const int64_t stride = (int64_t)gridDim.x * GROUPS;
-  const int64_t iters = ceil_div64(n, stride);
+  const int64_t iters = ceil_div64(n, stride * U);
   float local = 0.f;
-  int64_t i = (int64_t)blockIdx.x * GROUPS + g;
-  for (int64_t it = 0; it < iters; ++it, i += stride) {
-    const bool ok = i < n;
-    const float *row = logits + (ok ? i : 0) * C;
-    float m = -INFINITY;
-    for (int c = 4 * l; c < C; c += 4 * kLossLPR) {
-      const float4 v = ldcs4(row + c);
-      m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+  int64_t i0 = (int64_t)blockIdx.x * GROUPS + g;
+  if (C == 4 * kLossLPR) {
+    // a row is one float4 per lane: read once, kept in registers for both the max and the sum
+    for (int64_t it = 0; it < iters; ++it, i0 += stride * U) {
+      float4 v[U];
+      int lab[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        lab[u] = 0;
+        if (i < n) {
+          v[u] = ldcs4(logits + i * C + 4 * l);
+          lab[u] = (int)__ldg(labels + i);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        float m = fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w));
+        for (int o = kLossLPR >> 1; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        float s = __expf(v[u].x - m) + __expf(v[u].y - m) + __expf(v[u].z - m) + __expf(v[u].w - m);
+        // the label's logit sits in lane lab / 4, component lab % 4
+        const int c = lab[u] & 3;
+        float pick = (lab[u] >> 2) == l ? (c == 0 ? v[u].x : c == 1 ? v[u].y : c == 2 ? v[u].z : v[u].w) : 0.f;
+        s = group_sum(s, kLossLPR);
+        pick = group_sum(pick, kLossLPR);
+        if (i < n && l == 0) {
+          const float z = m + __logf(s);
+          lse[i] = z;
+          local += z - pick;
+        }
+      }
     }
-    for (int o = kLossLPR >> 1; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    float s = 0.f;
-    for (int c = 4 * l; c < C; c += 4 * kLossLPR) {
-      const float4 v = ldg4(row + c);  // second pass hits L1/L2
-      s += __expf(v.x - m) + __expf(v.y - m) + __expf(v.z - m) + __expf(v.w - m);
-    }
-    s = group_sum(s, kLossLPR);
-    if (ok && l == 0) {
-      const float z = m + __logf(s);
-      lse[i] = z;
-      local += z - __ldg(row + __ldg(labels + i));
+  } else {
+    for (int64_t it = 0; it < iters * U; ++it, i0 += stride) {
+      const int64_t i = i0;
+      const bool ok = i < n;
+      const float *row = logits + (ok ? i : 0) * C;
+      float m = -INFINITY;
+      for (int c = 4 * l; c < C; c += 4 * kLossLPR) {
+        const float4 v = ldcs4(row + c);
+        m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+      }
+      for (int o = kLossLPR >> 1; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+      float s = 0.f;
+      for (int c = 4 * l; c < C; c += 4 * kLossLPR) {
+        const float4 v = ldg4(row + c);  // second pass hits L1/L2
+        s += __expf(v.x - m) + __expf(v.y - m) + __expf(v.z - m) + __expf(v.w - m);
+      }
+      s = group_sum(s, kLossLPR);
+      if (ok && l == 0) {
+        const float z = m + __logf(s);
+        lse[i] = z;
+        local += z - __ldg(row + __ldg(labels + i));
+      }
     }
   }
   // one atomic per CTA
