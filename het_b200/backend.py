@@ -818,25 +818,29 @@ def hgt_reordered_projections(g, h, k_linears, w_att, w_msg):
 
 
 class HGTReorderedProjectionsSharded(th.autograd.Function):
-    """HGTReorderedProjections on a destination shard (het_b200/parallel.py): ``h`` are the owned rows,
-    ``hg`` the all-gathered layer input. k = hg.W_k[type] is computed HERE for every gathered row
-    (the typed linear over the gathered layout's (rank, type) segments) instead of being gathered
-    as a second tensor: one exchange per layer instead of two, at the price of a typed linear over
-    N instead of N/P rows. msg_c reads hg through the (relation, source) lists, left_c reads the
-    local h. Backward: the k and msg_c input gradients land in ONE [Ng, D] buffer (whose
-    reduce-scatter is the exchange's backward), the left_c gradient in grad_h."""
+    """HGTReorderedProjections on a destination shard (het_b200/parallel.py): ``h`` are the owned rows;
+    the layer-input exchange (``xch``: a parallel.RowExchange) happens INSIDE this node so that it can
+    overlap: forward = start the exchange, run the destination-side typed linear (left_c reads only the
+    local h), finish the exchange, then k = hg.W_k[type] for every received row (one exchange per layer
+    instead of gathering k and v; the price is a typed linear over the received rows instead of N/P)
+    and msg_c through the (relation, source) lists. Backward = the two input gradients of hg into ONE
+    buffer, start its reverse exchange, run the three weight-gradient kernels and the left_c input
+    gradient under it, then add the returned rows into grad_h."""
 
     @staticmethod
-    def forward(ctx, gathered_type_ptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att, w_msg):
-        ng, d_out = hg.size(0), k_ext.size(1) * k_ext.size(3)
-        k = th.empty((ng, d_out), dtype=hg.dtype, device=hg.device)
-        K.rgnn_relational_matmul_no_scatter_gather_list(gathered_type_ptrs, k_ext, hg, k)
+    def forward(ctx, xch, gathered_type_ptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, k_ext, w_att, w_msg):
+        handle = xch.forward_start(h)
         left = th.empty((nodes_col.numel(), w_att.size(1), w_att.size(3)), dtype=h.dtype, device=h.device)
         K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col,
                                   "unique_srcs_and_dests_node_indices": nodes_col}, 1, w_att, h, left, True)
+        hg = xch.forward_finish(handle)
+        ng, d_out = hg.size(0), k_ext.size(1) * k_ext.size(3)
+        k = th.empty((ng, d_out), dtype=hg.dtype, device=hg.device)
+        K.rgnn_relational_matmul_no_scatter_gather_list(gathered_type_ptrs, k_ext, hg, k)
         msg = th.empty((nodes_row.numel(), w_msg.size(1), w_msg.size(3)), dtype=h.dtype, device=h.device)
         K.rgnn_relational_matmul({"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row,
                                   "unique_srcs_and_dests_node_indices": nodes_row}, 1, w_msg, hg, msg, True)
+        ctx.xch = xch
         ctx.save_for_backward(gathered_type_ptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att,
                               w_msg)
         return k, left, msg
@@ -844,33 +848,40 @@ class HGTReorderedProjectionsSharded(th.autograd.Function):
     @staticmethod
     def backward(ctx, grad_k, grad_left, grad_msg):
         gptrs, rel_ptrs_col, nodes_col, rel_ptrs_row, nodes_row, h, hg, k_ext, w_att, w_msg = ctx.saved_tensors
-        grad_hg = th.empty_like(hg, memory_format=th.contiguous_format)  # the segments cover every gathered row
+        row = {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row, "unique_srcs_and_dests_node_indices": nodes_row}
+        col = {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col, "unique_srcs_and_dests_node_indices": nodes_col}
+        none = h.new_empty(0)  # "skip this half" for the backward ops
+        grad_k, grad_msg = grad_k.contiguous(), grad_msg.contiguous()
+        wk_t, wmsg_t = th.transpose(k_ext, 2, 3).contiguous(), th.transpose(w_msg, 2, 3).contiguous()
+        # input gradients of the received rows first: their reverse exchange is the long pole
+        grad_hg = th.empty_like(hg, memory_format=th.contiguous_format)  # the segments cover every received row
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(gptrs, wk_t, hg, grad_k, grad_hg, none)
+        K.backward_rgnn_relational_matmul(row, 1, wmsg_t, hg, grad_msg, grad_hg, none, True)
+        handle = ctx.xch.backward_start(grad_hg)
+        # under the exchange: the weight gradients and the destination-side input gradient
         grad_wk = th.zeros_like(k_ext, memory_format=th.contiguous_format)
-        K.backward_rgnn_relational_matmul_no_scatter_gather_list(
-            gptrs, th.transpose(k_ext, 2, 3).contiguous(), hg, grad_k.contiguous(), grad_hg, grad_wk)
+        K.backward_rgnn_relational_matmul_no_scatter_gather_list(gptrs, wk_t, hg, grad_k, none, grad_wk)
         grad_wmsg = th.zeros_like(w_msg, memory_format=th.contiguous_format)
-        K.backward_rgnn_relational_matmul(
-            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_row, "unique_srcs_and_dests_node_indices": nodes_row}, 1,
-            th.transpose(w_msg, 2, 3).contiguous(), hg, grad_msg.contiguous(), grad_hg, grad_wmsg, True)
+        K.backward_rgnn_relational_matmul(row, 1, wmsg_t, hg, grad_msg, none, grad_wmsg, True)
         grad_h = th.zeros_like(h, memory_format=th.contiguous_format)
         grad_watt = th.zeros_like(w_att, memory_format=th.contiguous_format)
-        K.backward_rgnn_relational_matmul(
-            {"unique_srcs_and_dests_rel_ptrs": rel_ptrs_col, "unique_srcs_and_dests_node_indices": nodes_col}, 1,
-            th.transpose(w_att, 2, 3).contiguous(), h, grad_left.contiguous(), grad_h, grad_watt, True)
-        return None, None, None, None, None, grad_h, grad_hg, grad_wk, grad_watt, grad_wmsg
+        K.backward_rgnn_relational_matmul(col, 1, th.transpose(w_att, 2, 3).contiguous(), h, grad_left.contiguous(),
+                                          grad_h, grad_watt, True)
+        ctx.xch.backward_finish(handle, grad_h)
+        return None, None, None, None, None, None, grad_h, grad_wk, grad_watt, grad_wmsg
 
 
-def hgt_reordered_projections_sharded(g, h, hg, k_linears, w_att, w_msg):
-    """k_linears [T, 1, in, out] -> one weight per segment of the gathered layout: per rank the T
-    types and a zero matrix for its padding rows."""
+def hgt_reordered_projections_sharded(g, h, xch, k_linears, w_att, w_msg):
+    """k_linears [T, 1, in, out] -> one weight per segment of the received-row layout: per rank the T
+    types (and, in the all-gather layout, a zero matrix for its padding rows)."""
     u = g.get_separate_unique_node_indices_single_sided()
     if g.gathered_segments_per_rank == k_linears.size(0) + 1:   # all-gather layout: T types + padding per rank
         k_ext = th.cat([k_linears, th.zeros_like(k_linears[:1])], 0).repeat(g.world, 1, 1, 1)
     else:                                                        # halo table: T types per owner block
         k_ext = k_linears.repeat(g.world, 1, 1, 1)
     return HGTReorderedProjectionsSharded.apply(
-        g.gathered_type_ptrs, u["rel_ptrs_col"], u["node_indices_col"], u["rel_ptrs_row"], u["node_indices_row"],
-        h.contiguous(), hg.contiguous(), k_ext.contiguous(), w_att.contiguous(), w_msg.contiguous())
+        xch, g.gathered_type_ptrs, u["rel_ptrs_col"], u["node_indices_col"], u["rel_ptrs_row"], u["node_indices_row"],
+        h.contiguous(), k_ext.contiguous(), w_att.contiguous(), w_msg.contiguous())
 
 
 class RelationalMatmulCompactPair(th.autograd.Function):

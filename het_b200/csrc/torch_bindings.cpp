@@ -167,18 +167,22 @@ void backward_rgnn_relational_matmul(TensorDict args, int64_t kind,
     return;
   }
   const int accumulate = (identical && a_heads == H) ? 0 : 1;
+  // hetb200 extension: a zero-element grad_node_feat / grad_weights skips that half, so a caller can put
+  // other work (a collective on the input gradient) between the two.
   // dX[gather[i]] += dY[scatter[i]] · W^T[r]
-  check_rc(hetb_segment_mm(f32(gradout, op, "gradout"), scatter, H,
-                           f32(weights_transposed, op, "weights_transposed"),
-                           f32w(grad_node_feat, op, "grad_node_feat"), gather,
-                           a_heads, rel_ptrs, R, M, H, N, K, accumulate, st),
-           op);
+  if (grad_node_feat.numel() > 0)
+    check_rc(hetb_segment_mm(f32(gradout, op, "gradout"), scatter, H,
+                             f32(weights_transposed, op, "weights_transposed"),
+                             f32w(grad_node_feat, op, "grad_node_feat"), gather,
+                             a_heads, rel_ptrs, R, M, H, N, K, accumulate, st),
+             op);
   // dW[r] += X[gather[i]]^T · dY[scatter[i]]
-  check_rc(hetb_segment_mm_grad_w(f32(node_feat, op, "node_feat"), gather,
-                                  a_heads, f32(gradout, op, "gradout"), scatter,
-                                  H, f32w(grad_weights, op, "grad_weights"),
-                                  rel_ptrs, R, M, H, K, N, st),
-           op);
+  if (grad_weights.numel() > 0)
+    check_rc(hetb_segment_mm_grad_w(f32(node_feat, op, "node_feat"), gather,
+                                    a_heads, f32(gradout, op, "gradout"), scatter,
+                                    H, f32w(grad_weights, op, "grad_weights"),
+                                    rel_ptrs, R, M, H, K, N, st),
+             op);
 }
 
 // OpExport/RGNNOps.inc.h:83-88
@@ -220,17 +224,20 @@ static void backward_no_scatter_gather_impl(const char *op, bool force_accumulat
   const int64_t *ptrs = i64(ntype_offset_ptrs, op, "ntype_offset_ptrs");
   const int64_t T = ntype_offset_ptrs.numel() - 1;
   const int accumulate = (force_accumulate || (a_heads == 1 && H > 1)) ? 1 : 0;
-  check_rc(hetb_segment_mm(f32(grad_node_feat_output, op, "grad_node_feat_output"),
-                           nullptr, H,
-                           f32(weights_transposed, op, "weights_transposed"),
-                           f32w(grad_node_feat_input, op, "grad_node_feat_input"),
-                           nullptr, a_heads, ptrs, T, M, H, N, K, accumulate, st),
-           op);
-  check_rc(hetb_segment_mm_grad_w(
-               f32(node_feat_input, op, "node_feat_input"), nullptr, a_heads,
-               f32(grad_node_feat_output, op, "grad_node_feat_output"), nullptr,
-               H, f32w(grad_weights, op, "grad_weights"), ptrs, T, M, H, K, N, st),
-           op);
+  // a zero-element grad_node_feat_input / grad_weights skips that half (hetb200 extension, see above)
+  if (grad_node_feat_input.numel() > 0)
+    check_rc(hetb_segment_mm(f32(grad_node_feat_output, op, "grad_node_feat_output"),
+                             nullptr, H,
+                             f32(weights_transposed, op, "weights_transposed"),
+                             f32w(grad_node_feat_input, op, "grad_node_feat_input"),
+                             nullptr, a_heads, ptrs, T, M, H, N, K, accumulate, st),
+             op);
+  if (grad_weights.numel() > 0)
+    check_rc(hetb_segment_mm_grad_w(
+                 f32(node_feat_input, op, "node_feat_input"), nullptr, a_heads,
+                 f32(grad_node_feat_output, op, "grad_node_feat_output"), nullptr,
+                 H, f32w(grad_weights, op, "grad_weights"), ptrs, T, M, H, K, N, st),
+             op);
 }
 
 void backward_rgnn_relational_matmul_no_scatter_gather_list(

@@ -383,7 +383,7 @@ class HET_HGTLayerHetero(nn.Module):
             elif reorder:
                 # destination shard: ONE exchange (the layer input); k is computed for the gathered rows here
                 k, attn_weight_dst_product_compact, message_compact = B.hgt_reordered_projections_sharded(
-                    G, h, gather(h), self.k_linears, w_att, w_msg)
+                    G, h, gather, self.k_linears, w_att, w_msg)
                 k = k.view(-1, self.num_heads, self.d_k)
             else:
                 attn_weight_dst_product_compact = B.rgnn_relational_matmul(

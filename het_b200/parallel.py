@@ -250,6 +250,106 @@ def gather_rows(x: torch.Tensor, plan: "ShardPlan", group=None) -> torch.Tensor:
     return all_gather_rows(x, plan.max_rows, group)
 
 
+class RowExchange:
+    """The layer-input exchange of one shard as an object: calling it is the autograd form
+    (``gather_rows``); the ``*_start`` / ``*_finish`` pairs are the same collectives issued asynchronously
+    (on NCCL's stream, ordered after the work already queued on the current stream) so that a caller can
+    put independent kernels between the two — ``backend.HGTReorderedProjectionsSharded`` runs the
+    destination-side typed linear under the forward exchange and the weight-gradient kernels under the
+    backward one. No autograd inside: the caller is an autograd node."""
+
+    def __init__(self, plan: "ShardPlan", group=None):
+        self.plan, self.group = plan, group
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        return gather_rows(x, self.plan, self.group)
+
+    def _send_idx(self, device):
+        plan = self.plan
+        if getattr(plan, "_send_idx_t", None) is None or plan._send_idx_t.device != device:
+            plan._send_idx_t = torch.from_numpy(plan.send_idx).to(device)
+        return plan._send_idx_t
+
+    def forward_start(self, x: torch.Tensor):
+        plan = self.plan
+        x = x.contiguous()
+        if plan.exchange == "halo":
+            send = _gather_rows(x, self._send_idx(x.device))
+            out = x.new_empty((sum(plan.recv_counts),) + tuple(x.shape[1:]))
+            work = dist.all_to_all_single(out, send, plan.recv_counts, plan.send_counts, group=self.group, async_op=True)
+            return work, out, send
+        if x.shape[0] == plan.max_rows:
+            part = x
+        else:
+            part = x.new_zeros((plan.max_rows,) + tuple(x.shape[1:]))
+            part[: x.shape[0]] = x
+        out = x.new_empty((plan.world * plan.max_rows,) + tuple(x.shape[1:]))
+        work = dist.all_gather_into_tensor(out, part, group=self.group, async_op=True)
+        return work, out, part
+
+    @staticmethod
+    def forward_finish(handle) -> torch.Tensor:
+        work, out, _keep = handle
+        work.wait()
+        return out
+
+    def backward_start(self, g: torch.Tensor):
+        plan = self.plan
+        g = g.contiguous()
+        if plan.exchange == "halo":
+            back = g.new_empty((sum(plan.send_counts),) + tuple(g.shape[1:]))
+            work = dist.all_to_all_single(back, g, plan.send_counts, plan.recv_counts, group=self.group, async_op=True)
+            return work, back, g
+        if dist.get_backend(self.group) == "nccl":
+            mine = g.new_empty((plan.max_rows,) + tuple(g.shape[1:]))
+            work = dist.reduce_scatter_tensor(mine, g, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            return work, mine, g
+        work = dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group, async_op=True)  # gloo has no reduce_scatter
+        r = dist.get_rank(self.group)
+        return work, g[r * plan.max_rows:(r + 1) * plan.max_rows], g
+
+    def backward_finish(self, handle, grad_x: torch.Tensor) -> None:
+        """Adds the exchanged gradient rows into ``grad_x`` ([n_local, D])."""
+        work, buf, _keep = handle
+        work.wait()
+        if self.plan.exchange == "halo":
+            _scatter_add_rows(grad_x, self._send_idx(grad_x.device), buf)
+        else:
+            grad_x += buf[: grad_x.shape[0]]
+
+
+class LocalRowExchange(RowExchange):
+    """Single-process stand-in with the all-gather layout (tests, tools/profile_shard.py): the own rows at
+    their place, the other ranks' rows zero; backward = the own rows of the gradient."""
+
+    def __init__(self, plan: "ShardPlan"):
+        assert plan.exchange == "all_gather"
+        super().__init__(plan, None)
+
+    def _place(self, x):
+        out = x.new_zeros((self.plan.num_gathered_rows,) + tuple(x.shape[1:]))
+        lo = self.plan.rank * self.plan.max_rows
+        out[lo: lo + x.shape[0]] = x
+        return out
+
+    def __call__(self, x):
+        return self._place(x)  # slice assignment into zeros: differentiable
+
+    def forward_start(self, x):
+        return None, self._place(x.detach()), None
+
+    @staticmethod
+    def forward_finish(handle):
+        return handle[1]
+
+    def backward_start(self, g):
+        return None, g, None
+
+    def backward_finish(self, handle, grad_x):
+        lo = self.plan.rank * self.plan.max_rows
+        grad_x += handle[1][lo: lo + grad_x.shape[0]]
+
+
 def all_reduce_grads(params, group=None) -> None:
     """One flat all-reduce (sum) of every parameter gradient (replicated weights)."""
     grads = [p.grad for p in params if p.grad is not None]

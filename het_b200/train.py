@@ -128,8 +128,11 @@ class FullGraphTrainer:
         self._loss = {}
 
     # ------------------------------------------------------------------
-    def _gather(self, x):
-        return parallel.gather_rows(x, self.plan, self.group)
+    @property
+    def _gather(self):
+        if getattr(self, "_row_exchange", None) is None:
+            self._row_exchange = parallel.RowExchange(self.plan, self.group)
+        return self._row_exchange
 
     def forward(self, h0):
         if self.kind == "rgcn":

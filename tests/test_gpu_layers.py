@@ -212,10 +212,7 @@ def test_hgt_fused_on_padded_shard_sources(cuda):
     n = plan.num_local_nodes
     assert plan.num_gathered_rows > 3 * n  # sources index the gathered matrix: long runs of rows without out-edges
 
-    def gather(t):
-        out = t.new_zeros((plan.num_gathered_rows,) + tuple(t.shape[1:]))
-        idx = torch.arange(n, device=t.device) + plan.rank * plan.max_rows
-        return out.index_add(0, idx, t)
+    gather = parallel.LocalRowExchange(plan)  # own rows at their place, the other ranks' rows zero
 
     outs = []
     for fused in (True, False):

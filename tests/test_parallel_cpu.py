@@ -101,6 +101,15 @@ def _worker(rank, world, port, q, exchange="all_gather"):
         (of * (torch.arange(coo.num_nodes * 4, dtype=torch.float64).view(-1, 4) / 100)).sum().backward()
         ok = (torch.allclose(out, of[own].detach()) and torch.allclose(w.grad, wf.grad)
               and torch.allclose(x_loc.grad, xf.grad[own]))
+        # the split (asynchronous) form of the same exchange gives the same rows and the same gradient
+        xch = parallel.RowExchange(plan)
+        xg2 = xch.forward_finish(xch.forward_start(x_loc.detach()))
+        ok = ok and torch.equal(xg2, xg.detach())
+        gg = torch.randn(xg.shape, dtype=torch.float64, generator=torch.Generator().manual_seed(5 + rank))
+        (want,) = torch.autograd.grad(parallel.gather_rows(x_loc, plan), x_loc, gg.clone())  # gloo reduces in place
+        got = torch.zeros_like(want)
+        xch.backward_finish(xch.backward_start(gg.clone()), got)
+        ok = ok and torch.allclose(got, want)
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()

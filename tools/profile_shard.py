@@ -25,16 +25,13 @@ else:
 
 
 def run(rank, profile=False):
-    plan = parallel.make_shard(coo, rank, world)
+    plan = parallel.make_shard(coo, rank, world, exchange="all_gather")
     g = parallel.shard_graph(plan, coo, dev)
     u = g.get_separate_unique_node_indices_single_sided()
     n = plan.num_local_nodes
     x = (torch.rand(n, 64, device=dev) * 2 - 1).requires_grad_(True)
 
-    def gather(t):  # stand-in for the all-gather: own rows at their place in the padded layout, zeros elsewhere
-        out = t.new_zeros((plan.num_gathered_rows,) + tuple(t.shape[1:]))
-        out[plan.gathered_offset: plan.gathered_offset + n] = t
-        return out
+    gather = parallel.LocalRowExchange(plan)  # stand-in for the exchange: own rows at their place, zeros elsewhere
 
     def step():
         x.grad = None
