@@ -16,6 +16,8 @@
 //   compact_index_kernel find_relational_compact_as_of_node_index with binary search
 //                        (kernel_enums.h:96-119): turns the binary-search compact kinds into the
 //                        direct-indexing form every edge kernel here takes.
+#include <cstdio>
+
 #include "common.cuh"
 
 namespace hetb {
@@ -340,6 +342,73 @@ extern "C" int hetb_rows_scatter_add(const int64_t *idx, int64_t n, const float 
   if (xlen % 4) return HETB_EUNSUPPORTED;
   rows_scatter_add_kernel<<<coo_grid(n * (xlen / 4)), kCThreads, 0, (cudaStream_t)stream>>>(idx, n, src, dst,
                                                                                            (int)(xlen / 4));
+  HETB_LAUNCH_OK();
+  return HETB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of hetb_hgt_enorm_to_unnormalized_bwd (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it). The [num_nodes, H] sum-of-products workspace
+// the caller of the existing entry point has to provide lives in a file-scope device array instead:
+// HETB_STATIC_SCRATCH_FLOATS floats (4 MB), held by every GPU that loads the library until exit.
+//
+// In host code the array's NAME is a host-side stand-in, not a device address; the address a kernel may
+// use is resolved with cudaGetSymbolAddress once per device, with that device current, and cached.
+// Every call shares the array and it keeps the last call's contents: the part a call uses is zeroed
+// on the call's stream first. Calls that overlap on the GPU (different streams, or the same device from
+// two threads) race on it. Calls nothing that allocates: no cudaMalloc / cudaFree, no torch.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) float g_static_scratch[HETB_STATIC_SCRATCH_FLOATS];
+
+static int static_scratch_ptr(float **out) {
+  constexpr int kMaxDevices = 64;
+  static float *ptrs[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) return (int)ce;
+  if (dev < 0 || dev >= kMaxDevices) return HETB_EUNSUPPORTED;
+  if (!ptrs[dev]) {
+    void *p = nullptr;
+    ce = cudaGetSymbolAddress(&p, g_static_scratch);  // device `dev` is current: its copy of the array
+    if (ce != cudaSuccess) return (int)ce;
+    ptrs[dev] = static_cast<float *>(p);
+  }
+  *out = ptrs[dev];
+  return HETB_OK;
+}
+
+extern "C" int hetb_hgt_enorm_to_unnormalized_bwd_static(const int64_t *dst, const int64_t *eids,
+                                                         const int64_t *rel_of_pos, const int64_t *rel_ptrs,
+                                                         int64_t num_rels, int64_t num_nodes, int64_t num_edges,
+                                                         const float *attn, const float *norm,
+                                                         const float *grad_norm, const float *mu, float *grad_attn,
+                                                         float *grad_mu, int H, void *stream) {
+  HETB_CHECK_ARG(num_nodes >= 0 && num_edges >= 0 && num_rels >= 0 && H > 0);
+  if (num_nodes > (int64_t)HETB_STATIC_SCRATCH_FLOATS / H) {
+    std::fprintf(stderr,
+                 "hetb_hgt_enorm_to_unnormalized_bwd_static: num_nodes * H = %lld exceeds the static scratch of %d "
+                 "floats; use hetb_hgt_enorm_to_unnormalized_bwd with a caller-provided workspace\n",
+                 (long long)num_nodes * H, (int)HETB_STATIC_SCRATCH_FLOATS);
+    return HETB_ETOOLARGE;
+  }
+  if (num_edges == 0) return HETB_OK;
+  HETB_CHECK_ARG(dst && eids && attn && norm && grad_norm && mu && grad_attn && grad_mu && (rel_of_pos || rel_ptrs) &&
+                 num_rels <= INT32_MAX);
+  float *sumprod = nullptr;
+  const int rc = static_scratch_ptr(&sumprod);
+  if (rc != HETB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t ce = cudaMemsetAsync(sumprod, 0, sizeof(float) * num_nodes * H, st);  // last call's contents
+  if (ce != cudaSuccess) return (int)ce;
+  int grid = coo_grid(num_edges * H);
+  enorm_bwd_sumprod_kernel<<<grid, kCThreads, 0, st>>>(dst, eids, num_edges, norm, grad_norm, sumprod, H);
+  HETB_LAUNCH_OK();
+  const int use_smem = (num_rels * H <= 4096) ? 1 : 0;
+  const size_t smem = use_smem ? (size_t)num_rels * H * sizeof(float) : 0;
+  if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+  enorm_bwd_apply_kernel<<<grid, kCThreads, smem, st>>>(dst, eids, rel_of_pos, rel_ptrs, (int)num_rels, num_edges, attn,
+                                                        norm, grad_norm, mu, sumprod, grad_attn, grad_mu, H, use_smem);
   HETB_LAUNCH_OK();
   return HETB_OK;
 }

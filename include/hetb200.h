@@ -34,6 +34,7 @@ extern "C" {
 #define HETB_EINVAL (-1)      /* null pointer / negative size */
 #define HETB_EUNSUPPORTED (-2) /* shape or kind outside what is implemented */
 #define HETB_ENOMEM (-3)      /* scratch allocation failed */
+#define HETB_ETOOLARGE (-4)   /* size beyond the fixed capacity of an allocation-free entry point */
 
 /* ABI version and a printable build string (replaces
  * hrt/buildutils/genutils/gen_headers.py:17-40 `build_debug_info`). */
@@ -446,6 +447,21 @@ int hetb_hgt_enorm_to_unnormalized_bwd(const int64_t *dst, const int64_t *eids, 
                                        int64_t num_edges, const float *attn, const float *norm,
                                        const float *grad_norm, const float *mu, float *sumprod_scratch,
                                        float *grad_attn, float *grad_mu, int H, void *stream);
+
+/* Allocation-free variant of hetb_hgt_enorm_to_unnormalized_bwd. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture,
+ * tight serving loops, harnesses that forbid it). Same inputs, outputs and maths; the [num_nodes, H]
+ * workspace is a static device array inside the library (HETB_STATIC_SCRATCH_FLOATS floats = 4 MB, held
+ * by every GPU that loads the library until exit) instead of a caller buffer. num_nodes * H beyond that
+ * returns HETB_ETOOLARGE (and says so on stderr); nothing is launched. Calls no cudaMalloc / cudaFree.
+ * All calls on a device share the array: it is zeroed on `stream` at the start of each call, and calls
+ * that overlap on the GPU (two streams, two threads) race. grad_mu must arrive zero-filled. */
+#define HETB_STATIC_SCRATCH_FLOATS (1 << 20)
+int hetb_hgt_enorm_to_unnormalized_bwd_static(const int64_t *dst, const int64_t *eids, const int64_t *rel_of_pos,
+                                              const int64_t *rel_ptrs, int64_t num_rels, int64_t num_nodes,
+                                              int64_t num_edges, const float *attn, const float *norm,
+                                              const float *grad_norm, const float *mu, float *grad_attn,
+                                              float *grad_mu, int H, void *stream);
 
 /* rgnn_gather_compact_to_non_compact (OpExport/RGNNOps.inc.h:449-600):
  * out[eids[i], :] = in[idx ? idx[i] : eids[i], :], rows of xlen floats (xlen % 4 == 0). */
