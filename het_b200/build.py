@@ -23,7 +23,7 @@ LIB = PKG / "lib"
 OBJ = PKG / "build"
 INCLUDE = ROOT / "include"
 
-CUDA_SOURCES = ["abi.cu", "edge_ops.cu", "edge_plan.cu", "edge_coo.cu", "segment_mm.cu", "segment_mm_tc.cu", "segment_mm_tc_wide.cu", "segment_mm_gradw_tc.cu", "convert.cu", "loss.cu", "optim.cu"]
+CUDA_SOURCES = ["abi.cu", "edge_ops.cu", "edge_plan.cu", "edge_coo.cu", "segment_mm.cu", "segment_mm_tc.cu", "segment_mm_tc_tma.cu", "segment_mm_tc_wide.cu", "segment_mm_gradw_tc.cu", "convert.cu", "loss.cu", "optim.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",

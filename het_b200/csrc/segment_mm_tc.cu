@@ -353,6 +353,19 @@ __global__ void __launch_bounds__(kThreads, 1)
 
 using namespace hetb;
 
+// defined in segment_mm_tc_tma.cu: the same item scheme with the A tile delivered by TMA
+int hetb_segment_mm_tc_tma(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
+                           const int64_t *c_idx, int c_heads, const int64_t *seg_ptrs, int64_t num_segs,
+                           int64_t num_rows, int H, int K, int N, int accumulate, int y_bf16, void *stream);
+
+static int g_segmm_tma = 1;  // 1: TMA-fed kernel first (falls through when unsupported), 0: register path only
+
+extern "C" int hetb_set_segment_mm_tma(int on) {
+  if (on != 0 && on != 1) return HETB_EINVAL;
+  g_segmm_tma = on;
+  return HETB_OK;
+}
+
 // Returns HETB_EUNSUPPORTED when the shape is outside the tensor-core path; the caller
 // (hetb_segment_mm) then uses the SIMT kernels.
 int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const float *W, float *Y,
@@ -364,6 +377,13 @@ int hetb_segment_mm_tc(const float *A, const int64_t *a_idx, int a_heads, const 
   if (y_bf16 && accumulate) return HETB_EUNSUPPORTED;
   const int probe = passes >> 4;
   passes &= 15;
+  // (a plain `Y += A.B` on contiguous rows is the one shape the register path measures faster: 0.246 vs 0.256 ms
+  //  at 1.94 M rows, both at 6 TB/s — profiles/r02r_segmm_tma_ab.log)
+  if (g_segmm_tma && passes == 3 && probe == 0 && !(accumulate && !c_idx && !a_idx)) {
+    const int rc = hetb_segment_mm_tc_tma(A, a_idx, a_heads, W, Y, c_idx, c_heads, seg_ptrs, num_segs, num_rows, H, K,
+                                          N, accumulate, y_bf16, stream);
+    if (rc != HETB_EUNSUPPORTED) return rc;
+  }
   if (a_heads == H && c_heads == H && H * K == tc::KK && H * N == tc::NN)
     bmode = (H == 1) ? tc::kDense : tc::kBlockDiag;
   else if (a_heads == 1 && c_heads == H && K == tc::KK && H * N == tc::NN)

@@ -1511,10 +1511,15 @@ void hetb200_set_segment_mm_impl(int64_t impl) {
   check_rc(hetb_set_segment_mm_impl((int)impl), "hetb200_set_segment_mm_impl");
 }
 
+void hetb200_set_segment_mm_tma(int64_t on) {
+  check_rc(hetb_set_segment_mm_tma((int)on), "hetb200_set_segment_mm_tma");
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_set_segment_mm_impl", hetb200_set_segment_mm_impl);
+  m.def("hetb200_set_segment_mm_tma", hetb200_set_segment_mm_tma);
   m.def("build_debug_info", build_debug_info);
   m.def("hetb200_launch_count", hetb200_launch_count);
   m.def("hetb200_stable_sort_by_key", hetb200_stable_sort_by_key);

@@ -80,6 +80,13 @@ int hetb_segment_mm_bf16out(const float *A, const int64_t *a_idx, int a_heads, c
  * 2 = tensor-core kernel only (HETB_EUNSUPPORTED if the shape is outside it). */
 int hetb_set_segment_mm_impl(int impl);
 
+/* A-operand path of the 64-wide tensor-core kernel (testing / A-B measurement): 1 (default) = the
+ * 128 x 64 tile of A reaches shared memory by TMA (cp.async.bulk.tensor tile copies for contiguous rows,
+ * tile::gather4 for gathered rows; plain whole-tile outputs leave by TMA too), 0 = producer warps load the
+ * rows through registers. Same products bit for bit. Replaces the shared-memory staging loops of
+ * RGNN/my_shmem_sgemm_func.cu.h:60-140 (no TMA in the reference). */
+int hetb_set_segment_mm_tma(int on);
+
 /* dW[s, h, :, :] += Σ_{i in segment s} A[a_idx?[i], (a_heads==1?0:h), :]^T
  *                                     · G[g_idx?[i], (g_heads==1?0:h), :]
  *   A : [*, a_heads, K]   G : [*, g_heads, N]   dW : [S, H, K, N] (caller

@@ -95,11 +95,15 @@ TC_SHAPES = [
 ]
 
 
-@pytest.fixture
-def force_tc():
+@pytest.fixture(params=[1, 0], ids=["tma", "registers"])
+def force_tc(request):
+    """Tensor-core kernels at every size, once with the A tile delivered by TMA (segment_mm_tc_tma.cu, the
+    default) and once through the producer warps' registers (segment_mm_tc.cu)."""
     from het_b200.kernels import K
     K.hetb200_set_segment_mm_impl(2)
+    K.hetb200_set_segment_mm_tma(request.param)
     yield
+    K.hetb200_set_segment_mm_tma(1)
     K.hetb200_set_segment_mm_impl(0)
 
 
@@ -129,6 +133,56 @@ def test_tensor_core_segment_mm(cuda, force_tc, n, e, r, H, Kd, Nd, head_one):
                                           gout.cpu(), a_heads)
         close(gX, gX_ref, f"tc grad_input/{gather_name}")
         close(gW, gW_ref, f"tc grad_weight/{gather_name}", rtol=2e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("gather,scatter,mode", [(False, False, "dense"), (True, False, "blockdiag"),
+                                                 (True, False, "heads_out"), (False, True, "dense"),
+                                                 (True, False, "bf16")])
+def test_tma_and_register_paths_give_the_same_bits(cuda, gather, scatter, mode):
+    """The TMA-fed kernel only changes how the A tile reaches shared memory: products, accumulation order and
+    stores are those of the register-path kernel, so plain stores agree bit for bit (C ABI, ragged tail,
+    segments cut inside tiles, rows past the end of the table in the last tile)."""
+    import ctypes
+    from het_b200.kernels import KERNEL_LIB
+    lib = ctypes.CDLL(str(KERNEL_LIB))
+    vp, i64, ci = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+    lib.hetb_segment_mm.argtypes = [vp, vp, ci, vp, vp, vp, ci, vp, i64, i64, ci, ci, ci, ci, vp]
+    lib.hetb_segment_mm_bf16out.argtypes = [vp, vp, ci, vp, vp, vp, vp, i64, i64, ci, ci, ci, vp]
+    g = torch.Generator().manual_seed(17)
+    table, rows = 3000, (20003 if gather else 3000 - 1)
+    sizes = torch.tensor([rows // 2 - 77, 0, 130, rows - (rows // 2 - 77) - 130])
+    seg = torch.cat([torch.zeros(1, dtype=torch.int64), sizes.cumsum(0)]).to(cuda)
+    A = torch.randn(table, 64, device=cuda)
+    a_idx = torch.randint(0, table, (rows,), generator=g).to(cuda) if gather else None
+    c_idx = torch.randperm(table, generator=g)[:rows].to(cuda) if scatter else None
+    H, K_, N_, ah, ch = {"dense": (1, 64, 64, 1, 1), "blockdiag": (4, 16, 16, 4, 4), "bf16": (4, 16, 16, 4, 4),
+                         "heads_out": (4, 64, 16, 1, 4)}[mode]
+    W = torch.randn(4, H, K_, N_, device=cuda) / K_ ** 0.5
+    st = torch.cuda.current_stream().cuda_stream
+    ptr = lambda t: None if t is None else t.data_ptr()
+    outs = []
+    lib.hetb_set_segment_mm_impl(2)
+    try:
+        for tma in (0, 1):
+            lib.hetb_set_segment_mm_tma(tma)
+            Y = torch.full((table if scatter else rows, 64), float("nan"), device=cuda,
+                           dtype=torch.bfloat16 if mode == "bf16" else torch.float32)
+            if mode == "bf16":
+                rc = lib.hetb_segment_mm_bf16out(ptr(A), ptr(a_idx), ah, ptr(W), ptr(Y), ptr(c_idx), ptr(seg), 4, rows,
+                                                 H, K_, N_, st)
+            else:
+                rc = lib.hetb_segment_mm(ptr(A), ptr(a_idx), ah, ptr(W), ptr(Y), ptr(c_idx), ch, ptr(seg), 4, rows,
+                                         H, K_, N_, 0, st)
+            assert rc == 0
+            torch.cuda.synchronize()
+            outs.append(torch.nan_to_num(Y.float(), nan=-7.0))
+    finally:
+        lib.hetb_set_segment_mm_tma(1)
+        lib.hetb_set_segment_mm_impl(0)
+    assert torch.equal(outs[0], outs[1])
+    want = R.segment_mm(A.cpu(), a_idx.cpu() if gather else None, W.cpu(), None, seg.cpu(), rows, ah)
+    got = outs[1][c_idx] if scatter else outs[1]
+    close(got.view(rows, H, N_), want, "tma vs oracle", **(dict(rtol=2e-2, atol=2e-2) if mode == "bf16" else {}))
 
 
 def test_tensor_core_matches_simt_bitwise_close(cuda):
