@@ -218,15 +218,19 @@ def cpu_dgl_baseline(wl, coo, steps, warmup, budget_s):
 # ---------------------------------------------------------------------------
 # Per-kernel roofline legs (timed alone, L2 flushed between launches)
 # ---------------------------------------------------------------------------
-def _time_kernel(torch, fn, flush, reps=10):
+def _time_kernel(torch, fn, flush, reps=10, pre=None):
     """Average device time (ms) of fn() over `reps` launches, each preceded by an L2 flush
     (a 256 MB write, larger than the 126 MB L2). CUDA events on torch's current stream,
-    which is the stream the torch_hrt ops launch on."""
+    which is the stream the torch_hrt ops launch on. `pre` (untimed) restores an input fn() consumes."""
     for _ in range(3):
+        if pre:
+            pre()
         fn()
     torch.cuda.synchronize()
     evs = []
     for _ in range(reps):
+        if pre:
+            pre()
         flush.add_(1.0)
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); fn(); b.record()
@@ -337,8 +341,8 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
     uniq_dst = int(torch.unique(coo["col_indices"]).numel())
     out = []
 
-    def leg(name, fn, nbytes, note):
-        ms = _time_kernel(torch, fn, flush)
+    def leg(name, fn, nbytes, note, pre=None):
+        ms = _time_kernel(torch, fn, flush, pre=pre)
         gbs = nbytes / (ms * 1e-3) / 1e9
         out.append({"kernel": name, "bound": "hbm", "achieved": round(gbs, 1), "peak": peak_gbs, "unit": "GB/s",
                     "frac": round(gbs / peak_gbs, 4), "peak_source": peak_src, "ms": round(ms, 4),
@@ -428,22 +432,23 @@ def kernel_rooflines_compact(trainer, peak_gbs, peak_src):
         ssum = torch.empty(N, H, device=dev)
         if getattr(layer, "fused_attention_aggregation_flag", False) and B.USE_EDGE_PLAN:
             pl, sc = g.get_edge_plan(), g.plan_scratch(H, D)
-            attn, lse = torch.empty(E, H, device=dev), torch.empty(N, H, device=dev)
+            attn, lse = torch.empty(0, H, device=dev), torch.empty(N, H, device=dev)   # no saved scores (default)
             fixed_f = pl["fwd"].blob.numel() * 4 - 3 * E * 4   # items, rows, lists: everything but the 3 per-position arrays
             leg("hgt_fused_fwd(plan walk: score + online softmax + aggregate)",
                 lambda: K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, wq, k, msg, mu, attn, lse, new_h,
                                                      sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"]),
-                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 3 * E * 4 + fixed_f + E * H * 4 + N * H * 4 + N * D * 4,
-                "left_c + k_unique + msg_c + int32 (src,urow,ucol) per position + items/rows ; score + lse + out")
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 3 * E * 4 + fixed_f + N * H * 4 + N * D * 4,
+                "left_c + k_unique + msg_c + int32 (src,urow,ucol) per position + items/rows ; lse + out "
+                "(nothing per edge is written: the backward recomputes the score)")
             gl, gk, gm, gmu = torch.zeros_like(wq), torch.empty_like(k), torch.empty_like(msg), torch.zeros(R, H, device=dev)
             fixed_b = pl["bwd"].blob.numel() * 4 - 4 * E * 4
             leg("hgt_fused_bwd(plan walk over (source, relation) runs)",
                 lambda: K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, wq, k, msg, mu, attn, lse, new_h, gout,
                                                      sc["gdot"], gl, gk, gm, gmu),
-                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 4 * E * 4 + fixed_b + E * H * 4 + 2 * N * H * 4 + 2 * N * D * 4
+                Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4 + 3 * E * 4 + fixed_b + 3 * N * H * 4 + 2 * N * D * 4
                 + Uc * D * 4 + uniq_src * D * 4 + Ur * D * 4,
-                "left_c,k,msg_c + int32 (dst,urow,ucol,fwd pos) per position + score,lse,gdoto,out,gout ; "
-                "grad_left_c + grad_k + grad_msg_c")
+                "left_c,k,msg_c + int32 (dst,urow,ucol) per position + lse,out,gout + (lse,gdoto) pairs ; "
+                "grad_left_c + grad_k + grad_msg_c (score recomputed, nothing per edge is read)")
         elif getattr(layer, "fused_attention_aggregation_flag", False):
             attn, t = torch.empty(E, H, device=dev), torch.empty(E, H, device=dev)
             leg("hgt_fused_score_softmax_aggregate_fwd(in-CSR, compact)",

@@ -1010,6 +1010,18 @@ def relational_fused_gat_csr_compact_with_logits(graph, feat_compact, er_compact
 USE_EDGE_PLAN = True  # False: the compact in-CSR / out-CSR walkers of csrc/edge_ops.cu (int64 indices, no max-subtraction)
 
 
+# Variants of the HGT plan backward (A/B partners of the default, measured in tools/bench_edge_plan.py and
+# covered by tests/test_gpu_fused_ops.py). Default: ONE walk that recomputes the raw score from the two rows it
+# holds anyway; the forward saves nothing per edge.
+# SAVE_HGT_SCORES: the forward stores the raw score per edge and the backward reads it back (one more random
+#   access per edge: 3.99 ms against the default at mag size).
+# TWO_PASS_HGT_BACKWARD: hetb_hgt_fused_bwd_plan2 — the destination-side gradient is owned by a second,
+#   destination-major walk instead of one vector reduction per edge: no atomics on grad_left, run-to-run
+#   identical, but 4.75 ms (needs the saved scores: it overwrites them with their gradient).
+SAVE_HGT_SCORES = False
+TWO_PASS_HGT_BACKWARD = False
+
+
 class HGTFusedAttentionAggregationPlan(th.autograd.Function):
     """Same op as HGTFusedAttentionAggregationCSRCompact (inner product + edge softmax + message
     aggregation, compact inputs) on the graph's walk plans: int32 indices, (destination, relation)-
@@ -1025,7 +1037,7 @@ class HGTFusedAttentionAggregationPlan(th.autograd.Function):
         dev = mu.device
         new_h = th.empty((n, h, f), dtype=th.float32, device=dev)
         lse = th.empty((n, h), dtype=th.float32, device=dev)
-        attn = th.empty((e, h), dtype=th.float32, device=dev)
+        attn = th.empty((e, h) if (SAVE_HGT_SCORES or TWO_PASS_HGT_BACKWARD) else (0, h), dtype=th.float32, device=dev)
         K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, left_compact, k, message_compact, mu, attn, lse,
                                      new_h, sc["part_m"], sc["part_s"], sc["part_acc"], sc["ssum"])
         ctx.graph = graph
@@ -1040,12 +1052,21 @@ class HGTFusedAttentionAggregationPlan(th.autograd.Function):
         h, f = mu.size(1), msg.size(2)
         sc = graph.plan_scratch(h, h * f)
         f32 = dict(dtype=th.float32, device=mu.device)
-        grad_left = th.zeros(left.shape, **f32)
         grad_mu = th.zeros(mu.shape, **f32)
         grad_k = th.empty(k.shape, **f32)
         grad_msg = th.empty(msg.shape, **f32)
-        K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
-                                     gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
+        if TWO_PASS_HGT_BACKWARD and attn.numel():
+            # attn is this node's own buffer and is consumed here (score in, gradient of the score out)
+            assert not getattr(ctx, "attn_consumed", False), "this node's backward overwrites its saved scores: no second pass"
+            ctx.attn_consumed = True
+            grad_left = th.empty(left.shape, **f32)
+            K.hetb200_hgt_fused_bwd_plan2(pl["bwd"].blob, pl["bwd"].meta, pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu,
+                                          attn, lse, new_h, gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg,
+                                          grad_mu)
+        else:
+            grad_left = th.zeros(left.shape, **f32)
+            K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
+                                         gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
         return None, grad_left, grad_k, grad_msg, grad_mu
 
 
@@ -1082,7 +1103,7 @@ class HGTLayerCoreBF16Tables(th.autograd.Function):
         sc = graph.plan_scratch(hh, d)
         new_h = th.empty((n, hh, f), dtype=th.float32, device=dev)
         lse = th.empty((n, hh), dtype=th.float32, device=dev)
-        attn = th.empty((e, hh), dtype=th.float32, device=dev)
+        attn = th.empty((e, hh) if (SAVE_HGT_SCORES or TWO_PASS_HGT_BACKWARD) else (0, hh), dtype=th.float32, device=dev)
         K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu, attn, lse, new_h, sc["part_m"],
                                      sc["part_s"], sc["part_acc"], sc["ssum"])
         ctx.graph = graph
@@ -1099,10 +1120,19 @@ class HGTLayerCoreBF16Tables(th.autograd.Function):
         hh, f = mu.size(1), msg.size(2)
         sc = graph.plan_scratch(hh, hh * f)
         f32 = dict(dtype=th.float32, device=mu.device)
-        grad_left, grad_mu = th.zeros(left.shape, **f32), th.zeros(mu.shape, **f32)
+        grad_mu = th.zeros(mu.shape, **f32)
         grad_k, grad_msg = th.empty(k.shape, **f32), th.empty(msg.shape, **f32)
-        K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
-                                     gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
+        if TWO_PASS_HGT_BACKWARD and attn.numel():
+            assert not getattr(ctx, "attn_consumed", False), "this node's backward overwrites its saved scores: no second pass"
+            ctx.attn_consumed = True
+            grad_left = th.empty(left.shape, **f32)
+            K.hetb200_hgt_fused_bwd_plan2(pl["bwd"].blob, pl["bwd"].meta, pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu,
+                                          attn, lse, new_h, gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg,
+                                          grad_mu)
+        else:
+            grad_left = th.zeros(left.shape, **f32)
+            K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, attn, lse, new_h,
+                                         gradout.contiguous(), sc["gdot"], grad_left, grad_k, grad_msg, grad_mu)
         grad_h = th.empty_like(h, memory_format=th.contiguous_format)
         grad_wk = th.zeros_like(k_linears, memory_format=th.contiguous_format)
         K.backward_rgnn_relational_matmul_no_scatter_gather_list(

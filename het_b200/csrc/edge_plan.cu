@@ -71,6 +71,33 @@ __device__ __forceinline__ float group_sum_m(float v, int width, unsigned mask) 
   return v;
 }
 
+// HW > 0: the head width is a compile-time constant (the shapes of the BASELINE configs), the reduction is
+// HW/2 .. 1 shuffles with no loop; HW == 0: the run-time loop above. The walks are bound by issue slots as
+// much as by memory (58 % of the slots busy at mag size), and the loop form costs ~11 instructions per step.
+template <int HW>
+__device__ __forceinline__ float group_sum_t(float v, int width, unsigned mask) {
+  if (HW == 0) return group_sum_m(v, width, mask);
+#pragma unroll
+  for (int o = HW >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+  return v;
+}
+
+// The raw attention score <left, kv> with a FIXED contraction order: the forward walk and the backward walk
+// (which recomputes the score instead of reading a saved copy) must produce the same bits, and the compiler
+// is free to contract a*b + c*d either way in different contexts.
+__device__ __forceinline__ float score_dot4(float4 a, float4 b) {
+  return __fmaf_rn(a.w, b.w, __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, __fmul_rn(a.x, b.x))));
+}
+
+// 2^x, one MUFU: inputs below -126 give 0 (softmax weights that small do not matter), no denormal fix-up.
+// The walks keep their logits in the log2 domain (x * log2(e)) so that this is the whole exponential.
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+
 __device__ __forceinline__ void atomic_max_float(float *addr, float v) {
   if (v >= 0.f) atomicMax(reinterpret_cast<int *>(addr), __float_as_int(v));
   else atomicMin(reinterpret_cast<unsigned *>(addr), __float_as_uint(v));
@@ -122,13 +149,13 @@ __global__ void __launch_bounds__(kPThreads)
   if (i >= num_pslots) return;
   const int64_t x = __ldg(pslot + i), d = __ldg(pslot_row + i);
   const int h = l / hw;
-  const float w = __expf(__ldg(part_m + x * H + h) - __ldg(lse + d * H + h));
+  const float w = ex2_ftz(__ldg(part_m + x * H + h) - __ldg(lse + d * H + h));  // both in the log2 domain
   const float4 a = ldcs4(part_acc + x * D + 4 * l);
   red_add4(ret + d * D + 4 * l, make_float4(w * a.x, w * a.y, w * a.z, w * a.w));
   if ((l % hw) == 0) atomicAdd(ssum + d * H + h, w * __ldg(part_s + x * H + h));
 }
 
-// Split rows: ret /= ssum; lse = M + log(ssum).
+// Split rows: ret /= ssum; lse = M + log(ssum) (natural units on return).
 template <int LPR>
 __global__ void __launch_bounds__(kPThreads)
     plan_fwd_normalize_kernel(const int *__restrict__ fix_rows, int num_fix, const float *__restrict__ ssum,
@@ -144,7 +171,7 @@ __global__ void __launch_bounds__(kPThreads)
   const float inv = s > 0.f ? 1.f / s : 0.f;
   float4 v = *reinterpret_cast<const float4 *>(ret + d * D + 4 * l);
   st4(ret + d * D + 4 * l, make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv));
-  if ((l % hw) == 0) lse[d * H + h] = lse[d * H + h] + __logf(s);
+  if ((l % hw) == 0) lse[d * H + h] = lse[d * H + h] * kLn2 + __logf(s);  // M was kept in the log2 domain
 }
 
 // ---------------------------------------------------------------------------
@@ -157,7 +184,7 @@ __global__ void __launch_bounds__(kPThreads)
 // MODE_RGAT (same walk, RGAT's logits): x = leaky_relu(el[M(p),h] + er[L(p),h]), msg = feat
 // (GAT/FusedGAT.cu.h:123-222,33-116); nothing per edge is saved (the backward recomputes x).
 // ---------------------------------------------------------------------------
-template <typename T, int LPR, bool MODE_RGAT>
+template <typename T, int LPR, bool MODE_RGAT, int HW>
 __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
     plan_fwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
                          const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
@@ -168,13 +195,19 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
                          const float *__restrict__ el, const float *__restrict__ er, float slope,  // RGAT
                          float *__restrict__ attn, float *__restrict__ lse, float *__restrict__ ret,
                          float *__restrict__ part_m, float *__restrict__ part_s, float *__restrict__ part_acc,
-                         int H, int hw) {
+                         int H, int hw_rt) {
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
   constexpr int U = HETB_PLAN_FWD_U;  // positions in flight per lane group
+  const int hw = HW ? HW : hw_rt;
   const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int g = blockIdx.x * GROUPS + grp;
   if (g >= num_items) return;  // whole lane group leaves: its lanes are in no other group's mask
+  // Sub-warp shuffle masks on purpose: the lane groups of a warp run their items INDEPENDENTLY (they diverge at
+  // the first row change and are scheduled as separate instruction streams from then on), which is worth more
+  // than the ~8 instructions per shuffle the compiler spends on the convergence check of a partial mask: a
+  // lockstep version with full-warp shuffles and 30 % fewer instructions measured 2.55 ms against 2.07
+  // (profiles/r02u_walk_variants.log).
   const unsigned gm = group_mask<LPR>();
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
@@ -189,7 +222,7 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
     if (row_start >= p0 && row_end <= p1) {  // the whole row was walked here
       const float inv = s > 0.f ? 1.f / s : 0.f;
       st4(ret + d * D + 4 * l, make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv));
-      if (leader) lse[d * H + h] = m + __logf(s);
+      if (leader) lse[d * H + h] = m * kLn2 + __logf(s);  // m is kept in the log2 domain
     } else {  // a piece of a split row: partial (m, s, acc) into this item's head / tail slot
       const int64_t x = 2 * (int64_t)g + (row_start < p0 ? 0 : 1);
       stcs4(part_acc + x * D + 4 * l, acc);
@@ -224,7 +257,7 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
       if (!MODE_RGAT) {
         lv[q] = ld_row4<T>(left, li[q], D, l);
         kvv[q] = ld_row4<T>(kv, sn[q], D, l);
-        xs[q] = __ldg(mu + __ldg(ucol_rel + li[q]) * H + h);
+        xs[q] = __ldg(mu + __ldg(ucol_rel + li[q]) * H + h) * kLog2e;
       } else {
         xs[q] = __ldg(el + (int64_t)mi[q] * H + h) + __ldg(er + (int64_t)li[q] * H + h);
       }
@@ -245,14 +278,14 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
         }
         float x;
         if (!MODE_RGAT) {
-          const float a = group_sum_m(dot4(lv[q], kvv[q]), hw, gm);
-          if (leader) attn[(int64_t)pp * H + h] = a;
+          const float a = group_sum_t<HW>(score_dot4(lv[q], kvv[q]), hw, gm);
+          if (leader && attn) attn[(int64_t)pp * H + h] = a;
           x = a * xs[q];
         } else {
-          x = xs[q] > 0.f ? xs[q] : slope * xs[q];
+          x = (xs[q] > 0.f ? xs[q] : slope * xs[q]) * kLog2e;
         }
-        const float mn = fmaxf(m, x);
-        const float sc = __expf(m - mn), w = __expf(x - mn);
+        const float mn = fmaxf(m, x);  // log2 domain: exp(v) = 2^(v·log2 e)
+        const float sc = ex2_ftz(m - mn), w = ex2_ftz(x - mn);
         acc.x = fmaf(acc.x, sc, w * mv[q].x);
         acc.y = fmaf(acc.y, sc, w * mv[q].y);
         acc.z = fmaf(acc.z, sc, w * mv[q].z);
@@ -282,11 +315,14 @@ __global__ void __launch_bounds__(kPThreads)
   if (aux && (l % hw) == 0) aux[r * H + l / hw] = 0.f;
 }
 
-// <a[d,h,:], b[d,h,:]> per (row, head): the softmax Jacobian's per-destination term <gout, out>.
+// <a[d,h,:], b[d,h,:]> per (row, head): the softmax Jacobian's per-destination term <gout, out>, stored
+// NEXT TO lse[d,h] as out[d] = (lse[d,0..H), dot[d,0..H)): the backward walks read both per edge, and what a
+// random access costs the memory system is the access, not its 16 bytes (37 G rows/s for anything up to
+// 128 B, profiles/r02_random_rows.log) — one 32-byte read per edge instead of two 16-byte reads.
 template <int LPR>
 __global__ void __launch_bounds__(kPThreads)
-    plan_rowdot_kernel(const float *__restrict__ a, const float *__restrict__ b, int64_t num_rows,
-                       float *__restrict__ out, int H, int hw) {
+    plan_rowdot_kernel(const float *__restrict__ a, const float *__restrict__ b, const float *__restrict__ lse,
+                       int64_t num_rows, float *__restrict__ out, int H, int hw) {
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
   const int g = threadIdx.x / LPR, l = threadIdx.x % LPR;
@@ -295,7 +331,10 @@ __global__ void __launch_bounds__(kPThreads)
   const unsigned gm = group_mask<LPR>();
   const float4 x = ldg4(a + d * D + 4 * l), y = ldg4(b + d * D + 4 * l);
   const float v = group_sum_m(dot4(x, y), hw, gm);
-  if ((l % hw) == 0) out[d * H + l / hw] = v;
+  if ((l % hw) == 0) {
+    out[d * 2 * H + l / hw] = __ldg(lse + d * H + l / hw) * kLog2e;  // the walks exponentiate in base 2
+    out[d * 2 * H + H + l / hw] = v;
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -310,8 +349,20 @@ __global__ void __launch_bounds__(kPThreads)
 //   grad_left[L(p),h,:] += ga · kv[s,h,:]         vector reduction (destination side: the only
 //                                                 gradient the source-major order cannot own)
 // Rows / runs split across items (bit 31 of nz_rows[j] / urow_rel[u]) are pre-zeroed and reduced.
+// TWO_PASS: the destination-side gradient is not reduced here. The walk leaves ga — the gradient of the raw
+// score — in `gattn` at the edge's forward position (in place of the score it has just read there: the
+// sector is in L2), and plan_hgt_grad_left_kernel, a second walk in the FORWARD (destination, relation)
+// order, owns grad_left[L] as a register accumulator: 256 B of kv[src] per edge instead of the 512 B
+// read-modify-write of a vector reduction, no zero-fill of grad_left, and a result that does not depend
+// on the order atomics land in.
 // ---------------------------------------------------------------------------
-template <typename T, int LPR>
+// SCORE: where the raw score a comes from. kRecompute (the default): a = <left[L], kv[s]> again — both rows
+// are in registers (kv[s] is the row constant, left[L] is gathered for grad_kv anyway), same operation order
+// as the forward, so the same bits — and the forward saves NOTHING per edge; kSaved: read from attn at the
+// edge's forward position (one more random access per edge: 3.99 vs 3.0x ms at mag size).
+enum ScoreSource : int { kSaved = 0, kRecompute = 1 };
+
+template <typename T, int LPR, bool TWO_PASS, int SCORE, int HW>
 __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
     plan_hgt_bwd_walk_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
                              const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
@@ -319,11 +370,13 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
                              const int *__restrict__ p_msg, const int *__restrict__ p_perm,
                              const int *__restrict__ urow_rel, int num_rels, const T *__restrict__ left,
                              const T *__restrict__ kv, const T *__restrict__ msg, const float *__restrict__ mu,
-                             const float *__restrict__ attn, const float *__restrict__ lse,
-                             const float *__restrict__ gdoto, const float *__restrict__ gout,
+                             const float *__restrict__ attn,
+                             const float *__restrict__ lse_gdoto /* [N, 2H]: plan_rowdot_kernel */,
+                             const float *__restrict__ gout,
                              float *__restrict__ grad_left, float *__restrict__ grad_kv,
-                             float *__restrict__ grad_msg, float *__restrict__ grad_mu, int H, int hw,
-                             int use_smem) {
+                             float *__restrict__ grad_msg, float *__restrict__ grad_mu, int H, int hw_rt,
+                             int use_smem, float *gattn /* TWO_PASS: score in, ga out; not restrict, never __ldg */) {
+  const int hw = HW ? HW : hw_rt;
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
   constexpr int U = HETB_PLAN_BWD_U;
@@ -335,7 +388,7 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
   }
   const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
   const int g = blockIdx.x * GROUPS + grp;
-  const unsigned gm = group_mask<LPR>();
+  const unsigned gm = group_mask<LPR>();  // sub-warp masks on purpose: see plan_fwd_walk_kernel
   const int h = l / hw;
   const bool leader = (l % hw) == 0;
   if (g < num_items) {
@@ -344,12 +397,14 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
     int rowword = __ldg(nz_rows + j);
     int64_t srow = rowword & 0x7fffffff;
     int row_end = __ldg(nz_ptr + j + 1);
-    float4 kvr = ld_row4<T>(kv, srow, D, l);
+    constexpr bool kNeedKv = !TWO_PASS || SCORE == kRecompute;
+    float4 kvr = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (kNeedKv) kvr = ld_row4<T>(kv, srow, D, l);
     float4 acc_k = make_float4(0.f, 0.f, 0.f, 0.f);
     // run state
     int cur_u = -1, relword = 0;
     float4 msgr = make_float4(0.f, 0.f, 0.f, 0.f), acc_m = make_float4(0.f, 0.f, 0.f, 0.f);
-    float mu_r = 0.f, acc_mu = 0.f;
+    float mu_r = 0.f, mu_r2 = 0.f, acc_mu = 0.f;
 
     auto flush_run = [&]() {
       if (cur_u < 0) return;
@@ -374,12 +429,12 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
         dn[q] = __ldg(p_dst + pp);
         li[q] = __ldg(p_left + pp);
         ui[q] = __ldg(p_msg + pp);
-        pq[q] = __ldg(p_perm + pp);
+        if (SCORE == kSaved || TWO_PASS) pq[q] = __ldg(p_perm + pp);
       }
     };
     if (HETB_PLAN_PREFETCH) load_idx(p0);
     for (int p = p0; p < p1; p += U) {
-      int lic[U], uic[U];
+      int lic[U], uic[U], pqc[U];
       if (!HETB_PLAN_PREFETCH) load_idx(p);
       float aa[U], ls[U], cc[U];
       float4 go[U], lv[U];
@@ -387,11 +442,12 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
       for (int q = 0; q < U; ++q) {
         go[q] = ldg4(gout + (int64_t)dn[q] * D + 4 * l);
         lv[q] = ld_row4<T>(left, li[q], D, l);
-        aa[q] = __ldg(attn + (int64_t)pq[q] * H + h);
-        ls[q] = __ldg(lse + (int64_t)dn[q] * H + h);
-        cc[q] = __ldg(gdoto + (int64_t)dn[q] * H + h);
+        if (SCORE == kSaved) aa[q] = TWO_PASS ? gattn[(int64_t)pq[q] * H + h] : __ldg(attn + (int64_t)pq[q] * H + h);
+        ls[q] = __ldg(lse_gdoto + (int64_t)dn[q] * 2 * H + h);
+        cc[q] = __ldg(lse_gdoto + (int64_t)dn[q] * 2 * H + H + h);
         lic[q] = li[q];
         uic[q] = ui[q];
+        pqc[q] = pq[q];
       }
       if (HETB_PLAN_PREFETCH && p + U < p1) load_idx(p + U);  // indices of the next batch while this batch's rows are in flight
 #pragma unroll
@@ -406,7 +462,7 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
             rowword = __ldg(nz_rows + j);
             srow = rowword & 0x7fffffff;
             row_end = __ldg(nz_ptr + j + 1);
-            kvr = ld_row4<T>(kv, srow, D, l);
+            if (kNeedKv) kvr = ld_row4<T>(kv, srow, D, l);
             acc_k = make_float4(0.f, 0.f, 0.f, 0.f);
           }
           if (uic[q] != cur_u) {
@@ -415,18 +471,24 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
             relword = __ldg(urow_rel + cur_u);
             msgr = ld_row4<T>(msg, cur_u, D, l);
             mu_r = __ldg(mu + (relword & 0x7fffffff) * H + h);
+            mu_r2 = mu_r * kLog2e;
             acc_m = make_float4(0.f, 0.f, 0.f, 0.f);
             acc_mu = 0.f;
           }
-          const float sdot = group_sum_m(dot4(go[q], msgr), hw, gm) - cc[q];
-          const float nrm = __expf(aa[q] * mu_r - ls[q]);
+          if (SCORE == kRecompute) aa[q] = group_sum_t<HW>(score_dot4(lv[q], kvr), hw, gm);  // the forward's a, bit for bit
+          const float sdot = group_sum_t<HW>(dot4(go[q], msgr), hw, gm) - cc[q];
+          const float nrm = ex2_ftz(aa[q] * mu_r2 - ls[q]);  // ls = lse·log2(e) (plan_rowdot_kernel)
           const float sg = sdot * nrm;
           const float ga = sg * mu_r;
           acc_mu = fmaf(sg, aa[q], acc_mu);
           fma4(acc_m, nrm, go[q]);
           fma4(acc_k, ga, lv[q]);
-          red_add4(grad_left + (int64_t)lic[q] * D + 4 * l,
-                   make_float4(ga * kvr.x, ga * kvr.y, ga * kvr.z, ga * kvr.w));
+          if (TWO_PASS) {
+            if (leader) gattn[(int64_t)pqc[q] * H + h] = ga;
+          } else {
+            red_add4(grad_left + (int64_t)lic[q] * D + 4 * l,
+                     make_float4(ga * kvr.x, ga * kvr.y, ga * kvr.z, ga * kvr.w));
+          }
         }
       }
     }
@@ -443,13 +505,82 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_BWD_MINB)
 }
 
 // ---------------------------------------------------------------------------
+// Second walk of the two-pass HGT backward, over the FORWARD plan ((destination, relation)-sorted):
+//   grad_left[L,h,:] = sum over the positions p of run L of ga[p,h] * kv[src(p),h,:]
+// (the destination half of RGNN/InnerProductEdgeParallel.cu.h:119-202, which the reference accumulates
+// with one atomicAdd per edge and element). A (destination, relation) run is a register accumulator
+// stored once; a run cut by an item boundary (hub rows only: listed in the plan's fix_runs and
+// pre-zeroed) reduces its pieces. ga is read in position order (coalesced).
+// ---------------------------------------------------------------------------
+template <typename T, int LPR>
+__global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
+    plan_hgt_grad_left_kernel(const int *__restrict__ item_ptr, int num_items, int num_positions,
+                              const int *__restrict__ p_src, const int *__restrict__ p_left,
+                              const T *__restrict__ kv, const float *__restrict__ gattn,
+                              float *__restrict__ grad_left, int H, int hw) {
+  constexpr int GROUPS = kPThreads / LPR;
+  constexpr int D = LPR * 4;
+  constexpr int U = HETB_PLAN_FWD_U;
+  const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int g = blockIdx.x * GROUPS + grp;
+  if (g >= num_items) return;
+  const int h = l / hw;
+  const int p0 = __ldg(item_ptr + g), p1 = __ldg(item_ptr + g + 1);
+  int cur = __ldg(p_left + p0);
+  bool open_head = p0 > 0 && __ldg(p_left + p0 - 1) == cur;  // the first run began in an earlier item
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  auto flush = [&](bool open_tail) {
+    float *dst = grad_left + (int64_t)cur * D + 4 * l;
+    if (open_head || open_tail) red_add4(dst, acc);
+    else st4(dst, acc);
+  };
+  int sn[U], li[U];
+  auto load_idx = [&](int p) {
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int pp = (p + q < p1) ? p + q : p1 - 1;
+      sn[q] = __ldg(p_src + pp);
+      li[q] = __ldg(p_left + pp);
+    }
+  };
+  if (HETB_PLAN_PREFETCH) load_idx(p0);
+  for (int p = p0; p < p1; p += U) {
+    if (!HETB_PLAN_PREFETCH) load_idx(p);
+    float4 kvv[U];
+    float ga[U];
+    int lic[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      kvv[q] = ld_row4<T>(kv, sn[q], D, l);
+      const int pp = (p + q < p1) ? p + q : p1 - 1;
+      ga[q] = __ldcs(gattn + (int64_t)pp * H + h);
+      lic[q] = li[q];
+    }
+    if (HETB_PLAN_PREFETCH && p + U < p1) load_idx(p + U);
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      if (p + q < p1) {  // uniform inside the lane group
+        if (lic[q] != cur) {
+          flush(false);
+          open_head = false;
+          cur = lic[q];
+          acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        fma4(acc, ga[q], kvv[q]);
+      }
+    }
+  }
+  flush(p1 < num_positions && __ldg(p_left + p1) == cur);
+}
+
+// ---------------------------------------------------------------------------
 // RGAT backward in plan form: one walk over the positions grouped by compact (relation, source)
 // row u (GAT/FusedGATBackward.cu.h:31-148 restated): feat[u], el[u] are run constants,
 // grad_feat[u] / grad_el[u] register accumulators with one store per run; the normalised score
 // is recomputed as exp(lrelu(el[u] + er[L]) − lse[d]); <gout[d], ret[d]> comes from the pre-pass.
 // grad_er takes one scalar atomic per edge and head (destination side).
 // ---------------------------------------------------------------------------
-template <typename T, int LPR>
+template <typename T, int LPR, int HW>
 __global__ void __launch_bounds__(kPThreads)
     plan_rgat_bwd_walk_kernel(const int *__restrict__ item_ptr, int num_items, const int *__restrict__ p_dst,
                               const int *__restrict__ p_left, const int *__restrict__ p_msg,
@@ -457,8 +588,9 @@ __global__ void __launch_bounds__(kPThreads)
                               const float *__restrict__ el, const float *__restrict__ er,
                               const float *__restrict__ lse, const float *__restrict__ gdotr,
                               const float *__restrict__ gout, float *__restrict__ grad_feat,
-                              float *__restrict__ grad_el, float *__restrict__ grad_er, int H, int hw,
+                              float *__restrict__ grad_el, float *__restrict__ grad_er, int H, int hw_rt,
                               float slope) {
+  const int hw = HW ? HW : hw_rt;
   constexpr int GROUPS = kPThreads / LPR;
   constexpr int D = LPR * 4;
   constexpr int U = 4;
@@ -498,8 +630,8 @@ __global__ void __launch_bounds__(kPThreads)
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       go[q] = ldg4(gout + (int64_t)dn[q] * D + 4 * l);
-      ls[q] = __ldg(lse + (int64_t)dn[q] * H + h);
-      cc[q] = __ldg(gdotr + (int64_t)dn[q] * H + h);
+      ls[q] = __ldg(gdotr + (int64_t)dn[q] * 2 * H + h);  // (lse, <gout, ret>) pairs: plan_rowdot_kernel
+      cc[q] = __ldg(gdotr + (int64_t)dn[q] * 2 * H + H + h);
       erv[q] = __ldg(er + (int64_t)li[q] * H + h);
     }
 #pragma unroll
@@ -514,9 +646,9 @@ __global__ void __launch_bounds__(kPThreads)
           acc_f = make_float4(0.f, 0.f, 0.f, 0.f);
           acc_el = 0.f;
         }
-        const float sdot = group_sum_m(dot4(go[q], featr), hw, gm) - cc[q];
+        const float sdot = group_sum_t<HW>(dot4(go[q], featr), hw, gm) - cc[q];
         const float x = elr + erv[q];
-        const float a = __expf((x > 0.f ? x : slope * x) - ls[q]);
+        const float a = ex2_ftz((x > 0.f ? x : slope * x) * kLog2e - ls[q]);  // ls = lse·log2(e)
         fma4(acc_f, a, go[q]);
         if (leader) {
           const float v = sdot * a * (x > 0.f ? 1.f : slope);
@@ -546,6 +678,13 @@ static int plan_lpr(int H, int F) {
     default: return HETB_EUNSUPPORTED;              \
   }
 
+// The walk kernels also take the head width as a constant for the two shapes of the BASELINE configs
+// (64-float rows: 4 heads of 16, 1 head of 64); every other shape runs the generic HWC = 0 instantiation.
+#define PLAN_LPR_HW(lpr, hw, CALL)                                         \
+  if ((lpr) == 16 && (hw) == 4) { constexpr int L = 16, HWC = 4; CALL; }   \
+  else if ((lpr) == 16 && (hw) == 16) { constexpr int L = 16, HWC = 16; CALL; } \
+  else { constexpr int HWC = 0; PLAN_LPR(lpr, CALL) }
+
 static inline unsigned grid_for(int64_t n, int groups) { return (unsigned)(n > 0 ? ceil_div64(n, groups) : 1); }
 
 template <typename T, bool RGAT>
@@ -564,7 +703,7 @@ static int fwd_plan_launch(const hetb_walk_plan *pl, const T *left, const T *kv,
     HETB_LAUNCH_OK();
   }
   if (pl->num_items == 0) return HETB_OK;
-  PLAN_LPR(lpr, (plan_fwd_walk_kernel<T, L, RGAT><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
+  PLAN_LPR_HW(lpr, hw, (plan_fwd_walk_kernel<T, L, RGAT, HWC><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
                     pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_b,
                     pl->idx_c, pl->row_rel, left, kv, msg, mu, el, er, slope, attn, lse, ret, part_m, part_s,
                     part_acc, H, hw)));
@@ -598,7 +737,7 @@ extern "C" int hetb_hgt_fused_fwd_plan(const hetb_walk_plan *plan, const void *l
                                        float *ret, float *part_m, float *part_s, float *part_acc, float *ssum,
                                        int H, int F, void *stream) {
   HETB_CHECK_ARG(plan_ok_fwd(plan) && lse && ret);
-  HETB_CHECK_ARG(plan->num_items == 0 || (left && kv && msg && mu && attn && plan->idx_a && plan->row_rel));
+  HETB_CHECK_ARG(plan->num_items == 0 || (left && kv && msg && mu && plan->idx_a && plan->row_rel));  // attn optional
   HETB_CHECK_ARG(plan->num_pslots == 0 || (part_m && part_s && part_acc && ssum));
   cudaStream_t st = (cudaStream_t)stream;
   if (table_dtype == HETB_DTYPE_F32)
@@ -630,10 +769,11 @@ extern "C" int hetb_rgat_fused_fwd_plan(const hetb_walk_plan *plan, const void *
 }
 
 template <typename T>
-static int hgt_bwd_plan_launch(const hetb_walk_plan *pl, int64_t num_rels, int64_t num_dst, const T *left,
-                               const T *kv, const T *msg, const float *mu, const float *attn, const float *lse,
-                               const float *out, const float *gout, float *gdoto, float *grad_left, float *grad_kv,
-                               float *grad_msg, float *grad_mu, int H, int F, cudaStream_t st) {
+static int hgt_bwd_plan_launch(const hetb_walk_plan *pl, const hetb_walk_plan *fwd, int64_t num_rels, int64_t num_dst,
+                               const T *left, const T *kv, const T *msg, const float *mu, const float *attn,
+                               float *gattn, const float *lse, const float *out, const float *gout, float *gdoto,
+                               float *grad_left, float *grad_kv, float *grad_msg, float *grad_mu, int H, int F,
+                               cudaStream_t st) {
   const int lpr = plan_lpr(H, F);
   if (!lpr) return HETB_EUNSUPPORTED;
   const int groups = kPThreads / lpr;
@@ -649,15 +789,40 @@ static int hgt_bwd_plan_launch(const hetb_walk_plan *pl, int64_t num_rels, int64
     HETB_LAUNCH_OK();
   }
   if (pl->num_items == 0) return HETB_OK;
-  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, out, num_dst, gdoto, H,
-                                                                                     hw)));
+  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, out, lse, num_dst, gdoto,
+                                                                                     H, hw)));
   HETB_LAUNCH_OK();
   const int use_smem = (num_rels * H <= kMaxSmemMuPlan) ? 1 : 0;
   const size_t smem = use_smem ? (size_t)num_rels * H * sizeof(float) : 0;
-  PLAN_LPR(lpr, (plan_hgt_bwd_walk_kernel<T, L><<<grid_for(pl->num_items, groups), kPThreads, smem, st>>>(
+  if (!fwd) {
+    if (attn) {
+      PLAN_LPR_HW(lpr, hw, (plan_hgt_bwd_walk_kernel<T, L, false, kSaved, HWC><<<grid_for(pl->num_items, groups), kPThreads, smem, st>>>(
+                        pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_c,
+                        pl->idx_b, pl->idx_d, pl->row_rel, (int)num_rels, left, kv, msg, mu, attn, gdoto, gout,
+                        grad_left, grad_kv, grad_msg, grad_mu, H, hw, use_smem, nullptr)));
+    } else {
+      PLAN_LPR_HW(lpr, hw, (plan_hgt_bwd_walk_kernel<T, L, false, kRecompute, HWC><<<grid_for(pl->num_items, groups), kPThreads, smem, st>>>(
+                        pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_c,
+                        pl->idx_b, pl->idx_d, pl->row_rel, (int)num_rels, left, kv, msg, mu, nullptr, gdoto, gout,
+                        grad_left, grad_kv, grad_msg, grad_mu, H, hw, use_smem, nullptr)));
+    }
+    HETB_LAUNCH_OK();
+    return HETB_OK;
+  }
+  // two passes: the source-major walk leaves ga in gattn, the destination-major walk owns grad_left
+  PLAN_LPR_HW(lpr, hw, (plan_hgt_bwd_walk_kernel<T, L, true, kSaved, HWC><<<grid_for(pl->num_items, groups), kPThreads, smem, st>>>(
                     pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_c,
-                    pl->idx_b, pl->idx_d, pl->row_rel, (int)num_rels, left, kv, msg, mu, attn, lse, gdoto, gout,
-                    grad_left, grad_kv, grad_msg, grad_mu, H, hw, use_smem)));
+                    pl->idx_b, pl->idx_d, pl->row_rel, (int)num_rels, left, kv, msg, mu, nullptr, gdoto, gout,
+                    nullptr, grad_kv, grad_msg, grad_mu, H, hw, use_smem, gattn)));
+  HETB_LAUNCH_OK();
+  if (fwd->num_fix_runs > 0) {
+    PLAN_LPR(lpr, (plan_zero_rows_kernel<L><<<grid_for(fwd->num_fix_runs, groups), kPThreads, 0, st>>>(
+                      fwd->fix_runs, fwd->num_fix_runs, grad_left, nullptr, H, hw)));
+    HETB_LAUNCH_OK();
+  }
+  PLAN_LPR(lpr, (plan_hgt_grad_left_kernel<T, L><<<grid_for(fwd->num_items, groups), kPThreads, 0, st>>>(
+                    fwd->item_ptr, fwd->num_items, (int)fwd->num_positions, fwd->idx_a, fwd->idx_c, kv, gattn,
+                    grad_left, H, hw)));
   HETB_LAUNCH_OK();
   return HETB_OK;
 }
@@ -674,18 +839,49 @@ extern "C" int hetb_hgt_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_r
                  (plan->num_fix_runs == 0 || (plan->fix_runs && grad_msg)));
   HETB_CHECK_ARG(plan->num_items == 0 ||
                  (plan->item_ptr && plan->item_row && plan->nz_rows && plan->nz_ptr && plan->idx_a && plan->idx_b &&
-                  plan->idx_c && plan->idx_d && plan->row_rel && left && kv && msg && mu && attn && lse && out &&
+                  plan->idx_c && plan->row_rel && (plan->idx_d || !attn) && left && kv && msg && mu && lse && out &&
                   gout && gdoto_scratch && grad_left && grad_kv && grad_msg && grad_mu && num_dst > 0));
   cudaStream_t st = (cudaStream_t)stream;
   if (table_dtype == HETB_DTYPE_F32)
-    return hgt_bwd_plan_launch<float>(plan, num_rels, num_dst, (const float *)left, (const float *)kv,
-                                      (const float *)msg, mu, attn, lse, out, gout, gdoto_scratch, grad_left,
-                                      grad_kv, grad_msg, grad_mu, H, F, st);
+    return hgt_bwd_plan_launch<float>(plan, nullptr, num_rels, num_dst, (const float *)left, (const float *)kv,
+                                      (const float *)msg, mu, attn, nullptr, lse, out, gout, gdoto_scratch,
+                                      grad_left, grad_kv, grad_msg, grad_mu, H, F, st);
   if (table_dtype == HETB_DTYPE_BF16)
-    return hgt_bwd_plan_launch<__nv_bfloat16>(plan, num_rels, num_dst, (const __nv_bfloat16 *)left,
-                                              (const __nv_bfloat16 *)kv, (const __nv_bfloat16 *)msg, mu, attn, lse,
-                                              out, gout, gdoto_scratch, grad_left, grad_kv, grad_msg, grad_mu, H, F,
-                                              st);
+    return hgt_bwd_plan_launch<__nv_bfloat16>(plan, nullptr, num_rels, num_dst, (const __nv_bfloat16 *)left,
+                                              (const __nv_bfloat16 *)kv, (const __nv_bfloat16 *)msg, mu, attn,
+                                              nullptr, lse, out, gout, gdoto_scratch, grad_left, grad_kv, grad_msg,
+                                              grad_mu, H, F, st);
+  return HETB_EUNSUPPORTED;
+}
+
+// Two-pass form (see plan_hgt_bwd_walk_kernel<.., TWO_PASS> and plan_hgt_grad_left_kernel): only grad_mu
+// must arrive zero-filled; grad_left, grad_kv and grad_msg are fully written. attn_inout holds the raw scores
+// of the forward on entry and the gradient of the raw scores (forward-plan position order) on return.
+extern "C" int hetb_hgt_fused_bwd_plan2(const hetb_walk_plan *plan, const hetb_walk_plan *fwd_plan, int64_t num_rels,
+                                        int64_t num_dst, const void *left, const void *kv, const void *msg,
+                                        int table_dtype, const float *mu, float *attn_inout, const float *lse,
+                                        const float *out, const float *gout, float *gdoto_scratch, float *grad_left,
+                                        float *grad_kv, float *grad_msg, float *grad_mu, int H, int F, void *stream) {
+  HETB_CHECK_ARG(plan && fwd_plan && plan->num_items >= 0 && num_rels >= 0 && num_dst >= 0);
+  HETB_CHECK_ARG(plan->num_positions == fwd_plan->num_positions && plan->num_positions <= INT32_MAX);
+  HETB_CHECK_ARG((plan->num_fix_rows == 0 || (plan->fix_rows && grad_kv)) &&
+                 (plan->num_fix_runs == 0 || (plan->fix_runs && grad_msg)) &&
+                 (fwd_plan->num_fix_runs == 0 || (fwd_plan->fix_runs && grad_left)));
+  HETB_CHECK_ARG(plan->num_items == 0 ||
+                 (plan->item_ptr && plan->item_row && plan->nz_rows && plan->nz_ptr && plan->idx_a && plan->idx_b &&
+                  plan->idx_c && plan->idx_d && plan->row_rel && fwd_plan->item_ptr && fwd_plan->idx_a &&
+                  fwd_plan->idx_c && left && kv && msg && mu && attn_inout && lse && out && gout && gdoto_scratch &&
+                  grad_left && grad_kv && grad_msg && grad_mu && num_dst > 0));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (table_dtype == HETB_DTYPE_F32)
+    return hgt_bwd_plan_launch<float>(plan, fwd_plan, num_rels, num_dst, (const float *)left, (const float *)kv,
+                                      (const float *)msg, mu, nullptr, attn_inout, lse, out, gout, gdoto_scratch,
+                                      grad_left, grad_kv, grad_msg, grad_mu, H, F, st);
+  if (table_dtype == HETB_DTYPE_BF16)
+    return hgt_bwd_plan_launch<__nv_bfloat16>(plan, fwd_plan, num_rels, num_dst, (const __nv_bfloat16 *)left,
+                                              (const __nv_bfloat16 *)kv, (const __nv_bfloat16 *)msg, mu, nullptr,
+                                              attn_inout, lse, out, gout, gdoto_scratch, grad_left, grad_kv,
+                                              grad_msg, grad_mu, H, F, st);
   return HETB_EUNSUPPORTED;
 }
 
@@ -704,10 +900,10 @@ static int rgat_bwd_plan_launch(const hetb_walk_plan *pl, int64_t num_dst, const
     HETB_LAUNCH_OK();
   }
   if (pl->num_items == 0) return HETB_OK;
-  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, ret, num_dst, gdotr, H,
-                                                                                     hw)));
+  PLAN_LPR(lpr, (plan_rowdot_kernel<L><<<grid_for(num_dst, groups), kPThreads, 0, st>>>(gout, ret, lse, num_dst, gdotr,
+                                                                                     H, hw)));
   HETB_LAUNCH_OK();
-  PLAN_LPR(lpr, (plan_rgat_bwd_walk_kernel<T, L><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
+  PLAN_LPR_HW(lpr, hw, (plan_rgat_bwd_walk_kernel<T, L, HWC><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
                     pl->item_ptr, pl->num_items, pl->idx_a, pl->idx_c, pl->idx_b, pl->row_rel, feat, el, er, lse,
                     gdotr, gout, grad_feat, grad_el, grad_er, H, hw, slope)));
   HETB_LAUNCH_OK();

@@ -974,12 +974,13 @@ void hetb200_hgt_fused_fwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &lef
   const int dt = table_dtype(left_compact, op, "left_compact");
   TORCH_CHECK(table_dtype(k, op, "k") == dt && table_dtype(messages_compact, op, "messages_compact") == dt,
               "torch_hrt::", op, ": left_compact, k and messages_compact must share one dtype");
-  TORCH_CHECK(attn.numel() == pl.num_positions * H && part_m.numel() >= 2 * (int64_t)pl.num_items * H &&
+  // attn: empty = do not save the raw scores (the default backward recomputes them)
+  TORCH_CHECK((attn.numel() == 0 || attn.numel() == pl.num_positions * H) && part_m.numel() >= 2 * (int64_t)pl.num_items * H &&
                   part_acc.numel() >= 2 * (int64_t)pl.num_items * H * F,
               "torch_hrt::", op, ": attn / scratch sizes do not match the plan");
   c10::cuda::CUDAGuard guard(ret.device());
   check_rc(hetb_hgt_fused_fwd_plan(&pl, left_compact.data_ptr(), k.data_ptr(), messages_compact.data_ptr(), dt,
-                                   f32(mu, op, "mu"), f32w(attn, op, "attn"), f32w(lse, op, "lse"),
+                                   f32(mu, op, "mu"), attn.numel() ? f32w(attn, op, "attn") : nullptr, f32w(lse, op, "lse"),
                                    f32w(ret, op, "ret"), f32w(part_m, op, "part_m"), f32w(part_s, op, "part_s"),
                                    f32w(part_acc, op, "part_acc"), f32w(ssum, op, "ssum"), H, F, stream_of(ret)),
            op);
@@ -996,14 +997,41 @@ void hetb200_hgt_fused_bwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &lef
   const int dt = table_dtype(left_compact, op, "left_compact");
   TORCH_CHECK(table_dtype(k, op, "k") == dt && table_dtype(messages_compact, op, "messages_compact") == dt,
               "torch_hrt::", op, ": left_compact, k and messages_compact must share one dtype");
-  TORCH_CHECK(gdoto_scratch.numel() >= out.size(0) * H, "torch_hrt::", op, ": gdoto_scratch too small");
+  TORCH_CHECK(gdoto_scratch.numel() >= 2 * out.size(0) * H, "torch_hrt::", op, ": gdoto_scratch too small ([N, 2H])");
+  TORCH_CHECK(attn.numel() == 0 || attn.numel() == pl.num_positions * H, "torch_hrt::", op, ": attn does not match the plan");
   c10::cuda::CUDAGuard guard(gradout.device());
   check_rc(hetb_hgt_fused_bwd_plan(&pl, mu.size(0), out.size(0), left_compact.data_ptr(), k.data_ptr(),
-                                   messages_compact.data_ptr(), dt, f32(mu, op, "mu"), f32(attn, op, "attn"),
+                                   messages_compact.data_ptr(), dt, f32(mu, op, "mu"),
+                                   attn.numel() ? f32(attn, op, "attn") : nullptr,
                                    f32(lse, op, "lse"), f32(out, op, "out"), f32(gradout, op, "gradout"),
                                    f32w(gdoto_scratch, op, "gdoto_scratch"), f32w(grad_left, op, "grad_left"),
                                    f32w(grad_k, op, "grad_k"), f32w(grad_message_compact, op, "grad_message_compact"),
                                    f32w(grad_mu, op, "grad_mu"), H, F, stream_of(gradout)),
+           op);
+}
+
+// Two-pass form: attn is overwritten with the gradient of the raw scores; grad_left needs no zero-fill.
+void hetb200_hgt_fused_bwd_plan2(Tensor &plan, c10::IntArrayRef meta, Tensor &fwd_plan, c10::IntArrayRef fwd_meta,
+                                 Tensor &left_compact, Tensor &k, Tensor &messages_compact, Tensor &mu, Tensor &attn,
+                                 Tensor &lse, Tensor &out, Tensor &gradout, Tensor &gdoto_scratch, Tensor &grad_left,
+                                 Tensor &grad_k, Tensor &grad_message_compact, Tensor &grad_mu) {
+  const char *op = "hetb200_hgt_fused_bwd_plan2";
+  const hetb_walk_plan pl = unpack_plan(plan, meta, op);
+  const hetb_walk_plan fpl = unpack_plan(fwd_plan, fwd_meta, op);
+  const int H = (int)mu.size(1);
+  const int F = (int)(xlen(out) / H);
+  const int dt = table_dtype(left_compact, op, "left_compact");
+  TORCH_CHECK(table_dtype(k, op, "k") == dt && table_dtype(messages_compact, op, "messages_compact") == dt,
+              "torch_hrt::", op, ": left_compact, k and messages_compact must share one dtype");
+  TORCH_CHECK(gdoto_scratch.numel() >= 2 * out.size(0) * H, "torch_hrt::", op, ": gdoto_scratch too small ([N, 2H])");
+  TORCH_CHECK(attn.numel() == pl.num_positions * H, "torch_hrt::", op, ": attn does not match the plan");
+  c10::cuda::CUDAGuard guard(gradout.device());
+  check_rc(hetb_hgt_fused_bwd_plan2(&pl, &fpl, mu.size(0), out.size(0), left_compact.data_ptr(), k.data_ptr(),
+                                    messages_compact.data_ptr(), dt, f32(mu, op, "mu"), f32w(attn, op, "attn"),
+                                    f32(lse, op, "lse"), f32(out, op, "out"), f32(gradout, op, "gradout"),
+                                    f32w(gdoto_scratch, op, "gdoto_scratch"), f32w(grad_left, op, "grad_left"),
+                                    f32w(grad_k, op, "grad_k"), f32w(grad_message_compact, op, "grad_message_compact"),
+                                    f32w(grad_mu, op, "grad_mu"), H, F, stream_of(gradout)),
            op);
 }
 
@@ -1031,7 +1059,7 @@ void hetb200_rgat_fused_bwd_plan(Tensor &plan, c10::IntArrayRef meta, Tensor &fe
   const hetb_walk_plan pl = unpack_plan(plan, meta, op);
   const int H = (int)xlen(el);
   const int F = (int)(xlen(ret) / H);
-  TORCH_CHECK(gdotr_scratch.numel() >= ret.size(0) * H, "torch_hrt::", op, ": gdotr_scratch too small");
+  TORCH_CHECK(gdotr_scratch.numel() >= 2 * ret.size(0) * H, "torch_hrt::", op, ": gdotr_scratch too small ([N, 2H])");
   c10::cuda::CUDAGuard guard(gradout.device());
   check_rc(hetb_rgat_fused_bwd_plan(&pl, ret.size(0), feat_compact.data_ptr(),
                                     table_dtype(feat_compact, op, "feat_compact"), f32(el, op, "el"),
@@ -1595,6 +1623,7 @@ TORCH_LIBRARY_FRAGMENT(torch_hrt, m) {
   m.def("hetb200_typed_linear_bf16out", hetb200_typed_linear_bf16out);
   m.def("hetb200_hgt_fused_fwd_plan", hetb200_hgt_fused_fwd_plan);
   m.def("hetb200_hgt_fused_bwd_plan", hetb200_hgt_fused_bwd_plan);
+  m.def("hetb200_hgt_fused_bwd_plan2", hetb200_hgt_fused_bwd_plan2);
   m.def("hetb200_rgat_fused_fwd_plan", hetb200_rgat_fused_fwd_plan);
   m.def("hetb200_rgat_fused_bwd_plan", hetb200_rgat_fused_bwd_plan);
   m.def("hetb200_column_sum", hetb200_column_sum);

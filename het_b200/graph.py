@@ -205,7 +205,7 @@ class HetGraph:
             pl["scratch"][key] = {
                 "part_m": torch.empty(2 * G * H, **f32), "part_s": torch.empty(2 * G * H, **f32),
                 "part_acc": torch.empty(2 * G * D, **f32), "ssum": torch.empty(self.num_nodes * H, **f32),
-                "gdot": torch.empty(self.num_nodes * H, **f32),
+                "gdot": torch.empty(2 * self.num_nodes * H, **f32),  # (lse, <gout, out>) pairs per destination
             }
         return pl["scratch"][key]
 

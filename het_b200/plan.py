@@ -16,7 +16,9 @@ the library's own stable radix sort (``K.hetb200_stable_sort_by_key``) on the GP
 Work items are ~``ITEM`` consecutive positions. A candidate boundary k·ITEM that falls inside a
 unit (forward: a destination row; backward: a run) no longer than ITEM is moved back to the unit's
 start, so such units are never split: only power-law hubs are, and those are listed
-(``fix_rows`` / ``fix_runs`` / the forward partial slots) instead of discovered at run time.
+(``fix_rows`` / ``fix_runs`` / the forward partial slots) instead of discovered at run time. A forward
+plan also lists the compact (relation, destination) rows cut by an item boundary (``fix_runs``): the
+second walk of the two-pass HGT backward owns every other such row outright.
 """
 from __future__ import annotations
 
@@ -82,8 +84,18 @@ def forward_arrays(dst_sorted, num_dst, idx_src, idx_urow, idx_ucol, ucol_rel, i
         pslot = pslot_row = g[:0]
     nz_word = nz.clone()
     nz_word[split] += _SPLIT
+    # compact (relation, destination) rows cut by an item boundary (inside split rows only): the second walk of
+    # the two-pass HGT backward pre-zeroes them and reduces their pieces
+    if E > 0:
+        change = torch.ones(E, dtype=torch.bool, device=dst_sorted.device)
+        change[1:] = idx_ucol[1:] != idx_ucol[:-1]
+        run_start = torch.nonzero(change, as_tuple=False).view(-1)
+        run_ptr = torch.cat([run_start, torch.tensor([E], dtype=torch.int64, device=dst_sorted.device)])
+        split_runs = idx_ucol[run_start][_split_units(run_ptr, item_ptr)]
+    else:
+        split_runs = item_ptr[:0]
     return dict(num_positions=E, item_ptr=item_ptr, item_row=item_row, nz_rows=nz_word, nz_ptr=nz_ptr,
-                fix_rows=nz[split], empty_rows=empty, pslot=pslot, pslot_row=pslot_row, fix_runs=None,
+                fix_rows=nz[split], empty_rows=empty, pslot=pslot, pslot_row=pslot_row, fix_runs=split_runs,
                 idx_a=idx_src, idx_b=idx_urow, idx_c=idx_ucol, idx_d=None, row_rel=ucol_rel)
 
 
@@ -140,6 +152,7 @@ class WalkPlan:
 def pack(arrays: dict, device, keep_arrays=False) -> WalkPlan:
     lim = (1 << 31) - 1
     parts, offs, pos = [], {}, 0
+
     for name in _ORDER:
         t = arrays.get(name)
         if t is None:

@@ -376,6 +376,8 @@ int hetb_expand_row_ptr(const int64_t *row_ptr, int64_t num_rows,
  * have positions: nz_rows[j] = row id, bit 31 set when the row is split across items;
  * nz_ptr[j] = first position). fix_rows: rows the pass accumulates into by reduction (pre-zeroed;
  * a forward pass also merges and normalises them); a backward plan lists empty rows there too.
+ * fix_runs: backward plan: compact (relation, source) rows split across items; forward plan: compact
+ * (relation, destination) rows split across items (hetb_hgt_fused_bwd_plan2's second walk).
  * empty_rows (forward): rows without positions (zero-filled). pslot / pslot_row (forward): the
  * valid partial slots (2*item + {0: head row, 1: tail row}) of split rows and the row of each. */
 typedef struct hetb_walk_plan {
@@ -391,10 +393,11 @@ typedef struct hetb_walk_plan {
  * OpExport/RGNNOps.inc.h:609-658; hgt_full_graph_edge_softmax_ops_csr: OpExport/HGTOps.inc.h:190-203;
  * hgt_full_graph_message_mean_aggregation_csr: :180-188) on compact inputs (kind 2 direct indexing,
  * kernel_enums.h:6-119).  left [Uc,H,F] compact (relation, destination) rows (W_att·q), kv [Nsrc,H,F]
- * (k), msg [Ur,H,F] compact (relation, source) rows, mu [R,H].  Writes attn [E,H] (the raw score, in
- * FORWARD-PLAN POSITION order), lse [N,H] (log-sum-exp of mu·attn per destination and head; replaces
- * the reference's per-edge exp and per-node sum), ret [N,H,F].  Scratch: part_m / part_s
- * [2*num_items,H], part_acc [2*num_items,H*F], ssum [N,H]. */
+ * (k), msg [Ur,H,F] compact (relation, source) rows, mu [R,H].  Writes lse [N,H] (log-sum-exp of
+ * mu·attn per destination and head; replaces the reference's per-edge exp and per-node sum), ret [N,H,F]
+ * and, when attn is not NULL, attn [E,H] (the raw score, in FORWARD-PLAN POSITION order; the default
+ * backward recomputes it and the default forward passes NULL: nothing is saved per edge).  Scratch:
+ * part_m / part_s [2*num_items,H], part_acc [2*num_items,H*F], ssum [N,H]. */
 int hetb_hgt_fused_fwd_plan(const hetb_walk_plan *plan, const void *left, const void *kv, const void *msg,
                             int table_dtype, const float *mu, float *attn, float *lse, float *ret, float *part_m,
                             float *part_s, float *part_acc, float *ssum, int H, int F, void *stream);
@@ -402,12 +405,29 @@ int hetb_hgt_fused_fwd_plan(const hetb_walk_plan *plan, const void *left, const 
 /* Backward of the above in one walk (a6 + a12: backward_inner_product_right_node_separatecoo
  * OpExport/RGNNOps.inc.h:1131-1181; backward_hgt_full_graph_{message_mean_aggregation,edge_softmax_ops}_csr
  * OpExport/HGTOps.inc.h:477-487, 553-566). grad_left [Uc,H,F] and grad_mu [R,H] must arrive
- * zero-filled; grad_kv [Nsrc,H,F] and grad_msg [Ur,H,F] are fully written. gdoto_scratch [N,H]. */
+ * zero-filled; grad_kv [Nsrc,H,F] and grad_msg [Ur,H,F] are fully written. gdoto_scratch [N,2H]
+ * ((lse, <gout,out>) pairs per destination). attn = NULL (the default): the raw score is recomputed from
+ * left and kv, in the forward's operation order (same bits); attn given: read at the edge's forward
+ * position (one more random access per edge). */
 int hetb_hgt_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_rels, int64_t num_dst, const void *left,
                             const void *kv, const void *msg, int table_dtype, const float *mu, const float *attn,
                             const float *lse, const float *out, const float *gout, float *gdoto_scratch,
                             float *grad_left, float *grad_kv, float *grad_msg, float *grad_mu, int H, int F,
                             void *stream);
+
+/* The same backward in two walks (the default of het_b200/backend.py): the (source, relation)-ordered walk
+ * of `plan` owns grad_kv / grad_msg as above but does not reduce into grad_left; it leaves the gradient of
+ * the raw score in attn_inout (forward-plan position order, in place of the score it read there), and a
+ * second walk over `fwd_plan` (the forward pass's (destination, relation) order) owns grad_left [Uc,H,F] as a
+ * register accumulator per compact (relation, destination) row: no atomics on the destination side
+ * (the reference: one atomicAdd per edge and element, RGNN/InnerProductEdgeParallel.cu.h:119-202), no
+ * zero-fill of grad_left, run-to-run identical results. Only grad_mu must arrive zero-filled. fwd_plan
+ * must carry fix_runs (the compact (relation, destination) rows cut by an item boundary). */
+int hetb_hgt_fused_bwd_plan2(const hetb_walk_plan *plan, const hetb_walk_plan *fwd_plan, int64_t num_rels,
+                             int64_t num_dst, const void *left, const void *kv, const void *msg, int table_dtype,
+                             const float *mu, float *attn_inout, const float *lse, const float *out,
+                             const float *gout, float *gdoto_scratch, float *grad_left, float *grad_kv,
+                             float *grad_msg, float *grad_mu, int H, int F, void *stream);
 
 /* RGAT logits + edge softmax (max-subtracted, online) + aggregation in one walk: a7
  * (relational_fused_gat_csr, OpExport/RGATOps.inc.h:251-277) on compact inputs: feat [Ur,H,F], el [Ur,H]
@@ -418,7 +438,7 @@ int hetb_rgat_fused_fwd_plan(const hetb_walk_plan *plan, const void *feat, int t
                              float *part_acc, float *ssum, int H, int F, void *stream);
 
 /* Backward of the above (a9: backward_relational_fused_gat_csr, OpExport/RGATOps.inc.h:430-461).
- * grad_er [Uc,H] must arrive zero-filled; grad_feat / grad_el are fully written. gdotr_scratch [N,H]. */
+ * grad_er [Uc,H] must arrive zero-filled; grad_feat / grad_el are fully written. gdotr_scratch [N,2H]. */
 int hetb_rgat_fused_bwd_plan(const hetb_walk_plan *plan, int64_t num_dst, const void *feat, int table_dtype,
                              const float *el, const float *er, const float *lse, const float *ret,
                              const float *gout, float *gdotr_scratch, float *grad_feat, float *grad_el,

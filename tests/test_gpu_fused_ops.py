@@ -55,10 +55,15 @@ HGT_CASES = [
 
 
 @pytest.mark.parametrize("n_dst,n_src,e,r,H,F,hub,gaps", HGT_CASES)
-@pytest.mark.parametrize("impl", ["plan", "csr"])
-def test_hgt_fused_attention_aggregation_op(cuda, n_dst, n_src, e, r, H, F, hub, gaps, impl):
+@pytest.mark.parametrize("impl", ["plan", "plan_saved_scores", "plan_two_pass", "csr"])
+def test_hgt_fused_attention_aggregation_op(cuda, n_dst, n_src, e, r, H, F, hub, gaps, impl, monkeypatch):
+    """plan = the default (one backward walk that recomputes the raw score; the forward saves nothing per
+    edge); plan_saved_scores = the forward stores the score, the backward reads it; plan_two_pass =
+    hetb_hgt_fused_bwd_plan2 (grad_left owned by a second, destination-major walk: no atomics)."""
     from het_b200 import backend as B
-    fused = (B.hgt_fused_attention_and_aggregation_plan if impl == "plan"
+    monkeypatch.setattr(B, "SAVE_HGT_SCORES", impl == "plan_saved_scores")
+    monkeypatch.setattr(B, "TWO_PASS_HGT_BACKWARD", impl == "plan_two_pass")
+    fused = (B.hgt_fused_attention_and_aggregation_plan if impl.startswith("plan")
              else B.hgt_fused_attention_and_aggregation_csr_compact)
     g = _graph(cuda, n_dst, n_src, e, r, seed=e + H + int(hub), hub=hub, gaps=gaps)
     u = g.get_separate_unique_node_indices_single_sided()
@@ -96,6 +101,61 @@ def test_hgt_fused_attention_aggregation_op(cuda, n_dst, n_src, e, r, H, F, hub,
     # empty destination rows are exactly zero, not garbage
     empty = (ic["row_ptrs"][1:] == ic["row_ptrs"][:-1])
     assert float(out[empty].abs().sum()) == 0.0
+
+
+def test_hgt_two_pass_backward_is_deterministic_and_needs_no_zero_fill(cuda):
+    """grad_left of the two-pass backward: NaN-filled on entry (every row is written), bit-identical
+    across runs (no atomics outside the hub runs the plan lists), equal to the single walk to fp32 rounding."""
+    from het_b200.kernels import K
+    n, e, r, H, F = 500, 60000, 5, 4, 16
+    g = _graph(cuda, n, n, e, r, seed=9, hub=True)
+    u = g.get_separate_unique_node_indices_single_sided()
+    pl = g.get_edge_plan()
+    assert pl["fwd"].meta[6] > 0, "the hub row should cut (relation, destination) runs"
+    Ur, Uc = u["node_indices_row"].numel(), u["node_indices_col"].numel()
+    torch.manual_seed(4)
+    left, k, msg = (torch.randn(m, H, F, device=cuda) for m in (Uc, n, Ur))
+    mu = torch.rand(r, H, device=cuda) + 0.5
+    sc = g.plan_scratch(H, H * F)
+    out, lse = torch.empty(n, H, F, device=cuda), torch.empty(n, H, device=cuda)
+    attn = torch.empty(e, H, device=cuda)
+    K.hetb200_hgt_fused_fwd_plan(pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu, attn, lse, out, sc["part_m"],
+                                 sc["part_s"], sc["part_acc"], sc["ssum"])
+    gout = torch.randn_like(out)
+    res = []
+    for _ in range(2):
+        a2 = attn.clone()
+        gl = torch.full((Uc, H, F), float("nan"), device=cuda)
+        gk, gm = torch.full_like(k, float("nan")), torch.full_like(msg, float("nan"))
+        gmu = torch.zeros_like(mu)
+        K.hetb200_hgt_fused_bwd_plan2(pl["bwd"].blob, pl["bwd"].meta, pl["fwd"].blob, pl["fwd"].meta, left, k, msg, mu,
+                                      a2, lse, out, gout, sc["gdot"], gl, gk, gm, gmu)
+        res.append((gl, gk, gm))
+    unsplit = torch.ones(Uc, dtype=torch.bool, device=cuda)
+    fix = pl["fwd"].blob[pl["fwd"].meta[7 + 8]: pl["fwd"].meta[7 + 8] + pl["fwd"].meta[6]].long()
+    unsplit[fix] = False
+    assert torch.equal(res[0][0][unsplit], res[1][0][unsplit])
+    # the single walk, with the saved scores and with the scores recomputed (the default): the recomputed
+    # score is the forward's bit for bit, so grad_k / grad_msg (no atomics on unsplit rows) are identical
+    outs = []
+    for a_in in (attn, torch.empty(0, H, device=cuda)):
+        gl1 = torch.zeros(Uc, H, F, device=cuda)
+        gk1, gm1, gmu1 = torch.empty_like(k), torch.empty_like(msg), torch.zeros_like(mu)
+        K.hetb200_hgt_fused_bwd_plan(pl["bwd"].blob, pl["bwd"].meta, left, k, msg, mu, a_in, lse, out, gout, sc["gdot"],
+                                     gl1, gk1, gm1, gmu1)
+        outs.append((gl1, gk1, gm1))
+        close(res[0][0], gl1.cpu(), "two-pass vs single-walk grad_left", rtol=2e-5, atol=2e-6)
+    bw = pl["bwd"]
+    rows_ok = torch.ones(n, dtype=torch.bool, device=cuda)
+    rows_ok[bw.blob[bw.meta[7 + 4]: bw.meta[7 + 4] + bw.meta[3]].long()] = False          # fix_rows: reduced
+    runs_ok = torch.ones(Ur, dtype=torch.bool, device=cuda)
+    runs_ok[bw.blob[bw.meta[7 + 8]: bw.meta[7 + 8] + bw.meta[6]].long()] = False          # fix_runs: reduced
+    assert int(runs_ok.sum()) > 0
+    for name, got in (("recomputed scores", outs[1]), ("two-pass", res[0])):
+        close(got[1], outs[0][1].cpu(), f"grad_k ({name})", rtol=2e-5, atol=2e-6)
+        close(got[2], outs[0][2].cpu(), f"grad_msg ({name})", rtol=2e-5, atol=2e-6)
+        assert torch.equal(got[1][rows_ok], outs[0][1][rows_ok]), f"grad_k of unsplit rows ({name})"
+        assert torch.equal(got[2][runs_ok], outs[0][2][runs_ok]), f"grad_msg of unsplit runs ({name})"
 
 
 RGAT_CASES = [

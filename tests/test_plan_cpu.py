@@ -162,6 +162,46 @@ def test_forward_plan_emulated_walk_matches_softmax_aggregation(seed, n_dst, n_s
     np.testing.assert_allclose(ret, want, rtol=1e-9, atol=1e-12)
     np.testing.assert_allclose(lse[has], want_lse[has], rtol=1e-9, atol=1e-9)
 
+    # second walk of the two-pass HGT backward (plan_hgt_grad_left_kernel) over the same items: a compact
+    # (relation, destination) row is stored by exactly one lane group unless an item boundary cuts it, in
+    # which case it is listed in fix_runs (pre-zeroed) and its pieces reduce
+    Uc = ucol_rel.size
+    val = g.normal(size=e)
+    gl = np.full(Uc, np.nan)
+    for uc in pl["fix_runs"]:
+        gl[uc] = 0.0
+    fix = set(int(t) for t in pl["fix_runs"])
+    stores_l = np.zeros(Uc, dtype=int)
+    left_of = pl["idx_c"]
+    for gi in range(pl["num_items"]):
+        p0, p1 = ip[gi], ip[gi + 1]
+        cur = left_of[p0]
+        open_head = p0 > 0 and left_of[p0 - 1] == cur
+        acc = 0.0
+
+        def flush_l(open_tail):
+            if open_head or open_tail:
+                assert int(cur) in fix, "a cut run is not listed"
+                gl[cur] += acc
+            else:
+                assert np.isnan(gl[cur]) and int(cur) not in fix
+                gl[cur] = acc
+                stores_l[cur] += 1
+
+        for p in range(p0, p1):
+            if left_of[p] != cur:
+                flush_l(False)
+                open_head = False
+                cur, acc = left_of[p], 0.0
+            acc += val[f[p]]
+        flush_l(p1 < e and left_of[p1] == cur)
+    want_l = np.zeros(Uc)
+    np.add.at(want_l, inv_col, val)
+    assert not np.isnan(gl).any()
+    np.testing.assert_allclose(gl, want_l, rtol=1e-9, atol=1e-9)
+    runlen_c = np.bincount(inv_col, minlength=Uc)
+    assert all(runlen_c[t] > 1 for t in fix)
+
 
 @pytest.mark.parametrize("seed,n_dst,n_src,e,r,hub,item", CASES)
 def test_backward_plan_emulated_walk_owns_every_row_and_run_once(seed, n_dst, n_src, e, r, hub, item):

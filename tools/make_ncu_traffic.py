@@ -28,10 +28,13 @@ for wl, rep in zip(sys.argv[1::2], sys.argv[2::2]):
     hdr, units = rows[0], rows[1]
     col = {h: i for i, h in enumerate(hdr)}
     out[wl] = {}
+    per_kernel = {}  # kernel substring -> max over its captured launches
     for r in rows[2:]:
-        for sub, leg in LEGS[wl].items():
+        for sub in LEGS[wl]:
             if sub in r[col["Kernel Name"]]:
                 b = sum(to_bytes(r[col[k]], units[col[k]]) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-                out[wl][leg] = int(max(out[wl].get(leg, 0), b))
+                per_kernel[sub] = int(max(per_kernel.get(sub, 0), b))
+    for sub, b in per_kernel.items():  # a leg that runs two kernels (the two-pass HGT backward) gets their sum
+        out[wl][LEGS[wl][sub]] = out[wl].get(LEGS[wl][sub], 0) + b
 json.dump(out, open(os.path.join(ROOT, "profiles", "ncu_traffic.json"), "w"), indent=1)
 print(json.dumps(out, indent=1))
