@@ -299,6 +299,132 @@ __global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD_MINB)
 }
 
 // ---------------------------------------------------------------------------
+// plan_fwd_walk_kernel for 64-float rows with EIGHT lanes per lane group (two float4 per lane and row): four
+// independent instruction streams per warp instead of two, and the per-position scalar work (indices, logits,
+// exponentials, row bookkeeping) is executed by half as many lanes. Same arithmetic per element and the same
+// reduction tree over a head's 16 floats (4 per-float4 partial sums are combined in the same order), so the
+// results are those of the 16-lane kernel bit for bit. HETB_FWD_LANES8 selects it.
+// ---------------------------------------------------------------------------
+#ifndef HETB_FWD_LANES8
+#define HETB_FWD_LANES8 0
+#endif
+#ifndef HETB_PLAN_FWD8_MINB
+#define HETB_PLAN_FWD8_MINB 4
+#endif
+
+template <typename T>
+__device__ __forceinline__ void ld_row8(const T *base, int64_t row, int l, float4 &a, float4 &b) {
+  a = ld_row4<T>(base, row, 64, 2 * l);
+  b = ld_row4<T>(base, row, 64, 2 * l + 1);
+}
+
+template <typename T, bool MODE_RGAT, int HW /* lanes per head: 2 (H = 4) or 8 (H = 1) */>
+__global__ void __launch_bounds__(kPThreads, HETB_PLAN_FWD8_MINB)
+    plan_fwd_walk8_kernel(const int *__restrict__ item_ptr, const int *__restrict__ item_row, int num_items,
+                          const int *__restrict__ nz_rows, const int *__restrict__ nz_ptr,
+                          const int *__restrict__ p_src, const int *__restrict__ p_msg,
+                          const int *__restrict__ p_left, const int *__restrict__ ucol_rel,
+                          const T *__restrict__ left, const T *__restrict__ kv, const T *__restrict__ msg,
+                          const float *__restrict__ mu, const float *__restrict__ el,
+                          const float *__restrict__ er, float slope, float *__restrict__ attn,
+                          float *__restrict__ lse, float *__restrict__ ret, float *__restrict__ part_m,
+                          float *__restrict__ part_s, float *__restrict__ part_acc, int H) {
+  constexpr int LPR = 8, D = 64, GROUPS = kPThreads / LPR;
+  const int grp = threadIdx.x / LPR, l = threadIdx.x % LPR;
+  const int g = blockIdx.x * GROUPS + grp;
+  if (g >= num_items) return;
+  const unsigned gm = group_mask<LPR>();
+  const int h = l / HW;
+  const bool leader = (l % HW) == 0;
+  const int p0 = __ldg(item_ptr + g), p1 = __ldg(item_ptr + g + 1);
+  int j = __ldg(item_row + g);
+  int64_t d = __ldg(nz_rows + j) & 0x7fffffff;
+  int row_start = __ldg(nz_ptr + j), row_end = __ldg(nz_ptr + j + 1);
+  float m = kNegInf, s = 0.f;
+  float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
+
+  auto flush = [&]() {
+    if (row_start >= p0 && row_end <= p1) {
+      const float inv = s > 0.f ? 1.f / s : 0.f;
+      st4(ret + d * D + 8 * l, make_float4(acc0.x * inv, acc0.y * inv, acc0.z * inv, acc0.w * inv));
+      st4(ret + d * D + 8 * l + 4, make_float4(acc1.x * inv, acc1.y * inv, acc1.z * inv, acc1.w * inv));
+      if (leader) lse[d * H + h] = m * kLn2 + __logf(s);
+    } else {
+      const int64_t x = 2 * (int64_t)g + (row_start < p0 ? 0 : 1);
+      stcs4(part_acc + x * D + 8 * l, acc0);
+      stcs4(part_acc + x * D + 8 * l + 4, acc1);
+      if (leader) {
+        part_m[x * H + h] = m;
+        part_s[x * H + h] = s;
+        atomic_max_float(lse + d * H + h, m);
+      }
+    }
+  };
+
+  int sn = 0, mi, li;
+  auto load_idx = [&](int p) {
+    const int pp = p < p1 ? p : p1 - 1;
+    mi = __ldg(p_msg + pp);
+    li = __ldg(p_left + pp);
+    if (!MODE_RGAT) sn = __ldg(p_src + pp);
+  };
+  load_idx(p0);
+  for (int p = p0; p < p1; ++p) {
+    float4 mv0, mv1, lv0, lv1, kv0, kv1;
+    float xs;
+    ld_row8<T>(msg, mi, l, mv0, mv1);
+    if (!MODE_RGAT) {
+      ld_row8<T>(left, li, l, lv0, lv1);
+      ld_row8<T>(kv, sn, l, kv0, kv1);
+      xs = __ldg(mu + __ldg(ucol_rel + li) * H + h) * kLog2e;
+    } else {
+      xs = __ldg(el + (int64_t)mi * H + h) + __ldg(er + (int64_t)li * H + h);
+    }
+    if (p + 1 < p1) load_idx(p + 1);
+    if (p == row_end) {
+      flush();
+      ++j;
+      d = __ldg(nz_rows + j) & 0x7fffffff;
+      row_start = p;
+      row_end = __ldg(nz_ptr + j + 1);
+      m = kNegInf; s = 0.f;
+      acc0 = acc1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float x;
+    if (!MODE_RGAT) {
+      // the 16-lane kernel sums a head's four float4 dots as (d0 + d2) + (d1 + d3); lane l here holds d_{2l}, d_{2l+1}
+      // of the row, i.e. (d0, d1) / (d2, d3) of its head: xor-1 first would give (d0 + d1) + (d2 + d3). Reproduce
+      // the 16-lane order: exchange the odd partial first.
+      const float da = score_dot4(lv0, kv0), db = score_dot4(lv1, kv1);
+      float a;
+      if (HW == 2) {
+        const float oa = __shfl_xor_sync(gm, da, 1), ob = __shfl_xor_sync(gm, db, 1);
+        a = (da + oa) + (db + ob);
+      } else {
+        a = group_sum_t<HW>(da + db, HW, gm);
+      }
+      if (leader && attn) attn[(int64_t)p * H + h] = a;
+      x = a * xs;
+    } else {
+      x = (xs > 0.f ? xs : slope * xs) * kLog2e;
+    }
+    const float mn = fmaxf(m, x);
+    const float sc = ex2_ftz(m - mn), w = ex2_ftz(x - mn);
+    acc0.x = fmaf(acc0.x, sc, w * mv0.x);
+    acc0.y = fmaf(acc0.y, sc, w * mv0.y);
+    acc0.z = fmaf(acc0.z, sc, w * mv0.z);
+    acc0.w = fmaf(acc0.w, sc, w * mv0.w);
+    acc1.x = fmaf(acc1.x, sc, w * mv1.x);
+    acc1.y = fmaf(acc1.y, sc, w * mv1.y);
+    acc1.z = fmaf(acc1.z, sc, w * mv1.z);
+    acc1.w = fmaf(acc1.w, sc, w * mv1.w);
+    s = fmaf(s, sc, w);
+    m = mn;
+  }
+  flush();
+}
+
+// ---------------------------------------------------------------------------
 // Pre-pass of a backward walk: zero the rows of `buf` ([*, D]) listed in rows[0..n).
 // ---------------------------------------------------------------------------
 template <int LPR>
@@ -703,6 +829,17 @@ static int fwd_plan_launch(const hetb_walk_plan *pl, const T *left, const T *kv,
     HETB_LAUNCH_OK();
   }
   if (pl->num_items == 0) return HETB_OK;
+  if (HETB_FWD_LANES8 && lpr == 16 && (hw == 4 || hw == 16)) {
+    const unsigned grid8 = grid_for(pl->num_items, kPThreads / 8);
+    if (hw == 4)
+      plan_fwd_walk8_kernel<T, RGAT, 2><<<grid8, kPThreads, 0, st>>>(
+          pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_b, pl->idx_c,
+          pl->row_rel, left, kv, msg, mu, el, er, slope, attn, lse, ret, part_m, part_s, part_acc, H);
+    else
+      plan_fwd_walk8_kernel<T, RGAT, 8><<<grid8, kPThreads, 0, st>>>(
+          pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_b, pl->idx_c,
+          pl->row_rel, left, kv, msg, mu, el, er, slope, attn, lse, ret, part_m, part_s, part_acc, H);
+  } else
   PLAN_LPR_HW(lpr, hw, (plan_fwd_walk_kernel<T, L, RGAT, HWC><<<grid_for(pl->num_items, groups), kPThreads, 0, st>>>(
                     pl->item_ptr, pl->item_row, pl->num_items, pl->nz_rows, pl->nz_ptr, pl->idx_a, pl->idx_b,
                     pl->idx_c, pl->row_rel, left, kv, msg, mu, el, er, slope, attn, lse, ret, part_m, part_s,
