@@ -169,10 +169,21 @@ class HetGraph:
         position is the canonical edge id) by one endpoint, done with the library's radix sort; the
         compact (relation, node) row of every position rides along as a payload."""
         if getattr(self, "_edge_plan", None) is None:
+            import os
             from . import plan as P
-            u = self.get_separate_unique_node_indices_single_sided()
             coo = self.separate_coo
             dev = coo["rel_ptrs"].device
+            cache_dir, cache_path, key = os.environ.get("HETB_PLAN_CACHE"), None, None
+            if cache_dir:  # on-disk plan cache (opt-in): keyed by the graph's own index arrays
+                key = P.graph_key(self.num_nodes, self.num_src_nodes, self.num_rels, coo["rel_ptrs"], coo["row_indices"],
+                                  coo["col_indices"], coo["eids"])
+                os.makedirs(cache_dir, exist_ok=True)
+                cache_path = os.path.join(cache_dir, f"hetb_plan_{key}.pt")
+                hit = P.load_plans(cache_path, key, dev)
+                if hit is not None:
+                    self._edge_plan = {"fwd": hit[0], "bwd": hit[1], "fwd_eids": hit[2], "scratch": {}, "from_cache": True}
+                    return self._edge_plan
+            u = self.get_separate_unique_node_indices_single_sided()
             E = self.num_edges
             assert max(E, self.num_nodes, self.num_src_nodes) < (1 << 31) - 1, "plan indices are int32"
             eid = coo["eids"]
@@ -190,7 +201,9 @@ class HetGraph:
             src_sorted = torch.repeat_interleave(torch.arange(self.num_src_nodes, device=dev), b_ptr[1:] - b_ptr[:-1])
             bwd = P.pack(P.backward_arrays(src_sorted, self.num_src_nodes, b_dst, b_urow, b_ucol, fwd_pos[b_eid],
                                            urow_rel), dev)
-            self._edge_plan = {"fwd": fwd, "bwd": bwd, "fwd_eids": f_eid, "scratch": {}}
+            self._edge_plan = {"fwd": fwd, "bwd": bwd, "fwd_eids": f_eid, "scratch": {}, "from_cache": False}
+            if cache_path:
+                P.save_plans(cache_path, key, fwd, bwd, f_eid)
         return self._edge_plan
 
     def plan_scratch(self, H, D):

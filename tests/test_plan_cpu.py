@@ -282,3 +282,30 @@ def test_backward_plan_emulated_walk_owns_every_row_and_run_once(seed, n_dst, n_
         assert runlen[u] > item
     for s_ in pl["fix_rows"]:
         assert outdeg[s_] == 0 or outdeg[s_] > 1       # an empty row, or a row with an interior boundary
+
+
+def test_plan_cache_round_trip_and_key(tmp_path):
+    """On-disk plan cache (het_b200/plan.py: graph_key / save_plans / load_plans): what is loaded is what was
+    saved; another graph, another item size or a truncated file is a miss, never a wrong plan."""
+    src, dst, rel = _random_graph(3, 60, 50, 900, 4, True)
+    fwd, bwd, f, b, *_ = _plans(src, dst, rel, 60, 50, 16)
+    T = torch.from_numpy
+    key = P.graph_key(60, 50, 4, T(src), T(dst), T(rel))
+    assert key == P.graph_key(60, 50, 4, T(src), T(dst), T(rel))
+    src2 = src.copy()
+    src2[17] = (src2[17] + 1) % 50
+    assert key != P.graph_key(60, 50, 4, T(src2), T(dst), T(rel))
+    assert key != P.graph_key(60, 50, 4, T(src), T(dst), T(rel), item=8)
+    path = str(tmp_path / "plan.pt")
+    assert P.load_plans(path, key, "cpu") is None
+    P.save_plans(path, key, fwd, bwd, T(f))
+    got = P.load_plans(path, key, "cpu")
+    assert got is not None
+    for a, w in ((got[0], fwd), (got[1], bwd)):
+        assert torch.equal(a.blob, w.blob) and a.meta == w.meta and a.num_items == w.num_items
+        assert a.num_positions == w.num_positions
+    assert torch.equal(got[2], T(f))
+    assert P.load_plans(path, "0" * 40, "cpu") is None       # a plan of another graph
+    with open(path, "r+b") as fh:
+        fh.truncate(100)
+    assert P.load_plans(path, key, "cpu") is None            # a damaged file
