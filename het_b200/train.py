@@ -18,6 +18,9 @@ is) and returns the loss as a Python float (a device→host read).
 """
 from __future__ import annotations
 
+import contextlib
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as Fn
@@ -27,6 +30,23 @@ from . import parallel
 from .graph import HetGraph
 from .graphs import HeteroCOO
 from .models import HET_HGT_DGLHetero, HET_RelGraphEmbed, HET_RGATModel, HET_RGCNModel
+
+
+_NVTX = os.environ.get("HETB_NVTX", "0") == "1"
+
+
+@contextlib.contextmanager
+def _nvtx_range(name):
+    torch.cuda.nvtx.range_push(name)
+    try:
+        yield
+    finally:
+        torch.cuda.nvtx.range_pop()
+
+
+@contextlib.contextmanager
+def _no_range(name):
+    yield
 
 
 class HetbAdam:
@@ -146,13 +166,20 @@ class FullGraphTrainer:
             h0, labels, opt = self.embed(), self.labels, self.opt_embed
         else:
             h0, labels, opt = self.x_in, self.labels_in, self.opt_feat
-        logits = self.forward(h0)
-        # = Fn.nll_loss(Fn.log_softmax(logits, dim=-1), labels, reduction="sum") / num_nodes_total, fused
-        loss = B.softmax_cross_entropy(logits, labels, self.num_nodes_total)
-        loss.backward()
-        if self.world > 1:
-            parallel.all_reduce_grads(list(self.model.parameters()), self.group)
-        opt.step()
+        # NVTX ranges (the reference brackets its phases with nvtx.range_push/pop,
+        # hrt/python/RGNNUtils/RGNNUtils.py:291-345) when HETB_NVTX=1: host-side markers, legal under graph capture
+        rng = _nvtx_range if _NVTX else _no_range
+        with rng("hetb200/forward"):
+            logits = self.forward(h0)
+        with rng("hetb200/loss"):
+            # = Fn.nll_loss(Fn.log_softmax(logits, dim=-1), labels, reduction="sum") / num_nodes_total, fused
+            loss = B.softmax_cross_entropy(logits, labels, self.num_nodes_total)
+        with rng("hetb200/backward"):
+            loss.backward()
+            if self.world > 1:
+                parallel.all_reduce_grads(list(self.model.parameters()), self.group)
+        with rng("hetb200/adam"):
+            opt.step()
         return loss.detach()
 
     def _zero(self, mode):
